@@ -1,0 +1,138 @@
+// common.cuh — shared helpers for the lodgs kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "../../include/lodgs.h"
+
+#define TILE_X 16
+#define TILE_Y 16
+#define TILE_PIX 256
+
+namespace lodgs {
+
+void set_error(const char* fmt, ...);
+void count_launch();
+int check_cuda(cudaError_t e, const char* what);
+
+#define LODGS_CUDA(call)                                              \
+    do {                                                              \
+        cudaError_t e__ = (call);                                     \
+        if (e__ != cudaSuccess) return ::lodgs::check_cuda(e__, #call); \
+    } while (0)
+
+#define LODGS_LAUNCHED(name)                                          \
+    do {                                                              \
+        ::lodgs::count_launch();                                      \
+        cudaError_t e__ = cudaGetLastError();                         \
+        if (e__ != cudaSuccess) return ::lodgs::check_cuda(e__, name); \
+    } while (0)
+
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// ---- 3x3 column-major matrix with glm-compatible semantics: m[c][r], product
+// R[c][r] = A[0][r]*B[c][0] + A[1][r]*B[c][1] + A[2][r]*B[c][2] summed left to right. Keeping the same
+// expression trees as the reference's glm calls lets nvcc contract them into the same FMA chains, which
+// is what makes radii / rects / tile counts bit-identical (SURVEY §7 hard part 1).
+struct mat3 {
+    float m[3][3];
+    __host__ __device__ mat3() {}
+    __host__ __device__ mat3(float a0, float a1, float a2, float b0, float b1, float b2, float c0, float c1, float c2) {
+        m[0][0] = a0; m[0][1] = a1; m[0][2] = a2;
+        m[1][0] = b0; m[1][1] = b1; m[1][2] = b2;
+        m[2][0] = c0; m[2][1] = c1; m[2][2] = c2;
+    }
+    __host__ __device__ float* operator[](int c) { return m[c]; }
+    __host__ __device__ const float* operator[](int c) const { return m[c]; }
+};
+
+__host__ __device__ inline mat3 mul(const mat3& a, const mat3& b) {
+    mat3 r;
+#pragma unroll
+    for (int c = 0; c < 3; c++)
+#pragma unroll
+        for (int k = 0; k < 3; k++) r.m[c][k] = a.m[0][k] * b.m[c][0] + a.m[1][k] * b.m[c][1] + a.m[2][k] * b.m[c][2];
+    return r;
+}
+__host__ __device__ inline mat3 transpose(const mat3& a) {
+    mat3 r;
+#pragma unroll
+    for (int c = 0; c < 3; c++)
+#pragma unroll
+        for (int k = 0; k < 3; k++) r.m[c][k] = a.m[k][c];
+    return r;
+}
+
+// ---- decoupled look-back (single-pass chained scan) state word: {flag:2 | value:62} packed in u64.
+// flag 0 = empty, 1 = aggregate available, 2 = inclusive prefix available.
+__device__ __forceinline__ unsigned long long pack_state(unsigned flag, unsigned long long v) {
+    return (static_cast<unsigned long long>(flag) << 62) | v;
+}
+__device__ __forceinline__ unsigned long long ld_relaxed(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// Look back from tile `tile` (>0) for the exclusive prefix; called by one full warp. Returns the
+// exclusive prefix to all lanes.
+__device__ __forceinline__ unsigned long long lookback_warp(const unsigned long long* state, int tile) {
+    const unsigned lane = threadIdx.x & 31;
+    unsigned long long exclusive = 0;
+    int base = tile - 1;
+    while (true) {
+        int idx = base - (int)lane;
+        unsigned long long s = pack_state(2, 0);  // virtual tile before 0: inclusive prefix 0
+        if (idx >= 0) {
+            do { s = ld_relaxed(state + idx); } while ((s >> 62) == 0);
+        }
+        unsigned flag = (unsigned)(s >> 62);
+        unsigned long long val = s & ((1ull << 62) - 1);
+        unsigned incl_mask = __ballot_sync(0xffffffffu, flag == 2);
+        // lanes strictly before (closer to us than) the first inclusive one contribute aggregates
+        int first = incl_mask ? (__ffs(incl_mask) - 1) : 32;
+        unsigned long long contrib = ((int)lane <= first) ? val : 0ull;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, o);
+        exclusive += contrib;
+        if (incl_mask) break;
+        base -= 32;
+    }
+    return exclusive;
+}
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// ---- mbarrier + 1-D bulk async copy (TMA unit; SASS: UBLKCP)
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, unsigned bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_addr(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_addr(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+    unsigned ok;
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(ok)
+            : "r"(smem_addr(bar)), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+
+}  // namespace lodgs

@@ -1,0 +1,185 @@
+/*
+ * lodgs.h — C ABI of the B200-native (sm_100a) hierarchical-LOD Gaussian hot path.
+ *
+ * Drop-in boundary for FelixWindisch/hierarchical-LOD-gaussians. Every entry point takes plain
+ * device/host pointers and sizes, an explicit CUDA stream (passed as void*), never allocates device
+ * memory (the caller owns all tensors and workspaces) and returns 0 on success or a negative
+ * LODGS_E_* code; lodgs_last_error() gives the text. No torch types appear here.
+ *
+ * Each function cites the reference interface it replaces (paths under /root/reference):
+ *   HR = submodules/hierarchy-rasterizer, GH = submodules/gaussianhierarchy, AR = submodules/alt-rasterizer
+ */
+#ifndef LODGS_H_INCLUDED
+#define LODGS_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LODGS_OK 0
+#define LODGS_E_ARG (-1)       /* bad argument (null pointer, negative size, ...) */
+#define LODGS_E_WORKSPACE (-2) /* caller workspace too small */
+#define LODGS_E_CUDA (-3)      /* CUDA runtime error (text in lodgs_last_error) */
+#define LODGS_E_IO (-4)        /* file not found / short read */
+
+/* Text of the last error on this thread ("" if none). */
+const char* lodgs_last_error(void);
+/* Library version, and the SM architecture the kernels were compiled for (100). */
+int lodgs_version(void);
+int lodgs_compiled_sm(void);
+/* Number of kernels launched by this library since load (bench.py's gpu_launches). */
+uint64_t lodgs_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * LOD cut.  Replaces Switching::expandToSize (GH/runtime_switching.cu:997-1030:
+ * markNodesForSize :495-529 + cub InclusiveSum + putRenderIndices :68-93) as bound by
+ * gaussian_hierarchy._C.expand_to_size (GH/torch/torch_interface.cpp:148-167).
+ *   nodes  [N,7] i32  {depth,parent,start,count_leafs,count_merged,start_children,count_children} (GH/types.h:83-92)
+ *   boxes  [N,2,4] f32 {min.xyz,w ; max.xyz,w}                                              (GH/types.h:51-55)
+ *   viewpoint_dev: 3 floats on the DEVICE (the reference dereferences it in the kernel, :1019)
+ * Outputs are written in ascending node-id order into caller buffers (capacity `capacity` entries;
+ * entries beyond capacity are dropped and LODGS_E_WORKSPACE is returned when the count is read back).
+ * count_host: if non-NULL the count is copied back and the stream synchronised (the reference's
+ * blocking cudaMemcpy, :1027-1028); if NULL the call is fully asynchronous and the count stays in
+ * the first int32 of `ws`.
+ * mode: 0 = single-pass flat rule (reference-equivalent work, 60 B/node), 1 = level-synchronous
+ * warp-cooperative traversal (requires lodgs_cut_prepare to have validated monotonicity; falls back to 0).
+ */
+size_t lodgs_cut_workspace_bytes(int N);
+int lodgs_expand_to_size(const int32_t* nodes, const float* boxes, int N, float target_size,
+                         const float* viewpoint_dev, int32_t* render_indices, int32_t* parent_indices,
+                         int32_t* nodes_for_render_indices, int capacity, void* ws, size_t ws_bytes,
+                         int mode, int32_t* count_host, void* stream);
+
+/* One-time hierarchy check for the traversal cut: verifies on the device that along every
+ * parent->child edge box(parent) contains box(child) and w(parent) >= w(child), which makes the
+ * top-down traversal select exactly the flat rule's set. Writes 1/0 to *monotone_host (synchronises). */
+int lodgs_cut_prepare(const int32_t* nodes, const float* boxes, int N, void* ws, size_t ws_bytes,
+                      int32_t* monotone_host, void* stream);
+
+/* Interpolation weights. Replaces Switching::getTsIndexed (GH/runtime_switching.cu:687-714,
+ * computeTsIndexed :588-634) as bound by gaussian_hierarchy._C.get_interpolation_weights
+ * (torch_interface.cpp:200-220). viewpoint is passed BY VALUE (host floats) as in the reference. */
+int lodgs_get_interpolation_weights(const int32_t* node_indices, int K, float target_size,
+                                    const int32_t* nodes, const float* boxes, float vx, float vy, float vz,
+                                    float* ts, int32_t* num_siblings, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Hierarchy file I/O (host only). Replaces HierarchyLoader::load (GH/hierarchy_loader.cpp:26-128)
+ * behind gaussian_hierarchy._C.load_hierarchy (torch_interface.cpp:9-40), and HierarchyWriter::write
+ * (GH/hierarchy_writer.cpp:27-119). Two-call protocol: lodgs_hier_probe gives P and N, then the caller
+ * allocates pos[P,3] shs[P,48] alpha[P] scales[P,3] rot[P,4] nodes[N,7] boxes[N,8] and calls lodgs_hier_load.
+ * Half-compressed files (negative P on disk) are expanded to fp32.
+ */
+int lodgs_hier_probe(const char* filename, int32_t* P, int32_t* N);
+int lodgs_hier_load(const char* filename, float* pos, float* shs, float* alpha, float* scales, float* rot,
+                    int32_t* nodes, float* boxes);
+int lodgs_hier_write(const char* filename, int P, int N, const float* pos, const float* shs, const float* alpha,
+                     const float* scales, const float* rot, const int32_t* nodes, const float* boxes,
+                     int compressed);
+
+/* ------------------------------------------------------------------------------------------------
+ * Rasterizer. Replaces CudaRasterizer::Rasterizer::forward / backward / markVisible
+ * (HR/cuda_rasterizer/rasterizer.h:20-109, rasterizer_impl.cu:203-517) as bound by
+ * diff_gaussian_rasterization._C.rasterize_gaussians[_backward] (HR/rasterize_points.cu:36-245).
+ *
+ * Scratch is three opaque caller-owned byte buffers (the reference's geomBuffer / binningBuffer /
+ * imgBuffer, HR/rasterize_points.cu:85-92); sizes come from the *_bytes functions. The layout is
+ * private to this library but fixed between forward and backward; lodgs_*_layout expose array offsets
+ * for parity tests.
+ *
+ * P     = length of the render list (K if `indices` is non-NULL else fullP)
+ * D, M  = active SH degree, SH coefficients stored per Gaussian
+ * All pointer arguments are DEVICE pointers unless named *_host. Optional inputs are NULL when absent
+ * (the reference's empty-tensor convention).
+ */
+size_t lodgs_geom_bytes(int P);
+size_t lodgs_image_bytes(int W, int H);
+size_t lodgs_binning_bytes(int R);
+
+/* Stage 1: preprocessCUDA (HR forward.cu:218-445) fused with the tile-count prefix sum
+ * (rasterizer_impl.cu:322). Writes radii[P], the geometry state, and the number of
+ * (Gaussian,tile) instances R. If num_rendered_host is non-NULL, R is copied back and the stream
+ * synchronised (rasterizer_impl.cu:330-331). */
+int lodgs_forward_preprocess(int P, int D, int M, int W, int H,
+                             const int32_t* indices, const int32_t* parent_indices, const float* ts,
+                             const float* means3D, const float* shs, const float* colors_precomp,
+                             const float* opacities, const float* scales, float scale_modifier,
+                             const float* rotations, const float* cov3D_precomp,
+                             const float* viewmatrix, const float* projmatrix, const float* campos,
+                             float tan_fovx, float tan_fovy, int32_t* radii,
+                             void* geom_buffer, size_t geom_bytes, int32_t* num_rendered_host, void* stream);
+
+/* Stage 2: duplicateWithKeys (rasterizer_impl.cu:70-115) -> onesweep LSD radix sort on the 64-bit
+ * tile|depth keys (replaces cub::DeviceRadixSort::SortPairs :358-363) -> identifyTileRanges (:120-142)
+ * -> sorted splat records -> renderCUDA (forward.cu:450-596). R is the value stage 1 reported.
+ * out_color [3,H,W]; out_invdepth [H,W] or NULL; seen [P] i32 or NULL (must be zero-filled by the caller,
+ * as the reference's torch::full does). */
+int lodgs_forward_render(int P, int W, int H, int R, const float* background,
+                         const float* ts, const int32_t* kids, const float* colors_precomp,
+                         const int32_t* radii, void* geom_buffer, void* binning_buffer, size_t binning_bytes,
+                         void* image_buffer, size_t image_bytes,
+                         float* out_color, float* out_invdepth, int32_t* seen, void* stream);
+
+/* Backward: renderCUDA bwd (HR backward.cu:498-721) with tile-level gradient reduction, then the
+ * fused computeCov2DCUDA + preprocessCUDA bwd (backward.cu:147-326, :398-495).
+ * All dL_d* outputs are [fullP,...] and must be zero-filled by the caller (rasterize_points.cu:178-187).
+ * dL_dmean2D [fullP,3], dL_dconic [fullP,4], dL_dopacity [fullP], dL_dcolor [fullP,3],
+ * dL_dinvdepth [fullP] or NULL, dL_dmean3D [fullP,3], dL_dcov3D [fullP,6], dL_dsh [fullP,M,3],
+ * dL_dscale [fullP,3], dL_drot [fullP,4]. */
+int lodgs_backward(int P, int fullP, int D, int M, int R, int W, int H, const float* background,
+                   const int32_t* indices, const int32_t* parent_indices, const float* ts, const int32_t* kids,
+                   const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
+                   const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                   const float* viewmatrix, const float* projmatrix, const float* campos,
+                   float tan_fovx, float tan_fovy, const int32_t* radii,
+                   void* geom_buffer, void* binning_buffer, void* image_buffer,
+                   const float* dL_dpix, const float* dL_dinvdepth_pix,
+                   float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                   float* dL_dinvdepth, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
+                   float* dL_dscale, float* dL_drot, void* stream);
+
+/* checkFrustum (HR rasterizer_impl.cu:54-66,145-157): present[i] = (view-space z > 0.2). present is u8[P]. */
+int lodgs_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                       uint8_t* present, void* stream);
+
+/* Parity-test accessors: byte offsets of the arrays inside the opaque buffers.
+ * geom:   [0]=depths f32[P] [1]=means2D f32[P,2] [2]=conic_opacity f32[P,4] [3]=rgb f32[P,3]
+ *         [4]=cov3D f32[P,6] [5]=clamped u8[P] (bit c = channel c clamped) [6]=tiles_touched u32[P]
+ *         [7]=point_offsets u32[P] [8]=rects i32[P,2]
+ * binning:[0]=keys_unsorted u64[R] [1]=values_unsorted u32[R] [2]=keys_sorted u64[R] [3]=point_list u32[R]
+ *         [4]=splat records f32[R,12]
+ * image:  [0]=final_T f32[W*H] [1]=n_contrib u32[W*H] [2]=ranges u32[tiles,2] */
+int lodgs_geom_layout(int P, size_t* offsets9);
+int lodgs_binning_layout(int R, size_t* offsets5);
+int lodgs_image_layout(int W, int H, size_t* offsets3);
+
+/* Stand-alone stable LSD radix sort of (u64 key, u32 value) pairs on bits [0,end_bit) — the onesweep
+ * kernel used inside lodgs_forward_render, exported for the CUB cross-check tests.
+ * ws must be lodgs_sort_workspace_bytes(n). Result is in keys_out/values_out. */
+size_t lodgs_sort_workspace_bytes(int n);
+int lodgs_sort_pairs(const uint64_t* keys_in, const uint32_t* values_in, uint64_t* keys_out,
+                     uint32_t* values_out, uint64_t* keys_tmp, uint32_t* values_tmp, int n, int end_bit,
+                     void* ws, size_t ws_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Sparse Adam. Replaces scene/OurAdam.py Adam.step(relevant) / _single_tensor_adam (:106-176, :251-354):
+ * Adam with bias correction restricted to the rows listed in `relevant` (i64 row indices, or NULL = all
+ * rows, which is _single_tensor_adam2 :357-452). One launch per parameter tensor of `width` floats per row.
+ * step_size = lr / (1 - beta1^step); denom = sqrt(v)/sqrt(1 - beta2^step) + eps (bias terms evaluated
+ * on the host in double as Python does).
+ * bias_correction = 0 gives AR's adamUpdateCUDA (AR/cuda_rasterizer/adam.cu:9-38: no bias correction,
+ * rows masked by `visible` u8[rows] instead of an index list).
+ */
+int lodgs_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq,
+                    const int64_t* relevant, int64_t n_relevant, const uint8_t* visible, int64_t rows,
+                    int width, float lr, float beta1, float beta2, float eps, int64_t step,
+                    int bias_correction, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LODGS_H_INCLUDED */
