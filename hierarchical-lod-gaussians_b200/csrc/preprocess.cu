@@ -1,0 +1,300 @@
+// preprocess.cu — forward per-Gaussian stage: LOD parent interpolation, projection, EWA covariance -> conic,
+// SH -> RGB, tile rectangle, fused with the prefix sum of tile counts.
+//
+// Replaces preprocessCUDA<3> (HR/cuda_rasterizer/forward.cu:218-445) and the following
+// cub::DeviceScan::InclusiveSum (rasterizer_impl.cu:322). One kernel: each 256-Gaussian tile ends with a block
+// scan of tiles_touched and a decoupled look-back, so point_offsets and num_rendered are final when the kernel
+// retires and tiles_touched never makes a second trip through HBM. SH coefficients (192 B per Gaussian at
+// degree 3) and quaternions move as 16-byte vector loads.
+#include "gaussmath.cuh"
+#include "state.cuh"
+#include <cfloat>
+
+namespace lodgs {
+
+struct PreParams {
+    int P, D, M, W, H;
+    const int32_t* indices;
+    const int32_t* parent_indices;
+    const float* ts;
+    const float* means3D;
+    const float* shs;
+    const float* colors_precomp;
+    const float* opacities;
+    const float* scales;
+    float scale_modifier;
+    const float* rotations;
+    const float* cov3D_precomp;
+    const float* viewmatrix;
+    const float* projmatrix;
+    const float* campos;
+    float tan_fovx, tan_fovy, focal_x, focal_y;
+    int32_t* radii;
+    unsigned grid_x, grid_y;
+    int sh_vec4;  // 1 when shs is 16-byte aligned and 3*M is a multiple of 4
+};
+
+// Load the (D+1)^2 RGB coefficient triples of Gaussian `idx`, lerped with parent `pidx` by t when has_parent
+// (interp(), forward.cu:79-85: t*a + (1-t)*b per component).
+__device__ __forceinline__ void load_sh(const PreParams& p, int idx, int pidx, bool has_parent, float t, v3* sh) {
+    const int ncoef = (p.D + 1) * (p.D + 1);
+    const int nfloat = ncoef * 3;
+    float* f = reinterpret_cast<float*>(sh);
+    const float* base = p.shs + (size_t)idx * p.M * 3;
+    const float* pbase = p.shs + (size_t)pidx * p.M * 3;
+    const float omt = 1.0f - t;
+    if (p.sh_vec4) {
+#pragma unroll
+        for (int k = 0; k < 12; k++) {
+            if (k * 4 < nfloat) {
+                float4 a = __ldg(reinterpret_cast<const float4*>(base) + k);
+                if (has_parent) {
+                    float4 b = __ldg(reinterpret_cast<const float4*>(pbase) + k);
+                    a.x = t * a.x + omt * b.x;
+                    a.y = t * a.y + omt * b.y;
+                    a.z = t * a.z + omt * b.z;
+                    a.w = t * a.w + omt * b.w;
+                }
+                f[k * 4 + 0] = a.x; f[k * 4 + 1] = a.y; f[k * 4 + 2] = a.z; f[k * 4 + 3] = a.w;
+            }
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 48; k++) {
+            if (k < nfloat) {
+                float a = __ldg(base + k);
+                if (has_parent) a = t * a + omt * __ldg(pbase + k);
+                f[k] = a;
+            }
+        }
+    }
+}
+
+// Everything preprocessCUDA does for one Gaussian; returns tiles_touched (0 = culled).
+__device__ __forceinline__ uint32_t preprocess_one(const PreParams& p, const GeomState& g, int t_idx, const float* view,
+                                                   const float* proj) {
+    const int r_idx = p.indices ? __ldg(p.indices + t_idx) : t_idx;
+    p.radii[t_idx] = 0;
+
+    int p_idx = 0;
+    float t = 0;
+    bool has_parent = false;
+    float3 p_orig = {__ldg(p.means3D + 3 * (size_t)r_idx), __ldg(p.means3D + 3 * (size_t)r_idx + 1), __ldg(p.means3D + 3 * (size_t)r_idx + 2)};
+    const float3 mean_own = p_orig;
+    if (p.parent_indices) {
+        p_idx = __ldg(p.parent_indices + t_idx);
+        if (p_idx != -1) {
+            has_parent = true;
+            t = __ldg(p.ts + t_idx);
+        }
+    }
+    if (has_parent) {
+        float3 pa = {__ldg(p.means3D + 3 * (size_t)p_idx), __ldg(p.means3D + 3 * (size_t)p_idx + 1), __ldg(p.means3D + 3 * (size_t)p_idx + 2)};
+        p_orig = {t * p_orig.x + (1.0f - t) * pa.x, t * p_orig.y + (1.0f - t) * pa.y, t * p_orig.z + (1.0f - t) * pa.z};
+    }
+
+    float4 p_hom = xform4x4(p_orig, proj);
+    float p_w = 1.0f / (p_hom.w + 0.0000001f);
+    float3 p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
+    float3 p_view = xform4x3(p_orig, view);
+    if (p_view.z <= 0.2f) return 0;
+    // box cull with the default +-FLT_MAX box (rasterizer_impl.cu:262-268): only non-finite means are dropped
+    if (p_orig.x < -FLT_MAX || p_orig.y < -FLT_MAX || p_orig.z < -FLT_MAX || p_orig.x > FLT_MAX || p_orig.y > FLT_MAX ||
+        p_orig.z > FLT_MAX)
+        return 0;
+
+    float cov6[6];
+    if (p.cov3D_precomp == nullptr) {
+        float sx = __ldg(p.scales + 3 * (size_t)r_idx), sy = __ldg(p.scales + 3 * (size_t)r_idx + 1), sz = __ldg(p.scales + 3 * (size_t)r_idx + 2);
+        float4 rot = __ldg(reinterpret_cast<const float4*>(p.rotations) + r_idx);
+        if (has_parent) {
+            float px = __ldg(p.scales + 3 * (size_t)p_idx), py = __ldg(p.scales + 3 * (size_t)p_idx + 1), pz = __ldg(p.scales + 3 * (size_t)p_idx + 2);
+            sx = t * sx + (1.0f - t) * px;
+            sy = t * sy + (1.0f - t) * py;
+            sz = t * sz + (1.0f - t) * pz;
+            float4 o = __ldg(reinterpret_cast<const float4*>(p.rotations) + p_idx);
+            float dot = (rot.x * o.x + rot.y * o.y) + (rot.z * o.z + rot.w * o.w);
+            if (dot < 0.0) { o.x = -o.x; o.y = -o.y; o.z = -o.z; o.w = -o.w; }
+            rot = {t * rot.x + (1.0f - t) * o.x, t * rot.y + (1.0f - t) * o.y, t * rot.z + (1.0f - t) * o.z, t * rot.w + (1.0f - t) * o.w};
+        }
+        cov3d_from_scale_rot(sx, sy, sz, p.scale_modifier, rot, cov6);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 6; k++) cov6[k] = __ldg(p.cov3D_precomp + 6 * (size_t)r_idx + k);
+    }
+#pragma unroll
+    for (int k = 0; k < 6; k++) g.cov3D[6 * (size_t)t_idx + k] = cov6[k];
+
+    float3 cov = project_cov(p_orig, p.focal_x, p.focal_y, p.tan_fovx, p.tan_fovy, cov6, view, nullptr);
+
+    constexpr float h_var = 0.3f;
+    const float det_cov = cov.x * cov.z - cov.y * cov.y;
+    cov.x += h_var;
+    cov.z += h_var;
+    const float det_cov_plus_h_cov = cov.x * cov.z - cov.y * cov.y;
+    const float h_convolution_scaling = sqrtf(max(0.000025f, det_cov / det_cov_plus_h_cov));
+    const float det = det_cov_plus_h_cov;
+    if (det == 0.0f) return 0;
+    float det_inv = 1.f / det;
+    float3 conic = {cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv};
+
+    float mid = 0.5f * (cov.x + cov.z);
+    float lambda1 = mid + sqrtf(max(0.1f, mid * mid - det));
+    float lambda2 = mid - sqrtf(max(0.1f, mid * mid - det));
+    float my_radius = ceilf(3.f * sqrtf(max(lambda1, lambda2)));
+    float2 point_image = {ndc_to_pix(p_proj.x, p.W), ndc_to_pix(p_proj.y, p.H)};
+    uint2 rmin, rmax;
+    const int2 my_rect = {(int)ceilf(3.f * sqrtf(cov.x)), (int)ceilf(3.f * sqrtf(cov.z))};
+    g.rects[t_idx] = my_rect;
+    tile_rect(point_image, my_rect, rmin, rmax, p.grid_x, p.grid_y);
+    if ((rmax.x - rmin.x) * (rmax.y - rmin.y) == 0) return 0;
+
+    if (p.colors_precomp == nullptr) {
+        // view direction from the UN-interpolated mean of r_idx (forward.cu:92: means[idx])
+        float cx = __ldg(p.campos), cy = __ldg(p.campos + 1), cz = __ldg(p.campos + 2);
+        float dx = mean_own.x - cx, dy = mean_own.y - cy, dz = mean_own.z - cz;
+        float len = sqrtf(dx * dx + dy * dy + dz * dz);
+        dx = dx / len; dy = dy / len; dz = dz / len;
+        v3 sh[16];
+        load_sh(p, r_idx, p_idx, has_parent, t, sh);
+        v3 result = sh_to_rgb(p.D, sh, dx, dy, dz);
+        result.x += 0.5f; result.y += 0.5f; result.z += 0.5f;
+        uint8_t cl = (result.x < 0 ? 1 : 0) | (result.y < 0 ? 2 : 0) | (result.z < 0 ? 4 : 0);
+        g.clamped[t_idx] = cl;
+        g.rgb[3 * (size_t)t_idx + 0] = max(result.x, 0.0f);
+        g.rgb[3 * (size_t)t_idx + 1] = max(result.y, 0.0f);
+        g.rgb[3 * (size_t)t_idx + 2] = max(result.z, 0.0f);
+    }
+
+    g.depths[t_idx] = p_view.z;
+    p.radii[t_idx] = (int)my_radius;
+    g.means2D[t_idx] = point_image;
+    float opacity = __ldg(p.opacities + r_idx);
+    if (has_parent) opacity = t * opacity + (1.0f - t) * __ldg(p.opacities + p_idx);
+    g.conic_opacity[t_idx] = {conic.x, conic.y, conic.z, opacity * h_convolution_scaling};
+    return (rmax.y - rmin.y) * (rmax.x - rmin.x);
+}
+
+__global__ void __launch_bounds__(PRE_BLOCK) preprocess_fwd_kernel(const PreParams p, const GeomState g) {
+    __shared__ int s_tile;
+    __shared__ unsigned s_warp_sum[PRE_BLOCK / 32];
+    __shared__ unsigned long long s_prefix;
+    __shared__ float s_view[16], s_proj[16];
+    if (threadIdx.x == 0) s_tile = atomicAdd(&g.hdr->ticket, 1);
+    if (threadIdx.x < 16) s_view[threadIdx.x] = __ldg(p.viewmatrix + threadIdx.x);
+    else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = __ldg(p.projmatrix + threadIdx.x - 16);
+    __syncthreads();
+    const int tile = s_tile;
+    const int t_idx = tile * PRE_BLOCK + threadIdx.x;
+    unsigned tiles = 0;
+    if (t_idx < p.P) {
+        tiles = preprocess_one(p, g, t_idx, s_view, s_proj);
+        g.tiles_touched[t_idx] = tiles;
+    }
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned incl = tiles;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        unsigned v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= (unsigned)o) incl += v;
+    }
+    if (lane == 31) s_warp_sum[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned w = (lane < PRE_BLOCK / 32) ? s_warp_sum[lane] : 0;
+        unsigned wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned v = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= (unsigned)o) wi += v;
+        }
+        if (lane < PRE_BLOCK / 32) s_warp_sum[lane] = wi - w;
+        unsigned block_total = __shfl_sync(0xffffffffu, wi, PRE_BLOCK / 32 - 1);
+        unsigned long long excl = 0;
+        if (tile == 0) {
+            if (lane == 0) st_relaxed(g.scan_state, pack_state(2, block_total));
+        } else {
+            if (lane == 0) st_relaxed(g.scan_state + tile, pack_state(1, block_total));
+            excl = lookback_warp(g.scan_state, tile);
+            if (lane == 0) st_relaxed(g.scan_state + tile, pack_state(2, excl + block_total));
+        }
+        if (lane == 0) {
+            s_prefix = excl;
+            if ((long long)tile * PRE_BLOCK + PRE_BLOCK >= p.P) g.hdr->num_rendered = (unsigned)(excl + block_total);
+        }
+    }
+    __syncthreads();
+    if (t_idx < p.P) g.point_offsets[t_idx] = (unsigned)s_prefix + s_warp_sum[warp] + incl;
+}
+
+__global__ void mark_visible_kernel(int P, const float* __restrict__ means, const float* __restrict__ view, uint8_t* present) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    float3 m = {__ldg(means + 3 * (size_t)i), __ldg(means + 3 * (size_t)i + 1), __ldg(means + 3 * (size_t)i + 2)};
+    float z = view[2] * m.x + view[6] * m.y + view[10] * m.z + view[14];
+    present[i] = !(z <= 0.2f);
+}
+
+}  // namespace lodgs
+
+using namespace lodgs;
+
+extern "C" size_t lodgs_geom_bytes(int P) { return geom_from_chunk(nullptr, P < 0 ? 0 : P).bytes + 128; }
+
+extern "C" int lodgs_geom_layout(int P, size_t* offsets9) {
+    GeomState g = geom_from_chunk(nullptr, P);
+    for (int i = 0; i < 9; i++) offsets9[i] = g.offsets[i];
+    return LODGS_OK;
+}
+
+extern "C" int lodgs_forward_preprocess(int P, int D, int M, int W, int H, const int32_t* indices, const int32_t* parent_indices,
+                                        const float* ts, const float* means3D, const float* shs, const float* colors_precomp,
+                                        const float* opacities, const float* scales, float scale_modifier, const float* rotations,
+                                        const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                                        const float* campos, float tan_fovx, float tan_fovy, int32_t* radii, void* geom_buffer,
+                                        size_t geom_bytes, int32_t* num_rendered_host, void* stream) {
+    if (P < 0 || W <= 0 || H <= 0 || D < 0 || D > 3) { set_error("lodgs_forward_preprocess: bad size argument"); return LODGS_E_ARG; }
+    if (P == 0) { if (num_rendered_host) *num_rendered_host = 0; return LODGS_OK; }
+    if (!means3D || !opacities || !viewmatrix || !projmatrix || !campos || !radii || !geom_buffer) {
+        set_error("lodgs_forward_preprocess: null pointer argument"); return LODGS_E_ARG;
+    }
+    if ((shs == nullptr) == (colors_precomp == nullptr)) { set_error("lodgs_forward_preprocess: provide exactly one of shs / colors_precomp"); return LODGS_E_ARG; }
+    if (((scales == nullptr) || (rotations == nullptr)) == (cov3D_precomp == nullptr)) { set_error("lodgs_forward_preprocess: provide exactly one of scales+rotations / cov3D_precomp"); return LODGS_E_ARG; }
+    if (shs && M < (D + 1) * (D + 1)) { set_error("lodgs_forward_preprocess: M=%d too small for degree %d", M, D); return LODGS_E_ARG; }
+    if (parent_indices && !ts) { set_error("lodgs_forward_preprocess: parent_indices without ts"); return LODGS_E_ARG; }
+    if (geom_bytes < lodgs_geom_bytes(P) - 128) { set_error("lodgs_forward_preprocess: geometry buffer too small"); return LODGS_E_WORKSPACE; }
+    if (((uintptr_t)geom_buffer & 127) != 0) { set_error("lodgs_forward_preprocess: geometry buffer must be 128-byte aligned"); return LODGS_E_ARG; }
+    cudaStream_t s = (cudaStream_t)stream;
+    GeomState g = geom_from_chunk(geom_buffer, P);
+    PreParams p;
+    p.P = P; p.D = D; p.M = M; p.W = W; p.H = H;
+    p.indices = indices; p.parent_indices = parent_indices; p.ts = ts; p.means3D = means3D; p.shs = shs;
+    p.colors_precomp = colors_precomp; p.opacities = opacities; p.scales = scales; p.scale_modifier = scale_modifier;
+    p.rotations = rotations; p.cov3D_precomp = cov3D_precomp; p.viewmatrix = viewmatrix; p.projmatrix = projmatrix;
+    p.campos = campos; p.tan_fovx = tan_fovx; p.tan_fovy = tan_fovy;
+    p.focal_y = H / (2.0f * tan_fovy);
+    p.focal_x = W / (2.0f * tan_fovx);
+    p.radii = radii;
+    p.grid_x = (W + TILE_X - 1) / TILE_X; p.grid_y = (H + TILE_Y - 1) / TILE_Y;
+    p.sh_vec4 = (shs && ((uintptr_t)shs & 15) == 0 && (M * 3) % 4 == 0) ? 1 : 0;
+    if (rotations && ((uintptr_t)rotations & 15) != 0) { set_error("lodgs_forward_preprocess: rotations must be 16-byte aligned"); return LODGS_E_ARG; }
+    LODGS_CUDA(cudaMemsetAsync(geom_buffer, 0, g.zero_bytes, s));
+    int tiles = (P + PRE_BLOCK - 1) / PRE_BLOCK;
+    preprocess_fwd_kernel<<<tiles, PRE_BLOCK, 0, s>>>(p, g);
+    LODGS_LAUNCHED("preprocess_fwd_kernel");
+    if (num_rendered_host) {
+        LODGS_CUDA(cudaMemcpyAsync(num_rendered_host, &g.hdr->num_rendered, sizeof(int), cudaMemcpyDeviceToHost, s));
+        LODGS_CUDA(cudaStreamSynchronize(s));
+    }
+    return LODGS_OK;
+}
+
+extern "C" int lodgs_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present,
+                                  void* stream) {
+    (void)projmatrix;
+    if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) { set_error("lodgs_mark_visible: bad argument"); return LODGS_E_ARG; }
+    if (P == 0) return LODGS_OK;
+    mark_visible_kernel<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream>>>(P, means3D, viewmatrix, present);
+    LODGS_LAUNCHED("mark_visible_kernel");
+    return LODGS_OK;
+}

@@ -1,0 +1,245 @@
+// radix_sort.cu — hand-written onesweep LSD radix sort of (u64 key, u32 value) pairs.
+//
+// Replaces cub::DeviceRadixSort::SortPairs (HR/cuda_rasterizer/rasterizer_impl.cu:358-363). Stable, 8-bit
+// digits over bits [0,end_bit): one histogram pass over the keys builds all digit histograms at once, then one
+// kernel per digit does rank -> decoupled look-back -> scatter, reading and writing every pair exactly once
+// per pass. Stability (and therefore bit-identical output to CUB) comes from ranking keys in index order:
+// warp-striped tiles, per-warp match-any ranking, warps and tiles chained in order.
+#include "state.cuh"
+
+namespace lodgs {
+
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = SORT_TILE / SORT_THREADS;  // 16
+constexpr int SORT_WARPS = SORT_THREADS / 32;
+
+// ---- global histograms for all passes in one read of the keys
+__global__ void __launch_bounds__(256) sort_histogram_kernel(const uint64_t* __restrict__ keys, int n, int passes, unsigned* hist) {
+    __shared__ unsigned s_hist[SORT_MAX_PASSES * SORT_RADIX];
+    for (int i = threadIdx.x; i < passes * SORT_RADIX; i += blockDim.x) s_hist[i] = 0;
+    __syncthreads();
+    const unsigned lane = threadIdx.x & 31;
+    // warp-uniform trip count so the shuffles below are always executed by full warps
+    const int stride = gridDim.x * blockDim.x;
+    for (int base = blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < n; base += stride) {
+        const int i = base + lane;
+        const bool valid = i < n;
+        const uint64_t key = valid ? __ldg(keys + i) : 0ull;
+        const unsigned vmask = __ballot_sync(0xffffffffu, valid);
+        for (int p = 0; p < passes; p++) {
+            const unsigned d = (unsigned)(key >> (8 * p)) & 255u;
+            const unsigned d0 = __shfl_sync(0xffffffffu, d, 0);
+            // degenerate digits (tile high byte, float exponent) are warp-uniform almost always: one add
+            if (__all_sync(0xffffffffu, !valid || d == d0)) {
+                if (lane == 0) atomicAdd(&s_hist[p * SORT_RADIX + d0], __popc(vmask));
+            } else if (valid) {
+                atomicAdd(&s_hist[p * SORT_RADIX + d], 1u);
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < passes * SORT_RADIX; i += blockDim.x) {
+        unsigned v = s_hist[i];
+        if (v) atomicAdd(&hist[i], v);
+    }
+}
+
+// ---- exclusive scan of each pass' 256-bin histogram (one block per pass)
+__global__ void __launch_bounds__(SORT_RADIX) sort_scan_hist_kernel(unsigned* hist) {
+    __shared__ unsigned s_w[8];
+    unsigned* h = hist + blockIdx.x * SORT_RADIX;
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned v = h[threadIdx.x];
+    unsigned incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= (unsigned)o) incl += t;
+    }
+    if (lane == 31) s_w[warp] = incl;
+    __syncthreads();
+    unsigned woff = 0;
+    for (unsigned w = 0; w < warp; w++) woff += s_w[w];
+    h[threadIdx.x] = woff + incl - v;
+}
+
+struct SortSmem {
+    uint64_t keys[SORT_TILE];
+    uint32_t vals[SORT_TILE];
+    unsigned warp_hist[SORT_WARPS][SORT_RADIX];  // per-warp digit counts -> exclusive offsets across warps
+    unsigned digit_start[SORT_RADIX];            // exclusive scan of the tile's digit counts
+    unsigned out_off[SORT_RADIX];                // global base of digit d minus digit_start[d]
+    unsigned scan_w[SORT_WARPS];
+    int tile;
+};
+
+__global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const uint64_t* __restrict__ keys_in,
+                                                                    const uint32_t* __restrict__ vals_in,
+                                                                    uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
+                                                                    int n, int pass, const unsigned* __restrict__ hist_base,
+                                                                    int* ticket, unsigned* lookback /* [tiles][256] */) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    SortSmem& sm = *reinterpret_cast<SortSmem*>(smem_raw);
+    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int shift = 8 * pass;
+    if (tid == 0) sm.tile = atomicAdd(ticket, 1);
+    for (int i = tid; i < SORT_WARPS * SORT_RADIX; i += SORT_THREADS) (&sm.warp_hist[0][0])[i] = 0;
+    __syncthreads();
+    const int tile = sm.tile;
+    const long long tile_base = (long long)tile * SORT_TILE;
+    const int tile_n = (int)min((long long)SORT_TILE, (long long)n - tile_base);
+
+    // ---- load, warp-striped: item k of lane l in warp w is element w*512 + k*32 + l of the tile
+    uint64_t key[SORT_ITEMS];
+    uint32_t val[SORT_ITEMS];
+    unsigned rank[SORT_ITEMS];
+    const int wbase = warp * (32 * SORT_ITEMS);
+#pragma unroll
+    for (int k = 0; k < SORT_ITEMS; k++) {
+        const int e = wbase + k * 32 + lane;
+        if (e < tile_n) {
+            key[k] = __ldg(keys_in + tile_base + e);
+            val[k] = __ldg(vals_in + tile_base + e);
+        } else {
+            key[k] = ~0ull;
+            val[k] = 0;
+        }
+    }
+    // ---- rank inside the warp, item by item (index order => stable)
+    unsigned* wh = sm.warp_hist[warp];
+#pragma unroll
+    for (int k = 0; k < SORT_ITEMS; k++) {
+        const int e = wbase + k * 32 + lane;
+        const bool valid = e < tile_n;
+        const unsigned d = (unsigned)(key[k] >> shift) & 255u;
+        // invalid lanes match on a private value so that they never join a digit group
+        const unsigned mask = __match_any_sync(0xffffffffu, valid ? d : (256u + lane));
+        const int leader = __ffs(mask) - 1;
+        unsigned old = 0;
+        if ((int)lane == leader && valid) {
+            old = wh[d];
+            wh[d] = old + __popc(mask);
+        }
+        old = __shfl_sync(0xffffffffu, old, leader);
+        rank[k] = old + __popc(mask & ((1u << lane) - 1u));
+        __syncwarp();
+    }
+    __syncthreads();
+
+    // ---- per digit (thread d): exclusive offsets across warps, tile count, look-back
+    {
+        const unsigned d = tid;
+        unsigned running = 0;
+#pragma unroll
+        for (int w = 0; w < SORT_WARPS; w++) {
+            unsigned c = sm.warp_hist[w][d];
+            sm.warp_hist[w][d] = running;
+            running += c;
+        }
+        const unsigned count = running;
+        // block exclusive scan over digits for the local reorder
+        unsigned incl = count;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= (unsigned)o) incl += t;
+        }
+        if (lane == 31) sm.scan_w[warp] = incl;
+        // decoupled look-back along the tile chain for this digit; state = {flag:2 | value:30}
+        unsigned* my = lookback + (size_t)tile * SORT_RADIX + d;
+        unsigned excl = 0;
+        if (tile == 0) {
+            atomicExch(my, (2u << 30) | count);
+        } else {
+            atomicExch(my, (1u << 30) | count);
+            for (int t = tile - 1; t >= 0; t--) {
+                const volatile unsigned* prev = lookback + (size_t)t * SORT_RADIX + d;
+                unsigned s;
+                do { s = *prev; } while ((s >> 30) == 0);
+                excl += s & 0x3fffffffu;
+                if ((s >> 30) == 2u) break;
+            }
+            atomicExch(my, (2u << 30) | (excl + count));
+        }
+        __syncthreads();
+        unsigned woff = 0;
+        for (unsigned w = 0; w < warp; w++) woff += sm.scan_w[w];
+        const unsigned dstart = woff + incl - count;
+        sm.digit_start[d] = dstart;
+        sm.out_off[d] = __ldg(hist_base + d) + excl - dstart;  // modular arithmetic: dst = out_off[d] + local index
+    }
+    __syncthreads();
+
+    // ---- reorder inside the tile through shared memory
+#pragma unroll
+    for (int k = 0; k < SORT_ITEMS; k++) {
+        const int e = wbase + k * 32 + lane;
+        if (e < tile_n) {
+            const unsigned d = (unsigned)(key[k] >> shift) & 255u;
+            const unsigned pos = sm.digit_start[d] + sm.warp_hist[warp][d] + rank[k];
+            sm.keys[pos] = key[k];
+            sm.vals[pos] = val[k];
+        }
+    }
+    __syncthreads();
+    // ---- scatter: runs of equal digits go to consecutive global addresses
+    for (int i = tid; i < tile_n; i += SORT_THREADS) {
+        const uint64_t kk = sm.keys[i];
+        const unsigned d = (unsigned)(kk >> shift) & 255u;
+        const unsigned dst = sm.out_off[d] + (unsigned)i;
+        keys_out[dst] = kk;
+        vals_out[dst] = sm.vals[i];
+    }
+}
+
+int sort_pairs_device(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, uint64_t* keys_tmp,
+                      uint32_t* vals_tmp, int n, int end_bit, void* ws, cudaStream_t s) {
+    if (n <= 0) return LODGS_OK;
+    int passes = (end_bit + 7) / 8;
+    if (passes < 1) passes = 1;
+    if (passes > SORT_MAX_PASSES) passes = SORT_MAX_PASSES;
+    SortWs w = sort_from_chunk(ws, n);
+    const size_t tiles = sort_tiles(n);
+    LODGS_CUDA(cudaMemsetAsync(ws, 0, (size_t)((char*)(w.lookback + (size_t)passes * tiles * SORT_RADIX) - (char*)ws), s));
+    static bool attr_set = false;
+    if (!attr_set) {
+        LODGS_CUDA(cudaFuncSetAttribute(sort_onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem)));
+        attr_set = true;
+    }
+    int hist_blocks = (int)min((size_t)148 * 8, ((size_t)n + 255) / 256);
+    sort_histogram_kernel<<<hist_blocks, 256, 0, s>>>(keys_in, n, passes, w.hist);
+    LODGS_LAUNCHED("sort_histogram_kernel");
+    sort_scan_hist_kernel<<<passes, SORT_RADIX, 0, s>>>(w.hist);
+    LODGS_LAUNCHED("sort_scan_hist_kernel");
+    const uint64_t* kin = keys_in;
+    const uint32_t* vin = vals_in;
+    for (int p = 0; p < passes; p++) {
+        const bool to_out = ((passes - 1 - p) % 2) == 0;
+        uint64_t* kout = to_out ? keys_out : keys_tmp;
+        uint32_t* vout = to_out ? vals_out : vals_tmp;
+        sort_onesweep_kernel<<<(unsigned)tiles, SORT_THREADS, sizeof(SortSmem), s>>>(kin, vin, kout, vout, n, p, w.hist + p * SORT_RADIX,
+                                                                                  w.tickets + p,
+                                                                                  w.lookback + (size_t)p * tiles * SORT_RADIX);
+        LODGS_LAUNCHED("sort_onesweep_kernel");
+        kin = kout;
+        vin = vout;
+    }
+    return LODGS_OK;
+}
+
+}  // namespace lodgs
+
+using namespace lodgs;
+
+extern "C" size_t lodgs_sort_workspace_bytes(int n) { return sort_from_chunk(nullptr, n < 0 ? 0 : n).bytes + 128; }
+
+extern "C" int lodgs_sort_pairs(const uint64_t* keys_in, const uint32_t* values_in, uint64_t* keys_out, uint32_t* values_out,
+                                uint64_t* keys_tmp, uint32_t* values_tmp, int n, int end_bit, void* ws, size_t ws_bytes, void* stream) {
+    if (n < 0 || end_bit < 1 || end_bit > 64) { set_error("lodgs_sort_pairs: bad size argument"); return LODGS_E_ARG; }
+    if (n == 0) return LODGS_OK;
+    if (!keys_in || !values_in || !keys_out || !values_out || !keys_tmp || !values_tmp || !ws) { set_error("lodgs_sort_pairs: null pointer"); return LODGS_E_ARG; }
+    if (n >= (1 << 30)) { set_error("lodgs_sort_pairs: n must be < 2^30"); return LODGS_E_ARG; }
+    if (ws_bytes < lodgs_sort_workspace_bytes(n) - 128) { set_error("lodgs_sort_pairs: workspace too small"); return LODGS_E_WORKSPACE; }
+    if (((uintptr_t)ws & 127) != 0) { set_error("lodgs_sort_pairs: workspace must be 128-byte aligned"); return LODGS_E_ARG; }
+    return sort_pairs_device(keys_in, values_in, keys_out, values_out, keys_tmp, values_tmp, n, end_bit, ws, (cudaStream_t)stream);
+}

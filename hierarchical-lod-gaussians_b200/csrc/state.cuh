@@ -1,0 +1,141 @@
+// state.cuh — layout of the three opaque scratch buffers (geometry / binning / image state).
+// Plays the role of GeometryState/BinningState/ImageState::fromChunk (HR/cuda_rasterizer/rasterizer_impl.cu:159-199)
+// but with its own SoA layout: clamp flags packed to one byte, rects kept inside, the scan's look-back
+// states and the sorted per-instance splat records added, no CUB temp.
+#pragma once
+#include "common.cuh"
+
+namespace lodgs {
+
+constexpr int PRE_BLOCK = 256;  // Gaussians per preprocess tile (one look-back state each)
+
+struct GeomHeader {
+    unsigned num_rendered;  // total (Gaussian,tile) instances, written by the last preprocess tile
+    int ticket;             // dynamic tile dispenser for the fused scan
+    int pad[30];
+};
+
+struct GeomState {
+    GeomHeader* hdr;
+    unsigned long long* scan_state;  // [ceil(P/PRE_BLOCK)]
+    float* depths;                   // [P]
+    float2* means2D;                 // [P]
+    float4* conic_opacity;           // [P]
+    float* rgb;                      // [P,3]
+    float* cov3D;                    // [P,6]
+    uint8_t* clamped;                // [P] bit c set = channel c clamped to 0
+    uint32_t* tiles_touched;         // [P]
+    uint32_t* point_offsets;         // [P] inclusive prefix sum of tiles_touched
+    int2* rects;                     // [P]
+    size_t offsets[9];
+    size_t bytes;
+    size_t zero_bytes;  // header + scan states: cleared at the start of every forward
+};
+
+template <typename T>
+static inline T* carve_arr(char* base, size_t& off, size_t count) {
+    off = align_up(off, 128);
+    T* p = reinterpret_cast<T*>(base + off);
+    off += count * sizeof(T);
+    return p;
+}
+
+static inline GeomState geom_from_chunk(void* chunk, size_t P) {
+    GeomState g;
+    char* b = (char*)chunk;
+    size_t off = 0;
+    g.hdr = carve_arr<GeomHeader>(b, off, 1);
+    g.scan_state = carve_arr<unsigned long long>(b, off, (P + PRE_BLOCK - 1) / PRE_BLOCK + 1);
+    g.zero_bytes = off;
+    g.depths = carve_arr<float>(b, off, P);            g.offsets[0] = (char*)g.depths - b;
+    g.means2D = carve_arr<float2>(b, off, P);          g.offsets[1] = (char*)g.means2D - b;
+    g.conic_opacity = carve_arr<float4>(b, off, P);    g.offsets[2] = (char*)g.conic_opacity - b;
+    g.rgb = carve_arr<float>(b, off, P * 3);           g.offsets[3] = (char*)g.rgb - b;
+    g.cov3D = carve_arr<float>(b, off, P * 6);         g.offsets[4] = (char*)g.cov3D - b;
+    g.clamped = carve_arr<uint8_t>(b, off, P);         g.offsets[5] = (char*)g.clamped - b;
+    g.tiles_touched = carve_arr<uint32_t>(b, off, P);  g.offsets[6] = (char*)g.tiles_touched - b;
+    g.point_offsets = carve_arr<uint32_t>(b, off, P);  g.offsets[7] = (char*)g.point_offsets - b;
+    g.rects = carve_arr<int2>(b, off, P);              g.offsets[8] = (char*)g.rects - b;
+    g.bytes = align_up(off, 128);
+    return g;
+}
+
+// Sorted per-instance splat record staged into shared memory by 1-D bulk copies in the blend kernels.
+struct __align__(16) SplatRec {
+    float x, y, conx, cony;      // projected mean, conic xx, xy
+    float conz, opac, r, g;      // conic yy, opacity (AA-compensated), colour
+    float b, depth, t, invkids;  // colour, view depth, LOD weight, 1/kids
+};
+static_assert(sizeof(SplatRec) == 48, "SplatRec must be 48 bytes");
+
+constexpr int SORT_RADIX = 256;
+constexpr int SORT_MAX_PASSES = 8;
+constexpr int SORT_TILE = 4096;  // keys per onesweep tile (256 threads x 16 keys)
+
+struct SortWs {
+    unsigned* hist;                  // [SORT_MAX_PASSES][256] global digit histograms -> exclusive bases
+    int* tickets;                    // [SORT_MAX_PASSES]
+    unsigned* lookback;              // [passes][tiles][256] packed {flag:2, count:30}
+    size_t bytes;
+    size_t zero_bytes;
+};
+static inline size_t sort_tiles(size_t n) { return (n + SORT_TILE - 1) / SORT_TILE; }
+static inline SortWs sort_from_chunk(void* chunk, size_t n) {
+    SortWs w;
+    char* b = (char*)chunk;
+    size_t off = 0;
+    w.hist = carve_arr<unsigned>(b, off, SORT_MAX_PASSES * SORT_RADIX);
+    w.tickets = carve_arr<int>(b, off, SORT_MAX_PASSES);
+    w.lookback = carve_arr<unsigned>(b, off, (size_t)SORT_MAX_PASSES * sort_tiles(n) * SORT_RADIX);
+    w.bytes = align_up(off, 128);
+    w.zero_bytes = w.bytes;
+    return w;
+}
+
+struct BinningState {
+    uint64_t* keys_unsorted;  // [R]
+    uint32_t* vals_unsorted;  // [R]
+    uint64_t* keys;           // [R] sorted
+    uint32_t* point_list;     // [R] sorted
+    SplatRec* recs;           // [R] sorted splat records
+    void* sort_ws;
+    size_t offsets[5];
+    size_t bytes;
+};
+static inline BinningState binning_from_chunk(void* chunk, size_t R) {
+    BinningState s;
+    char* b = (char*)chunk;
+    size_t off = 0;
+    s.keys_unsorted = carve_arr<uint64_t>(b, off, R);  s.offsets[0] = (char*)s.keys_unsorted - b;
+    s.vals_unsorted = carve_arr<uint32_t>(b, off, R);  s.offsets[1] = (char*)s.vals_unsorted - b;
+    s.keys = carve_arr<uint64_t>(b, off, R);           s.offsets[2] = (char*)s.keys - b;
+    s.point_list = carve_arr<uint32_t>(b, off, R + 8); s.offsets[3] = (char*)s.point_list - b;
+    s.recs = carve_arr<SplatRec>(b, off, R);           s.offsets[4] = (char*)s.recs - b;
+    off = align_up(off, 128);
+    s.sort_ws = b + off;
+    off += sort_from_chunk(nullptr, R).bytes;
+    s.bytes = align_up(off, 128);
+    return s;
+}
+
+struct ImageState {
+    float* final_T;       // [W*H]
+    uint32_t* n_contrib;  // [W*H]
+    uint2* ranges;        // [tiles]
+    size_t offsets[3];
+    size_t bytes;
+};
+static inline ImageState image_from_chunk(void* chunk, int W, int H) {
+    ImageState s;
+    char* b = (char*)chunk;
+    size_t off = 0;
+    size_t N = (size_t)W * H;
+    size_t tiles = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+    s.final_T = carve_arr<float>(b, off, N);        s.offsets[0] = (char*)s.final_T - b;
+    s.n_contrib = carve_arr<uint32_t>(b, off, N);   s.offsets[1] = (char*)s.n_contrib - b;
+    s.ranges = carve_arr<uint2>(b, off, tiles);     s.offsets[2] = (char*)s.ranges - b;
+    s.bytes = align_up(off, 128);
+    return s;
+}
+
+}  // namespace lodgs
