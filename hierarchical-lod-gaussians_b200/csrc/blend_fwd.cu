@@ -1,0 +1,179 @@
+// blend_fwd.cu — per-tile front-to-back alpha blending with hierarchical-LOD alpha.
+//
+// Replaces renderCUDA<3> forward (HR/cuda_rasterizer/forward.cu:450-596). One CTA per 16x16 tile; the tile's
+// sorted splat records (48 B each, built after the sort) are streamed into a two-stage shared-memory ring by
+// 1-D bulk async copies (cp.async.bulk -> UBLKCP, completion on an mbarrier) issued by one thread, so the copy
+// of batch b+1 overlaps the blending of batch b and colours/depths never come from global memory inside the
+// pixel loop (the reference fetches them per blended pair). A warp leaves a batch as soon as all of its 32
+// pixels are saturated (ballot), the CTA leaves when all warps have.
+// The arithmetic keeps the reference's expression order (quadratic form, expf, __powf, blend FMAs) so that
+// n_contrib — an integer output decided by the alpha<1/255 and T<1e-4 tests — and the image are bit-identical.
+#include "state.cuh"
+
+namespace lodgs {
+
+constexpr int BLEND_BATCH = 256;
+
+struct BlendSmem {
+    SplatRec recs[2][BLEND_BATCH];
+    uint32_t ids[2][BLEND_BATCH + 8];
+    uint8_t flag[2][BLEND_BATCH];
+    uint64_t bar[2];
+};
+
+template <bool LOD, bool DEPTH, bool SEEN>
+__global__ void __launch_bounds__(TILE_PIX) blend_fwd_kernel(const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
+                                                            const uint32_t* __restrict__ point_list, int W, int H,
+                                                            const float* __restrict__ bg_color, float* __restrict__ final_T,
+                                                            uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
+                                                            float* __restrict__ out_invdepth, int32_t* __restrict__ seen) {
+    __shared__ BlendSmem sm;
+    const unsigned tid = threadIdx.y * TILE_X + threadIdx.x;
+    const unsigned horizontal_blocks = (W + TILE_X - 1) / TILE_X;
+    const uint2 pix = {blockIdx.x * TILE_X + threadIdx.x, blockIdx.y * TILE_Y + threadIdx.y};
+    const uint32_t pix_id = W * pix.y + pix.x;
+    const float2 pixf = {(float)pix.x, (float)pix.y};
+    const bool inside = pix.x < (unsigned)W && pix.y < (unsigned)H;
+    bool done = !inside;
+
+    const uint2 range = ranges[blockIdx.y * horizontal_blocks + blockIdx.x];
+    const int total = (int)(range.y - range.x);
+    const int rounds = (total + BLEND_BATCH - 1) / BLEND_BATCH;
+
+    if (tid == 0) {
+        mbar_init(&sm.bar[0], 1);
+        mbar_init(&sm.bar[1], 1);
+        mbar_fence_init();
+    }
+    if (SEEN) {
+        sm.flag[0][tid] = 0;
+        sm.flag[1][tid] = 0;
+    }
+    __syncthreads();
+
+    auto issue = [&](int b) {
+        const int s = b & 1;
+        const unsigned start = range.x + (unsigned)b * BLEND_BATCH;
+        const unsigned cnt = min((unsigned)BLEND_BATCH, range.y - start);
+        const unsigned rec_bytes = cnt * (unsigned)sizeof(SplatRec);
+        unsigned id_bytes = 0;
+        const unsigned a0 = start & ~3u;
+        if (SEEN) id_bytes = (((start - a0) + cnt) * 4u + 15u) & ~15u;
+        mbar_expect_tx(&sm.bar[s], rec_bytes + id_bytes);
+        bulk_g2s(&sm.recs[s][0], recs + start, rec_bytes, &sm.bar[s]);
+        if (SEEN) bulk_g2s(&sm.ids[s][0], point_list + a0, id_bytes, &sm.bar[s]);
+    };
+    if (tid == 0 && rounds > 0) issue(0);
+
+    float T = 1.0f;
+    uint32_t last_contributor = 0;
+    float C[3] = {0.f, 0.f, 0.f};
+    float expected_invdepth = 0.0f;
+    uint32_t my_id = 0;    // id of the splat this thread flushes `seen` for (previous batch)
+    int pending = -1;      // batch whose seen flags still have to be flushed
+
+    auto flush_seen = [&]() {
+        if (SEEN && pending >= 0) {
+            const int ps = pending & 1;
+            if (sm.flag[ps][tid]) {
+                seen[my_id] = 1;
+                sm.flag[ps][tid] = 0;
+            }
+        }
+    };
+
+    int toDo = total;
+    for (int b = 0; b < rounds; b++, toDo -= BLEND_BATCH) {
+        // barrier: everyone has left batch b-1, so its ring slot may be refilled; also the CTA-wide exit vote
+        const int num_done = __syncthreads_count(done);
+        flush_seen();
+        pending = -1;
+        const int s = b & 1;
+        if (num_done == TILE_PIX) {
+            // batch b's bulk copy is still in flight: it must land before the CTA (and its smem) goes away
+            mbar_wait(&sm.bar[s], (unsigned)(b >> 1) & 1u);
+            break;
+        }
+        if (tid == 0 && b + 1 < rounds) issue(b + 1);
+        mbar_wait(&sm.bar[s], (unsigned)(b >> 1) & 1u);
+        const int cnt = min(BLEND_BATCH, toDo);
+        if (SEEN) {
+            const unsigned mis = (range.x + (unsigned)b * BLEND_BATCH) & 3u;
+            if ((int)tid < cnt) my_id = sm.ids[s][mis + tid];
+            pending = b;
+        }
+        const SplatRec* __restrict__ rb = sm.recs[s];
+        const uint32_t base = (uint32_t)b * BLEND_BATCH;
+        for (int j = 0; j < cnt; j++) {
+            // ballot-based early termination: the warp stops scanning once all 32 pixels are saturated
+            if (__all_sync(0xffffffffu, done)) break;
+            if (done) continue;
+            const float4 q0 = *reinterpret_cast<const float4*>(&rb[j].x);     // x y conx cony
+            const float4 q1 = *reinterpret_cast<const float4*>(&rb[j].conz);  // conz opac r g
+            const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
+            const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
+            if (power > 0.0f) continue;
+            const float my_alpha = min(0.99f, q1.y * expf(power));
+            float alpha;
+            float4 q2;
+            if (LOD || DEPTH) q2 = *reinterpret_cast<const float4*>(&rb[j].b);  // b depth t invkids
+            if (LOD) {
+                const float kidsqrt_alpha = 1.0f - __powf(1.0f - my_alpha, q2.w);
+                alpha = q2.z * my_alpha + (1.0f - q2.z) * kidsqrt_alpha;
+            } else {
+                alpha = my_alpha;
+            }
+            if (alpha < 1.0f / 255.0f) continue;
+            const float test_T = T * (1 - alpha);
+            if (test_T < 0.0001f) {
+                done = true;
+                continue;
+            }
+            if (SEEN) sm.flag[s][j] = 1;
+            const float cb = (LOD || DEPTH) ? q2.x : rb[j].b;
+            C[0] += q1.z * alpha * T;
+            C[1] += q1.w * alpha * T;
+            C[2] += cb * alpha * T;
+            if (DEPTH) expected_invdepth += (1 / q2.y) * alpha * T;
+            T = test_T;
+            last_contributor = base + (uint32_t)j + 1u;
+        }
+    }
+    if (SEEN) {
+        __syncthreads();
+        flush_seen();
+    }
+    if (inside) {
+        final_T[pix_id] = T;
+        n_contrib[pix_id] = last_contributor;
+        const size_t HW = (size_t)H * W;
+        out_color[0 * HW + pix_id] = C[0] + T * bg_color[0];
+        out_color[1 * HW + pix_id] = C[1] + T * bg_color[1];
+        out_color[2 * HW + pix_id] = C[2] + T * bg_color[2];
+        if (DEPTH) out_invdepth[pix_id] = expected_invdepth;
+    }
+}
+
+template <bool LOD, bool DEPTH>
+static int launch_blend_seen(bool has_seen, dim3 grid, dim3 block, cudaStream_t s, const uint2* ranges, const SplatRec* recs,
+                             const uint32_t* point_list, int W, int H, const float* bg, float* final_T, uint32_t* n_contrib,
+                             float* out_color, float* out_invdepth, int32_t* seen) {
+    if (has_seen)
+        blend_fwd_kernel<LOD, DEPTH, true><<<grid, block, 0, s>>>(ranges, recs, point_list, W, H, bg, final_T, n_contrib, out_color, out_invdepth, seen);
+    else
+        blend_fwd_kernel<LOD, DEPTH, false><<<grid, block, 0, s>>>(ranges, recs, point_list, W, H, bg, final_T, n_contrib, out_color, out_invdepth, seen);
+    LODGS_LAUNCHED("blend_fwd_kernel");
+    return LODGS_OK;
+}
+
+int launch_blend_fwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, int W, int H, const float* bg,
+                     float* out_color, float* out_invdepth, int32_t* seen, cudaStream_t s) {
+    dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1), block(TILE_X, TILE_Y, 1);
+    const bool hs = seen != nullptr;
+    if (lod && depth) return launch_blend_seen<true, true>(hs, grid, block, s, img.ranges, bin.recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
+    if (lod && !depth) return launch_blend_seen<true, false>(hs, grid, block, s, img.ranges, bin.recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
+    if (!lod && depth) return launch_blend_seen<false, true>(hs, grid, block, s, img.ranges, bin.recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
+    return launch_blend_seen<false, false>(hs, grid, block, s, img.ranges, bin.recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
+}
+
+}  // namespace lodgs

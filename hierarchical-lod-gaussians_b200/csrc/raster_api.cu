@@ -1,0 +1,102 @@
+// raster_api.cu — C ABI orchestration of the forward render stage and the layout accessors.
+// Mirrors the tail of CudaRasterizer::Rasterizer::forward (HR/cuda_rasterizer/rasterizer_impl.cu:334-400).
+#include "state.cuh"
+
+namespace lodgs {
+int launch_emit_keys(int P, const GeomState& g, const int32_t* radii, unsigned gx, unsigned gy, uint64_t* keys, uint32_t* vals,
+                     cudaStream_t s);
+int launch_tile_ranges(int R, const uint64_t* keys, uint2* ranges, size_t ntiles, cudaStream_t s);
+int launch_build_records(int R, int P, const BinningState& b, const GeomState& g, const float* colors, const float* ts,
+                         const int32_t* kids, cudaStream_t s);
+int sort_pairs_device(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, uint64_t* keys_tmp,
+                      uint32_t* vals_tmp, int n, int end_bit, void* ws, cudaStream_t s);
+int launch_blend_fwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, int W, int H, const float* bg,
+                     float* out_color, float* out_invdepth, int32_t* seen, cudaStream_t s);
+
+// Same as getHigherMsb (rasterizer_impl.cu:35-50): number of bits needed for the tile id.
+static uint32_t higher_msb(uint32_t n) {
+    uint32_t msb = sizeof(n) * 4;
+    uint32_t step = msb;
+    while (step > 1) {
+        step /= 2;
+        if (n >> msb) msb += step;
+        else msb -= step;
+    }
+    if (n >> msb) msb++;
+    return msb;
+}
+}  // namespace lodgs
+
+using namespace lodgs;
+
+// The binning buffer additionally holds the sort's ping-pong pair; it is carved after the public arrays.
+struct BinningFull {
+    BinningState b;
+    uint64_t* keys_tmp;
+    uint32_t* vals_tmp;
+    size_t bytes;
+};
+static BinningFull binning_full(void* chunk, size_t R) {
+    BinningFull f;
+    f.b = binning_from_chunk(chunk, R);
+    char* base = (char*)chunk;
+    size_t off = f.b.bytes;
+    f.keys_tmp = carve_arr<uint64_t>(base, off, R);
+    f.vals_tmp = carve_arr<uint32_t>(base, off, R);
+    f.bytes = align_up(off, 128);
+    return f;
+}
+
+extern "C" size_t lodgs_image_bytes(int W, int H) { return image_from_chunk(nullptr, W, H).bytes + 128; }
+extern "C" size_t lodgs_binning_bytes(int R) { return binning_full(nullptr, R < 0 ? 0 : R).bytes + 128; }
+
+extern "C" int lodgs_binning_layout(int R, size_t* offsets5) {
+    BinningState b = binning_from_chunk(nullptr, R);
+    for (int i = 0; i < 5; i++) offsets5[i] = b.offsets[i];
+    return LODGS_OK;
+}
+extern "C" int lodgs_image_layout(int W, int H, size_t* offsets3) {
+    ImageState s = image_from_chunk(nullptr, W, H);
+    for (int i = 0; i < 3; i++) offsets3[i] = s.offsets[i];
+    return LODGS_OK;
+}
+
+extern "C" int lodgs_forward_render(int P, int W, int H, int R, const float* background, const float* ts, const int32_t* kids,
+                                    const float* colors_precomp, const int32_t* radii, void* geom_buffer, void* binning_buffer,
+                                    size_t binning_bytes, void* image_buffer, size_t image_bytes, float* out_color,
+                                    float* out_invdepth, int32_t* seen, void* stream) {
+    if (P < 0 || W <= 0 || H <= 0 || R < 0) { set_error("lodgs_forward_render: bad size argument"); return LODGS_E_ARG; }
+    if (!background || !out_color || !image_buffer) { set_error("lodgs_forward_render: null pointer argument"); return LODGS_E_ARG; }
+    if (image_bytes < lodgs_image_bytes(W, H) - 128) { set_error("lodgs_forward_render: image buffer too small"); return LODGS_E_WORKSPACE; }
+    if (((uintptr_t)image_buffer & 127) != 0) { set_error("lodgs_forward_render: image buffer must be 128-byte aligned"); return LODGS_E_ARG; }
+    cudaStream_t s = (cudaStream_t)stream;
+    ImageState img = image_from_chunk(image_buffer, W, H);
+    const unsigned gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+    BinningFull bf;
+    bf.b = binning_from_chunk(nullptr, 0);
+    if (R > 0) {
+        if (!geom_buffer || !binning_buffer || !radii || P == 0) { set_error("lodgs_forward_render: null pointer argument"); return LODGS_E_ARG; }
+        if (binning_bytes < lodgs_binning_bytes(R) - 128) { set_error("lodgs_forward_render: binning buffer too small"); return LODGS_E_WORKSPACE; }
+        if (((uintptr_t)binning_buffer & 127) != 0) { set_error("lodgs_forward_render: binning buffer must be 128-byte aligned"); return LODGS_E_ARG; }
+        GeomState g = geom_from_chunk(geom_buffer, P);
+        bf = binning_full(binning_buffer, R);
+        int rc = launch_emit_keys(P, g, radii, gx, gy, bf.b.keys_unsorted, bf.b.vals_unsorted, s);
+        if (rc) return rc;
+        const int bit = (int)higher_msb(gx * gy);
+        rc = sort_pairs_device(bf.b.keys_unsorted, bf.b.vals_unsorted, bf.b.keys, bf.b.point_list, bf.keys_tmp, bf.vals_tmp, R, 32 + bit,
+                               bf.b.sort_ws, s);
+        if (rc) return rc;
+        rc = launch_tile_ranges(R, bf.b.keys, img.ranges, (size_t)gx * gy, s);
+        if (rc) return rc;
+        const float* colors = colors_precomp ? colors_precomp : g.rgb;
+        rc = launch_build_records(R, P, bf.b, g, colors, ts, kids, s);
+        if (rc) return rc;
+    } else {
+        // The reference returns before rendering when nothing is visible (rasterizer_impl.cu:332-333), leaving the
+        // zero-filled image; the blend below runs with empty ranges and writes the background instead. Keep the
+        // reference behaviour: leave out_color untouched.
+        return LODGS_OK;
+    }
+    const bool lod = ts != nullptr && kids != nullptr;
+    return launch_blend_fwd(lod, out_invdepth != nullptr, img, bf.b, W, H, background, out_color, out_invdepth, seen, s);
+}

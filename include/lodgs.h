@@ -18,6 +18,9 @@
 #ifdef __cplusplus
 extern "C" {
 #endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
 
 #define LODGS_OK 0
 #define LODGS_E_ARG (-1)       /* bad argument (null pointer, negative size, ...) */
@@ -179,6 +182,9 @@ int lodgs_adam_step(float* param, const float* grad, float* exp_avg, float* exp_
                     int width, float lr, float beta1, float beta2, float eps, int64_t step,
                     int bias_correction, void* stream);
 
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
 #ifdef __cplusplus
 }
 #endif
