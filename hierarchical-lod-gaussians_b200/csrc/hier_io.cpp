@@ -1,0 +1,171 @@
+// hier_io.cpp — .hier reader/writer (host only).
+// File format of HierarchyLoader::load (GH/hierarchy_loader.cpp:26-128) / HierarchyWriter::write
+// (GH/hierarchy_writer.cpp:27-119): int P (negative => half-compressed), pos[P,3] f32, rot[P,4], log-scales[P,3],
+// opacities[P], SH[P,48] (f32 or IEEE half, round-to-nearest), int N, nodes (7 x i32, or HalfNode = 3 x i32 +
+// 4 x i16 {depth,count_children,count_leafs,count_merged}), boxes (8 x f32 or 8 x half).
+#include "common.cuh"
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+namespace {
+
+float half_to_float(uint16_t h) {
+    uint32_t sign = (uint32_t)(h & 0x8000u) << 16;
+    uint32_t exp = (h >> 10) & 0x1f;
+    uint32_t man = h & 0x3ffu;
+    uint32_t bits;
+    if (exp == 0) {
+        if (man == 0) {
+            bits = sign;
+        } else {  // subnormal half -> normal float
+            int e = -1;
+            do { e++; man <<= 1; } while ((man & 0x400u) == 0);
+            bits = sign | ((uint32_t)(127 - 15 - e) << 23) | ((man & 0x3ffu) << 13);
+        }
+    } else if (exp == 31) {
+        bits = sign | 0x7f800000u | (man << 13);
+    } else {
+        bits = sign | ((exp + 112) << 23) | (man << 13);
+    }
+    float f;
+    memcpy(&f, &bits, 4);
+    return f;
+}
+
+uint16_t float_to_half(float f) {  // round to nearest even
+    uint32_t x;
+    memcpy(&x, &f, 4);
+    uint16_t sign = (uint16_t)((x >> 16) & 0x8000u);
+    uint32_t abs = x & 0x7fffffffu;
+    if (abs >= 0x7f800000u) return sign | 0x7c00u | (abs > 0x7f800000u ? 0x200u | ((abs >> 13) & 0x3ffu) : 0);
+    if (abs >= 0x477ff000u) return sign | 0x7c00u;  // rounds to >= 65520 -> inf
+    if (abs < 0x33000001u) return sign;             // < 2^-25 (or exactly 2^-25, ties to even 0)
+    int e = (int)(abs >> 23) - 127;
+    uint32_t m = (abs & 0x7fffffu) | 0x800000u;
+    int shift = (e < -14) ? (13 + (-14 - e)) : 13;
+    uint32_t hm = m >> shift;
+    uint32_t rem = m & ((1u << shift) - 1u);
+    uint32_t half_ulp = 1u << (shift - 1);
+    uint32_t base = (e < -14) ? hm : (((uint32_t)(e + 15) << 10) + (hm & 0x3ffu));
+    if (rem > half_ulp || (rem == half_ulp && (base & 1u))) base++;
+    return sign | (uint16_t)base;
+}
+
+struct File {
+    FILE* f;
+    explicit File(const char* name, const char* mode) : f(fopen(name, mode)) {}
+    ~File() { if (f) fclose(f); }
+    bool rd(void* p, size_t n) { return n == 0 || fread(p, 1, n, f) == n; }
+    bool wr(const void* p, size_t n) { return n == 0 || fwrite(p, 1, n, f) == n; }
+};
+
+struct HalfNodeRec {
+    int32_t parent, start, start_children;
+    int16_t dccc[4];
+};
+static_assert(sizeof(HalfNodeRec) == 20, "HalfNode layout");
+
+}  // namespace
+
+extern "C" int lodgs_hier_probe(const char* filename, int32_t* P, int32_t* N) {
+    if (!filename || !P || !N) { lodgs::set_error("lodgs_hier_probe: null argument"); return LODGS_E_ARG; }
+    File in(filename, "rb");
+    if (!in.f) { lodgs::set_error("File not found!"); return LODGS_E_IO; }
+    int32_t p;
+    if (!in.rd(&p, 4)) { lodgs::set_error("lodgs_hier_probe: short read"); return LODGS_E_IO; }
+    const bool half = p < 0;
+    const long long ap = half ? -(long long)p : p;
+    const long long per = half ? (12 + 8 + 6 + 2 + 96) : (12 + 16 + 12 + 4 + 192);
+    if (fseek(in.f, (long)(4 + ap * per), SEEK_SET) != 0) { lodgs::set_error("lodgs_hier_probe: seek failed"); return LODGS_E_IO; }
+    int32_t n;
+    if (!in.rd(&n, 4)) { lodgs::set_error("lodgs_hier_probe: short read"); return LODGS_E_IO; }
+    *P = (int32_t)ap;
+    *N = n;
+    return LODGS_OK;
+}
+
+extern "C" int lodgs_hier_load(const char* filename, float* pos, float* shs, float* alpha, float* scales, float* rot, int32_t* nodes,
+                               float* boxes) {
+    if (!filename) { lodgs::set_error("lodgs_hier_load: null filename"); return LODGS_E_ARG; }
+    File in(filename, "rb");
+    if (!in.f) { lodgs::set_error("File not found!"); return LODGS_E_IO; }
+    int32_t p;
+    bool ok = in.rd(&p, 4);
+    if (!ok) { lodgs::set_error("lodgs_hier_load: short read"); return LODGS_E_IO; }
+    if (p >= 0) {
+        size_t P = (size_t)p;
+        ok = in.rd(pos, P * 12) && in.rd(rot, P * 16) && in.rd(scales, P * 12) && in.rd(alpha, P * 4) && in.rd(shs, P * 192);
+        int32_t n = 0;
+        ok = ok && in.rd(&n, 4);
+        ok = ok && in.rd(nodes, (size_t)n * 28) && in.rd(boxes, (size_t)n * 32);
+    } else {
+        size_t P = (size_t)(-(long long)p);
+        std::vector<uint16_t> h(P * 48);
+        ok = in.rd(pos, P * 12);
+        ok = ok && in.rd(h.data(), P * 8);
+        if (ok) for (size_t i = 0; i < P * 4; i++) rot[i] = half_to_float(h[i]);
+        ok = ok && in.rd(h.data(), P * 6);
+        if (ok) for (size_t i = 0; i < P * 3; i++) scales[i] = half_to_float(h[i]);
+        ok = ok && in.rd(h.data(), P * 2);
+        if (ok) for (size_t i = 0; i < P; i++) alpha[i] = half_to_float(h[i]);
+        ok = ok && in.rd(h.data(), P * 96);
+        if (ok) for (size_t i = 0; i < P * 48; i++) shs[i] = half_to_float(h[i]);
+        int32_t n = 0;
+        ok = ok && in.rd(&n, 4);
+        if (ok) {
+            size_t N = (size_t)n;
+            std::vector<HalfNodeRec> hn(N);
+            std::vector<uint16_t> hb(N * 8);
+            ok = in.rd(hn.data(), N * sizeof(HalfNodeRec)) && in.rd(hb.data(), N * 16);
+            if (ok) {
+                for (size_t i = 0; i < N; i++) {
+                    int32_t* o = nodes + i * 7;
+                    o[0] = hn[i].dccc[0]; o[1] = hn[i].parent; o[2] = hn[i].start; o[3] = hn[i].dccc[2];
+                    o[4] = hn[i].dccc[3]; o[5] = hn[i].start_children; o[6] = hn[i].dccc[1];
+                    for (int j = 0; j < 8; j++) boxes[i * 8 + j] = half_to_float(hb[i * 8 + j]);
+                }
+            }
+        }
+    }
+    if (!ok) { lodgs::set_error("lodgs_hier_load: short read"); return LODGS_E_IO; }
+    return LODGS_OK;
+}
+
+extern "C" int lodgs_hier_write(const char* filename, int P, int N, const float* pos, const float* shs, const float* alpha,
+                                const float* scales, const float* rot, const int32_t* nodes, const float* boxes, int compressed) {
+    if (!filename || P < 0 || N < 0) { lodgs::set_error("lodgs_hier_write: bad argument"); return LODGS_E_ARG; }
+    File out(filename, "wb");
+    if (!out.f) { lodgs::set_error("File not created!"); return LODGS_E_IO; }
+    bool ok;
+    const size_t sp = (size_t)P, sn = (size_t)N;
+    if (!compressed) {
+        int32_t p = P, n = N;
+        ok = out.wr(&p, 4) && out.wr(pos, sp * 12) && out.wr(rot, sp * 16) && out.wr(scales, sp * 12) && out.wr(alpha, sp * 4) &&
+             out.wr(shs, sp * 192) && out.wr(&n, 4) && out.wr(nodes, sn * 28) && out.wr(boxes, sn * 32);
+    } else {
+        int32_t p = -P, n = N;
+        std::vector<uint16_t> h(sp * 48);
+        ok = out.wr(&p, 4) && out.wr(pos, sp * 12);
+        for (size_t i = 0; i < sp * 4; i++) h[i] = float_to_half(rot[i]);
+        ok = ok && out.wr(h.data(), sp * 8);
+        for (size_t i = 0; i < sp * 3; i++) h[i] = float_to_half(scales[i]);
+        ok = ok && out.wr(h.data(), sp * 6);
+        for (size_t i = 0; i < sp; i++) h[i] = float_to_half(alpha[i]);
+        ok = ok && out.wr(h.data(), sp * 2);
+        for (size_t i = 0; i < sp * 48; i++) h[i] = float_to_half(shs[i]);
+        ok = ok && out.wr(h.data(), sp * 96);
+        std::vector<HalfNodeRec> hn(sn);
+        std::vector<uint16_t> hb(sn * 8);
+        for (size_t i = 0; i < sn; i++) {
+            const int32_t* o = nodes + i * 7;
+            if (o[0] > 32000 || o[6] > 32000 || o[3] > 32000 || o[4] > 32000) { lodgs::set_error("Would lose information!"); return LODGS_E_ARG; }
+            hn[i].parent = o[1]; hn[i].start = o[2]; hn[i].start_children = o[5];
+            hn[i].dccc[0] = (int16_t)o[0]; hn[i].dccc[1] = (int16_t)o[6]; hn[i].dccc[2] = (int16_t)o[3]; hn[i].dccc[3] = (int16_t)o[4];
+            for (int j = 0; j < 8; j++) hb[i * 8 + j] = float_to_half(boxes[i * 8 + j]);
+        }
+        ok = ok && out.wr(&n, 4) && out.wr(hn.data(), sn * sizeof(HalfNodeRec)) && out.wr(hb.data(), sn * 16);
+    }
+    if (!ok) { lodgs::set_error("lodgs_hier_write: short write"); return LODGS_E_IO; }
+    return LODGS_OK;
+}

@@ -100,3 +100,58 @@ extern "C" int lodgs_forward_render(int P, int W, int H, int R, const float* bac
     const bool lod = ts != nullptr && kids != nullptr;
     return launch_blend_fwd(lod, out_invdepth != nullptr, img, bf.b, W, H, background, out_color, out_invdepth, seen, s);
 }
+
+// ------------------------------------------------------------------------------------------------ backward
+namespace lodgs {
+struct PreBwdParams;
+int launch_blend_bwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, int W, int H, const float* bg,
+                     const int32_t* indices, const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic,
+                     float* dL_dopacity, float* dL_dcolor, float* dL_dinvdepth, cudaStream_t s);
+int run_preprocess_bwd(int P, int D, int M, const int32_t* indices, const int32_t* parent_indices, const float* ts, const float* means3D,
+                       const int32_t* radii, const float* shs, const uint8_t* clamped, const float* opacities, const float* scales,
+                       const float* rotations, float scale_modifier, const float* cov3Ds, int cov3D_by_global, const float* viewmatrix,
+                       const float* projmatrix, const float* campos, float focal_x, float focal_y, float tan_fovx, float tan_fovy,
+                       const float* dL_dmean2D, const float* dL_dconic, const float* dL_dinvdepth, const float* dL_dcolor,
+                       float* dL_dopacity, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                       cudaStream_t s);
+}  // namespace lodgs
+
+extern "C" int lodgs_backward(int P, int fullP, int D, int M, int R, int W, int H, const float* background, const int32_t* indices,
+                              const int32_t* parent_indices, const float* ts, const int32_t* kids, const float* means3D,
+                              const float* shs, const float* colors_precomp, const float* opacities, const float* scales,
+                              float scale_modifier, const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                              const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy, const int32_t* radii,
+                              void* geom_buffer, void* binning_buffer, void* image_buffer, const float* dL_dpix,
+                              const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                              float* dL_dinvdepth, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                              void* stream) {
+    (void)colors_precomp;
+    if (P < 0 || fullP < 0 || W <= 0 || H <= 0 || R < 0 || D < 0 || D > 3) { set_error("lodgs_backward: bad size argument"); return LODGS_E_ARG; }
+    if (P == 0) return LODGS_OK;
+    if (!background || !means3D || !opacities || !viewmatrix || !projmatrix || !campos || !radii || !geom_buffer || !image_buffer || !dL_dpix ||
+        !dL_dmean2D || !dL_dconic || !dL_dopacity || !dL_dcolor || !dL_dmean3D || !dL_dcov3D) {
+        set_error("lodgs_backward: null pointer argument");
+        return LODGS_E_ARG;
+    }
+    if ((dL_dinvdepth_pix == nullptr) != (dL_dinvdepth == nullptr)) { set_error("lodgs_backward: dL_dinvdepth_pix and dL_dinvdepth go together"); return LODGS_E_ARG; }
+    if (shs && !dL_dsh) { set_error("lodgs_backward: dL_dsh missing"); return LODGS_E_ARG; }
+    if (scales && (!rotations || !dL_dscale || !dL_drot)) { set_error("lodgs_backward: scale/rotation gradient buffers missing"); return LODGS_E_ARG; }
+    cudaStream_t s = (cudaStream_t)stream;
+    GeomState g = geom_from_chunk(geom_buffer, P);
+    ImageState img = image_from_chunk(image_buffer, W, H);
+    if (R > 0) {
+        if (!binning_buffer) { set_error("lodgs_backward: null binning buffer"); return LODGS_E_ARG; }
+        BinningState bin = binning_from_chunk(binning_buffer, R);
+        const bool lod = ts != nullptr && kids != nullptr;
+        int rc = launch_blend_bwd(lod, dL_dinvdepth_pix != nullptr, img, bin, W, H, background, indices, dL_dpix, dL_dinvdepth_pix,
+                                  dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dinvdepth, s);
+        if (rc) return rc;
+    }
+    const float focal_y = H / (2.0f * tan_fovy);
+    const float focal_x = W / (2.0f * tan_fovx);
+    const float* cov3Ds = cov3D_precomp ? cov3D_precomp : g.cov3D;
+    return run_preprocess_bwd(P, D, M, indices, parent_indices, ts, means3D, radii, shs, g.clamped, opacities, scales, rotations,
+                              scale_modifier, cov3Ds, cov3D_precomp ? 1 : 0, viewmatrix, projmatrix, campos, focal_x, focal_y, tan_fovx,
+                              tan_fovy, dL_dmean2D, dL_dconic, dL_dinvdepth, dL_dcolor, dL_dopacity, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale,
+                              dL_drot, s);
+}

@@ -1,0 +1,121 @@
+"""ctypes binding of liblodgs.so (include/lodgs.h). PyTorch is used only for device memory and streams.
+
+The library is mandatory: importing this module fails loudly when liblodgs.so is missing or does not export
+every symbol of the header; there is no CPU or PyTorch fallback anywhere in the product path.
+"""
+import ctypes as C
+import os
+import re
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_PKG = os.path.dirname(_HERE)
+LIB_PATH = os.path.join(_PKG, "lib", "liblodgs.so")
+HEADER_PATH = os.path.join(os.path.dirname(_PKG), "include", "lodgs.h")
+
+OK, E_ARG, E_WORKSPACE, E_CUDA, E_IO = 0, -1, -2, -3, -4
+
+
+class LodgsError(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__("lodgs error %d: %s" % (code, text))
+        self.code = code
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        try:
+            import importlib.util
+            spec = importlib.util.spec_from_file_location("_lodgs_build", os.path.join(_PKG, "build.py"))
+            mod = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(mod)
+            mod.build(verbose=False)
+        except Exception as e:  # noqa: BLE001
+            raise ImportError("liblodgs.so is missing at %s and could not be built: %s" % (LIB_PATH, e))
+    return C.CDLL(LIB_PATH)
+
+
+lib = _load()
+
+_p, _i, _f, _sz, _i64, _d = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_int64, C.c_double
+
+_SIGS = {
+    "lodgs_last_error": (C.c_char_p, []),
+    "lodgs_version": (_i, []),
+    "lodgs_compiled_sm": (_i, []),
+    "lodgs_launch_count": (C.c_uint64, []),
+    "lodgs_cut_workspace_bytes": (_sz, [_i]),
+    "lodgs_expand_to_size": (_i, [_p, _p, _i, _f, _p, _p, _p, _p, _i, _p, _sz, _i, _p, _p]),
+    "lodgs_cut_prepare": (_i, [_p, _p, _i, _p, _sz, _p, _p]),
+    "lodgs_get_interpolation_weights": (_i, [_p, _i, _f, _p, _p, _f, _f, _f, _p, _p, _p]),
+    "lodgs_hier_probe": (_i, [C.c_char_p, _p, _p]),
+    "lodgs_hier_load": (_i, [C.c_char_p, _p, _p, _p, _p, _p, _p, _p]),
+    "lodgs_hier_write": (_i, [C.c_char_p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _i]),
+    "lodgs_geom_bytes": (_sz, [_i]),
+    "lodgs_image_bytes": (_sz, [_i, _i]),
+    "lodgs_binning_bytes": (_sz, [_i]),
+    "lodgs_forward_preprocess": (_i, [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _f, _f, _p,
+                                      _p, _sz, _p, _p]),
+    "lodgs_forward_render": (_i, [_i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _sz, _p, _sz, _p, _p, _p, _p]),
+    "lodgs_backward": (_i, [_i, _i, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _f, _f, _p,
+                            _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "lodgs_mark_visible": (_i, [_i, _p, _p, _p, _p, _p]),
+    "lodgs_geom_layout": (_i, [_i, _p]),
+    "lodgs_binning_layout": (_i, [_i, _p]),
+    "lodgs_image_layout": (_i, [_i, _i, _p]),
+    "lodgs_sort_workspace_bytes": (_sz, [_i]),
+    "lodgs_sort_pairs": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _p, _sz, _p]),
+    "lodgs_adam_step": (_i, [_p, _p, _p, _p, _p, _i64, _p, _i64, _i, _d, _d, _d, _d, _i64, _i, _p]),
+}
+
+
+def header_symbols():
+    """Names of all functions declared in include/lodgs.h."""
+    with open(HEADER_PATH) as fh:
+        text = fh.read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(lodgs_[a-z0-9_]+)\s*\(", text)))
+
+
+def _bind():
+    missing = []
+    for name, (res, args) in _SIGS.items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError:
+            missing.append(name)
+            continue
+        fn.restype = res
+        fn.argtypes = args
+    if missing:
+        raise ImportError("liblodgs.so does not export: %s" % ", ".join(missing))
+
+
+_bind()
+
+
+def last_error():
+    return lib.lodgs_last_error().decode()
+
+
+def check(code):
+    if code != 0:
+        raise LodgsError(code, last_error())
+    return code
+
+
+def ptr(t):
+    """Device/host pointer of a torch tensor; None or an empty tensor -> NULL (the reference's empty-tensor convention)."""
+    if t is None:
+        return None
+    if t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def current_stream():
+    import torch
+    return torch.cuda.current_stream().cuda_stream
+
+
+def launch_count():
+    return int(lib.lodgs_launch_count())

@@ -173,13 +173,13 @@ int lodgs_sort_pairs(const uint64_t* keys_in, const uint32_t* values_in, uint64_
  * Adam with bias correction restricted to the rows listed in `relevant` (i64 row indices, or NULL = all
  * rows, which is _single_tensor_adam2 :357-452). One launch per parameter tensor of `width` floats per row.
  * step_size = lr / (1 - beta1^step); denom = sqrt(v)/sqrt(1 - beta2^step) + eps (bias terms evaluated
- * on the host in double as Python does).
+ * on the host in double as Python does; lr/betas/eps are doubles because Python floats are).
  * bias_correction = 0 gives AR's adamUpdateCUDA (AR/cuda_rasterizer/adam.cu:9-38: no bias correction,
  * rows masked by `visible` u8[rows] instead of an index list).
  */
 int lodgs_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq,
                     const int64_t* relevant, int64_t n_relevant, const uint8_t* visible, int64_t rows,
-                    int width, float lr, float beta1, float beta2, float eps, int64_t step,
+                    int width, double lr, double beta1, double beta2, double eps, int64_t step,
                     int bias_correction, void* stream);
 
 #if defined(__GNUC__)
