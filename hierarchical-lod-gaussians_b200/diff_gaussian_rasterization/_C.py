@@ -1,0 +1,115 @@
+"""diff_gaussian_rasterization._C — same functions, argument order and return tuples as the reference's pybind
+module (HR/ext.cpp:15-19, HR/rasterize_points.cu:36-245), implemented as a thin ctypes shim over liblodgs.so.
+`mark_visible`, which the reference's Python calls but never binds, is provided too."""
+import ctypes as C
+
+import torch
+
+import lodgs
+from lodgs import check, current_stream, lib, ptr
+
+NUM_CHANNELS = 3
+
+# Persistent high-water scratch arena per device for the binning buffer would save an allocation per call; the
+# reference hands fresh torch byte tensors back to Python (rasterize_points.cu:85-92) and so do we: they are what
+# autograd saves for backward.
+
+
+def _byte_buffer(nbytes, device):
+    # torch allocations are 512-byte aligned, which satisfies the library's 128-byte requirement
+    return torch.empty(int(nbytes), dtype=torch.uint8, device=device)
+
+
+def _f(t):
+    return t.contiguous() if t is not None else t
+
+
+def rasterize_gaussians(background, indices, parent_indices, ts, kids, means3D, colors, opacity, scales, rotations,
+                        scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height,
+                        image_width, sh, degree, campos, prefiltered, debug, do_depth):
+    if means3D.dim() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    dev = means3D.device
+    if dev.type != "cuda":
+        raise RuntimeError("lodgs rasterizer needs CUDA tensors (there is no CPU path)")
+    P = means3D.size(0) if indices.numel() == 0 else indices.size(0)
+    H, W = int(image_height), int(image_width)
+    out_color = torch.zeros((NUM_CHANNELS, H, W), dtype=torch.float32, device=dev)
+    out_invdepth = torch.zeros((1 if do_depth else 0, H, W), dtype=torch.float32, device=dev)
+    radii = torch.zeros((P,), dtype=torch.int32, device=dev)
+    seen = torch.zeros((P,), dtype=torch.int32, device=dev)
+    geom = torch.empty(0, dtype=torch.uint8, device=dev)
+    binning = torch.empty(0, dtype=torch.uint8, device=dev)
+    img = torch.empty(0, dtype=torch.uint8, device=dev)
+    rendered = 0
+    if P != 0:
+        M = sh.size(1) if sh.numel() != 0 else 0
+        t = [_f(x.to(dev)) if x.numel() and x.device != dev else _f(x) for x in
+             (background, indices, parent_indices, ts, kids, means3D, colors, opacity, scales, rotations, cov3D_precomp,
+              viewmatrix, projmatrix, sh, campos)]
+        (background, indices, parent_indices, ts, kids, means3D, colors, opacity, scales, rotations, cov3D_precomp,
+         viewmatrix, projmatrix, sh, campos) = t
+        stream = current_stream()
+        geom = _byte_buffer(lib.lodgs_geom_bytes(P), dev)
+        img = _byte_buffer(lib.lodgs_image_bytes(W, H), dev)
+        n = C.c_int32(0)
+        check(lib.lodgs_forward_preprocess(P, int(degree), M, W, H, ptr(indices), ptr(parent_indices), ptr(ts), ptr(means3D),
+                                           ptr(sh), ptr(colors), ptr(opacity), ptr(scales), float(scale_modifier),
+                                           ptr(rotations), ptr(cov3D_precomp), ptr(viewmatrix), ptr(projmatrix), ptr(campos),
+                                           float(tan_fovx), float(tan_fovy), ptr(radii), geom.data_ptr(), geom.numel(),
+                                           C.addressof(n), stream))
+        rendered = int(n.value)
+        if rendered > 0:
+            binning = _byte_buffer(lib.lodgs_binning_bytes(rendered), dev)
+            check(lib.lodgs_forward_render(P, W, H, rendered, ptr(background), ptr(ts), ptr(kids), ptr(colors), ptr(radii),
+                                           geom.data_ptr(), binning.data_ptr(), binning.numel(), img.data_ptr(), img.numel(),
+                                           ptr(out_color), ptr(out_invdepth) if do_depth else None, ptr(seen), stream))
+        if debug:
+            torch.cuda.synchronize()
+    return rendered, out_color, radii, geom, binning, img, out_invdepth, seen
+
+
+def rasterize_gaussians_backward(background, indices, parent_indices, ts, kids, means3D, radii, colors, opacities, scales,
+                                 rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
+                                 dL_dout_color, dL_dout_invdepth, sh, degree, campos, geomBuffer, R, binningBuffer,
+                                 imageBuffer, debug):
+    dev = means3D.device
+    fullP = means3D.size(0)
+    P = fullP if indices.numel() == 0 else indices.size(0)
+    H, W = dL_dout_color.size(1), dL_dout_color.size(2)
+    M = sh.size(1) if sh.numel() != 0 else 0
+    z = lambda *shape: torch.zeros(shape, dtype=torch.float32, device=dev)  # noqa: E731
+    dL_dmeans3D, dL_dmeans2D, dL_dcolors = z(fullP, 3), z(fullP, 3), z(fullP, NUM_CHANNELS)
+    dL_dconic, dL_dopacity, dL_dcov3D = z(fullP, 2, 2), z(fullP, 1), z(fullP, 6)
+    dL_dsh, dL_dscales, dL_drotations = z(fullP, M, 3), z(fullP, 3), z(fullP, 4)
+    has_depth = dL_dout_invdepth is not None and dL_dout_invdepth.numel() != 0
+    dL_dinvdepths = z(fullP, 1) if has_depth else z(0, 1)
+    if P != 0:
+        t = [_f(x.to(dev)) if x.numel() and x.device != dev else _f(x) for x in
+             (background, indices, parent_indices, ts, kids, means3D, colors, opacities, scales, rotations, cov3D_precomp,
+              viewmatrix, projmatrix, sh, campos)]
+        (background, indices, parent_indices, ts, kids, means3D, colors, opacities, scales, rotations, cov3D_precomp,
+         viewmatrix, projmatrix, sh, campos) = t
+        dL_dout_color = dL_dout_color.contiguous()
+        if has_depth:
+            dL_dout_invdepth = dL_dout_invdepth.contiguous()
+        check(lib.lodgs_backward(P, fullP, int(degree), M, int(R), W, H, ptr(background), ptr(indices), ptr(parent_indices),
+                                 ptr(ts), ptr(kids), ptr(means3D), ptr(sh), ptr(colors), ptr(opacities), ptr(scales),
+                                 float(scale_modifier), ptr(rotations), ptr(cov3D_precomp), ptr(viewmatrix), ptr(projmatrix),
+                                 ptr(campos), float(tan_fovx), float(tan_fovy), ptr(radii), ptr(geomBuffer), ptr(binningBuffer),
+                                 ptr(imageBuffer), ptr(dL_dout_color), ptr(dL_dout_invdepth) if has_depth else None,
+                                 ptr(dL_dmeans2D), ptr(dL_dconic), ptr(dL_dopacity), ptr(dL_dcolors),
+                                 ptr(dL_dinvdepths) if has_depth else None, ptr(dL_dmeans3D), ptr(dL_dcov3D), ptr(dL_dsh),
+                                 ptr(dL_dscales), ptr(dL_drotations), current_stream()))
+        if debug:
+            torch.cuda.synchronize()
+    return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    P = means3D.size(0)
+    present = torch.zeros((P,), dtype=torch.bool, device=means3D.device)
+    if P != 0:
+        check(lib.lodgs_mark_visible(P, ptr(means3D.contiguous()), ptr(viewmatrix.contiguous()), ptr(projmatrix.contiguous()),
+                                     present.data_ptr(), current_stream()))
+    return present

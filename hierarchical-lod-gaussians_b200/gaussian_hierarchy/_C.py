@@ -1,0 +1,93 @@
+"""gaussian_hierarchy._C — expand_to_size / get_interpolation_weights / load_hierarchy / write_hierarchy with the
+reference's signatures and tensor layouts (GH/ext.cpp:15-27, GH/torch/torch_interface.cpp), bound to liblodgs.so.
+
+Device conventions of the reference are kept: expand_to_size takes `viewpoint` as a CUDA tensor (read
+inside the kernel) and `viewdir` as a CPU tensor; get_interpolation_weights reads `viewpoint` on the host. Either
+device is accepted and copied as needed."""
+import ctypes as C
+
+import torch
+
+from lodgs import LodgsError, check, current_stream, lib, ptr
+
+_ws_cache = {}          # (device index) -> workspace tensor (grown on demand; the reference mallocs per call)
+_traversable = {}       # (nodes ptr, N) -> bool, from lodgs_cut_prepare
+TRAVERSAL_MIN_NODES = 16_000_000   # below this the single-pass flat kernel is faster than ~25 grid-synchronised levels
+
+
+def _workspace(N, dev):
+    need = int(lib.lodgs_cut_workspace_bytes(N))
+    ws = _ws_cache.get(dev.index)
+    if ws is None or ws.numel() < need:
+        ws = torch.empty(need, dtype=torch.uint8, device=dev)
+        _ws_cache[dev.index] = ws
+    return ws
+
+
+def prepare_hierarchy(nodes, boxes):
+    """Validate once that the traversal cut selects exactly the flat rule's set (monotone sizes, single root)."""
+    N = nodes.size(0)
+    ws = _workspace(N, nodes.device)
+    ok = C.c_int32(0)
+    check(lib.lodgs_cut_prepare(ptr(nodes), ptr(boxes), N, ws.data_ptr(), ws.numel(), C.addressof(ok), current_stream()))
+    _traversable[(nodes.data_ptr(), N)] = bool(ok.value)
+    return bool(ok.value)
+
+
+def expand_to_size(nodes, boxes, size, viewpoint, viewdir, render_indices, parent_indices, nodes_for_render_indices,
+                   mode=None):
+    """-> number of cut entries K; writes render_indices[:K], parent_indices[:K], nodes_for_render_indices[:K]."""
+    if nodes.device.type != "cuda":
+        raise RuntimeError("expand_to_size needs CUDA tensors (there is no CPU path)")
+    dev = nodes.device
+    nodes, boxes = nodes.contiguous(), boxes.contiguous()
+    N = nodes.size(0)
+    vp = viewpoint.to(device=dev, dtype=torch.float32).contiguous()
+    if mode is None:
+        mode = 1 if (N >= TRAVERSAL_MIN_NODES and _traversable.get((nodes.data_ptr(), N), False)) else 0
+    if mode == 1 and not _traversable.get((nodes.data_ptr(), N), False):
+        if not prepare_hierarchy(nodes, boxes):
+            mode = 0
+    ws = _workspace(N, dev)
+    capacity = min(render_indices.numel(), parent_indices.numel() if parent_indices.numel() else 1 << 62,
+                   nodes_for_render_indices.numel() if nodes_for_render_indices.numel() else 1 << 62)
+    count = C.c_int32(0)
+    check(lib.lodgs_expand_to_size(ptr(nodes), ptr(boxes), N, float(size), ptr(vp), ptr(render_indices), ptr(parent_indices),
+                                   ptr(nodes_for_render_indices), int(capacity), ws.data_ptr(), ws.numel(), int(mode),
+                                   C.addressof(count), current_stream()))
+    return int(count.value)
+
+
+def get_interpolation_weights(indices, size, nodes, boxes, viewpoint, viewdir, ts, num_kids):
+    K = indices.size(0)
+    if K == 0:
+        return
+    v = viewpoint.detach().to("cpu", torch.float32)
+    check(lib.lodgs_get_interpolation_weights(ptr(indices.contiguous()), K, float(size), ptr(nodes.contiguous()),
+                                              ptr(boxes.contiguous()), float(v[0]), float(v[1]), float(v[2]), ptr(ts),
+                                              ptr(num_kids), current_stream()))
+
+
+def load_hierarchy(filename):
+    """-> (pos[P,3], shs[P,16,3], alpha[P,1], scales[P,3], rot[P,4], nodes[N,7] i32, boxes[N,2,4]) CPU tensors."""
+    P, N = C.c_int32(0), C.c_int32(0)
+    fn = str(filename).encode()
+    try:
+        check(lib.lodgs_hier_probe(fn, C.addressof(P), C.addressof(N)))
+    except LodgsError as e:
+        raise RuntimeError(str(e).split(": ", 1)[-1])
+    P, N = P.value, N.value
+    pos, shs = torch.empty(P, 3), torch.empty(P, 16, 3)
+    alpha, scales, rot = torch.empty(P, 1), torch.empty(P, 3), torch.empty(P, 4)
+    nodes, boxes = torch.empty(N, 7, dtype=torch.int32), torch.empty(N, 2, 4)
+    check(lib.lodgs_hier_load(fn, pos.data_ptr(), shs.data_ptr(), alpha.data_ptr(), scales.data_ptr(), rot.data_ptr(),
+                              nodes.data_ptr(), boxes.data_ptr()))
+    return pos, shs, alpha, scales, rot, nodes, boxes
+
+
+def write_hierarchy(filename, pos, shs, opacities, log_scales, rotations, nodes, boxes, compressed=False):
+    t = [x.detach().to("cpu").contiguous() for x in (pos, shs, opacities, log_scales, rotations)]
+    nodes_c, boxes_c = nodes.detach().to("cpu", torch.int32).contiguous(), boxes.detach().to("cpu", torch.float32).contiguous()
+    check(lib.lodgs_hier_write(str(filename).encode(), t[0].size(0), nodes_c.size(0), t[0].data_ptr(), t[1].data_ptr(),
+                               t[2].data_ptr(), t[3].data_ptr(), t[4].data_ptr(), nodes_c.data_ptr(), boxes_c.data_ptr(),
+                               1 if compressed else 0))
