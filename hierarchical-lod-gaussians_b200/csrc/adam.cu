@@ -60,6 +60,7 @@ extern "C" int lodgs_adam_step(float* param, const float* grad, float* exp_avg, 
     const long long total = n_rows * width;
     int blocks = (int)std::min<long long>((total + 255) / 256, 148LL * 16);
     cudaStream_t s = (cudaStream_t)stream;
+    prof_stage_begin(s);
     if (bias_correction) {
         if (step < 1) { set_error("lodgs_adam_step: step must be >= 1 with bias correction"); return LODGS_E_ARG; }
         // bias terms in double on the host, exactly like the Python floats in OurAdam.py:331-337

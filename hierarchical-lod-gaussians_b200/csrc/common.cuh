@@ -14,6 +14,8 @@ namespace lodgs {
 void set_error(const char* fmt, ...);
 void count_launch();
 int check_cuda(cudaError_t e, const char* what);
+void prof_stage_begin(cudaStream_t s);
+void prof_mark(const char* name);
 
 #define LODGS_CUDA(call)                                              \
     do {                                                              \
@@ -24,6 +26,7 @@ int check_cuda(cudaError_t e, const char* what);
 #define LODGS_LAUNCHED(name)                                          \
     do {                                                              \
         ::lodgs::count_launch();                                      \
+        ::lodgs::prof_mark(name);                                     \
         cudaError_t e__ = cudaGetLastError();                         \
         if (e__ != cudaSuccess) return ::lodgs::check_cuda(e__, name); \
     } while (0)

@@ -411,6 +411,7 @@ extern "C" int lodgs_cut_prepare(const int32_t* nodes, const float* boxes, int N
     if (!nodes || !boxes || !ws || !monotone_host || N < 0) { set_error("lodgs_cut_prepare: bad argument"); return LODGS_E_ARG; }
     if (ws_bytes < lodgs_cut_workspace_bytes(N)) { set_error("lodgs_cut_prepare: workspace too small"); return LODGS_E_WORKSPACE; }
     cudaStream_t s = (cudaStream_t)stream;
+    prof_stage_begin(s);
     CutWs c = carve(ws, N);
     int one = 1;
     LODGS_CUDA(cudaMemcpyAsync(&c.hdr->monotone, &one, sizeof(int), cudaMemcpyHostToDevice, s));
@@ -433,6 +434,7 @@ extern "C" int lodgs_expand_to_size(const int32_t* nodes, const float* boxes, in
     }
     if (ws_bytes < lodgs_cut_workspace_bytes(N)) { set_error("lodgs_expand_to_size: workspace too small (%zu < %zu)", ws_bytes, lodgs_cut_workspace_bytes(N)); return LODGS_E_WORKSPACE; }
     cudaStream_t s = (cudaStream_t)stream;
+    prof_stage_begin(s);
     CutWs c = carve(ws, N);
     if (N == 0) {
         LODGS_CUDA(cudaMemsetAsync(c.hdr, 0, sizeof(CutHeader), s));
@@ -485,6 +487,7 @@ extern "C" int lodgs_get_interpolation_weights(const int32_t* node_indices, int 
         return LODGS_E_ARG;
     }
     if (K == 0) return LODGS_OK;
+    prof_stage_begin((cudaStream_t)stream);
     cut_weights_kernel<<<(K + 255) / 256, 256, 0, (cudaStream_t)stream>>>(nodes, boxes, K, node_indices, vx, vy, vz, target_size,
                                                                          ts, num_siblings);
     LODGS_LAUNCHED("cut_weights_kernel");

@@ -265,6 +265,7 @@ extern "C" int lodgs_forward_preprocess(int P, int D, int M, int W, int H, const
     if (geom_bytes < lodgs_geom_bytes(P) - 128) { set_error("lodgs_forward_preprocess: geometry buffer too small"); return LODGS_E_WORKSPACE; }
     if (((uintptr_t)geom_buffer & 127) != 0) { set_error("lodgs_forward_preprocess: geometry buffer must be 128-byte aligned"); return LODGS_E_ARG; }
     cudaStream_t s = (cudaStream_t)stream;
+    prof_stage_begin(s);
     GeomState g = geom_from_chunk(geom_buffer, P);
     PreParams p;
     p.P = P; p.D = D; p.M = M; p.W = W; p.H = H;
@@ -294,6 +295,7 @@ extern "C" int lodgs_mark_visible(int P, const float* means3D, const float* view
     (void)projmatrix;
     if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) { set_error("lodgs_mark_visible: bad argument"); return LODGS_E_ARG; }
     if (P == 0) return LODGS_OK;
+    prof_stage_begin((cudaStream_t)stream);
     mark_visible_kernel<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream>>>(P, means3D, viewmatrix, present);
     LODGS_LAUNCHED("mark_visible_kernel");
     return LODGS_OK;

@@ -241,5 +241,6 @@ extern "C" int lodgs_sort_pairs(const uint64_t* keys_in, const uint32_t* values_
     if (n >= (1 << 30)) { set_error("lodgs_sort_pairs: n must be < 2^30"); return LODGS_E_ARG; }
     if (ws_bytes < lodgs_sort_workspace_bytes(n) - 128) { set_error("lodgs_sort_pairs: workspace too small"); return LODGS_E_WORKSPACE; }
     if (((uintptr_t)ws & 127) != 0) { set_error("lodgs_sort_pairs: workspace must be 128-byte aligned"); return LODGS_E_ARG; }
+    prof_stage_begin((cudaStream_t)stream);
     return sort_pairs_device(keys_in, values_in, keys_out, values_out, keys_tmp, values_tmp, n, end_bit, ws, (cudaStream_t)stream);
 }

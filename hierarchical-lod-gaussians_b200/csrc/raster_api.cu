@@ -70,6 +70,7 @@ extern "C" int lodgs_forward_render(int P, int W, int H, int R, const float* bac
     if (image_bytes < lodgs_image_bytes(W, H) - 128) { set_error("lodgs_forward_render: image buffer too small"); return LODGS_E_WORKSPACE; }
     if (((uintptr_t)image_buffer & 127) != 0) { set_error("lodgs_forward_render: image buffer must be 128-byte aligned"); return LODGS_E_ARG; }
     cudaStream_t s = (cudaStream_t)stream;
+    prof_stage_begin(s);
     ImageState img = image_from_chunk(image_buffer, W, H);
     const unsigned gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     BinningFull bf;
@@ -137,6 +138,7 @@ extern "C" int lodgs_backward(int P, int fullP, int D, int M, int R, int W, int 
     if (shs && !dL_dsh) { set_error("lodgs_backward: dL_dsh missing"); return LODGS_E_ARG; }
     if (scales && (!rotations || !dL_dscale || !dL_drot)) { set_error("lodgs_backward: scale/rotation gradient buffers missing"); return LODGS_E_ARG; }
     cudaStream_t s = (cudaStream_t)stream;
+    prof_stage_begin(s);
     GeomState g = geom_from_chunk(geom_buffer, P);
     ImageState img = image_from_chunk(image_buffer, W, H);
     if (R > 0) {

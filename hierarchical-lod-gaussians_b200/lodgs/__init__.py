@@ -43,6 +43,8 @@ _SIGS = {
     "lodgs_version": (_i, []),
     "lodgs_compiled_sm": (_i, []),
     "lodgs_launch_count": (C.c_uint64, []),
+    "lodgs_profile": (_i, [_i]),
+    "lodgs_profile_dump": (_i, [C.c_char_p, _sz]),
     "lodgs_cut_workspace_bytes": (_sz, [_i]),
     "lodgs_expand_to_size": (_i, [_p, _p, _i, _f, _p, _p, _p, _p, _i, _p, _sz, _i, _p, _p]),
     "lodgs_cut_prepare": (_i, [_p, _p, _i, _p, _sz, _p, _p]),
@@ -119,3 +121,18 @@ def current_stream():
 
 def launch_count():
     return int(lib.lodgs_launch_count())
+
+
+def profile(enable):
+    check(lib.lodgs_profile(1 if enable else 0))
+
+
+def profile_dump():
+    """-> {kernel_name: (total_ms, launches)} since profile(True)."""
+    buf = C.create_string_buffer(1 << 16)
+    check(lib.lodgs_profile_dump(buf, len(buf)))
+    out = {}
+    for line in buf.value.decode().splitlines():
+        name, ms, n = line.rsplit(" ", 2)
+        out[name] = (float(ms), int(n))
+    return out

@@ -35,6 +35,11 @@ int lodgs_version(void);
 int lodgs_compiled_sm(void);
 /* Number of kernels launched by this library since load (bench.py's gpu_launches). */
 uint64_t lodgs_launch_count(void);
+/* Per-kernel device timing for bench.py's roofline: lodgs_profile(1) starts recording a CUDA event after every
+ * kernel launch on the launching stream (and at every API entry), lodgs_profile(0) stops and clears.
+ * lodgs_profile_dump synchronises the device and writes "kernel_name total_ms launches\n" lines into buf. */
+int lodgs_profile(int enable);
+int lodgs_profile_dump(char* buf, size_t nbytes);
 
 /* ------------------------------------------------------------------------------------------------
  * LOD cut.  Replaces Switching::expandToSize (GH/runtime_switching.cu:997-1030:

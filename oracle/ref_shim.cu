@@ -92,6 +92,12 @@ REF_API void ref_get_ts_indexed(int K, int* indices, float target_size, int* nod
     Switching::getTsIndexed(K, indices, target_size, nodes, boxes, vx, vy, vz, zx, zy, zz, ts, kids, stream);
 }
 
+REF_API int ref_copy_d2d(void* dst, const void* src, size_t nbytes) {
+    cudaError_t e = cudaMemcpy(dst, src, nbytes, cudaMemcpyDeviceToDevice);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    return (int)e;
+}
+
 REF_API void ref_free(void) {
     for (Buf* b : {&g_geom, &g_bin, &g_img}) {
         if (b->p) cudaFree(b->p);

@@ -1,13 +1,13 @@
 """TEST INFRASTRUCTURE: ctypes loader for oracle/_ref/libref_lodgs.so — the UNMODIFIED reference CUDA kernels
-(built by oracle/Makefile from /root/reference) behind oracle/ref_shim.cu. Used by GPU parity tests and by
-bench.py --impl reference only."""
+(built by oracle/Makefile from /root/reference) behind oracle/ref_shim.cu. Used by the GPU parity tests, by
+__graft_entry__.smoke() and by bench.py --impl reference only; never by the product path."""
 import ctypes as C
 import os
 
 import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-REF_LIB = os.path.join(ROOT, "oracle", "_ref", "libref_lodgs.so")
+REF_LIB = os.path.join(ROOT, "oracle", "_ref", "libref_lodgs.so")  # ROOT = repo root
 _p, _i, _f = C.c_void_p, C.c_int, C.c_float
 _lib = None
 
@@ -26,6 +26,8 @@ def lib():
         _lib.ref_backward.restype = None
         _lib.ref_backward.argtypes = [_i, _i, _i, _i, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _f, _f,
                                       _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i]
+        _lib.ref_copy_d2d.restype = _i
+        _lib.ref_copy_d2d.argtypes = [_p, _p, C.c_size_t]
         _lib.ref_geom_ptrs.argtypes = [_i, _p]
         _lib.ref_binning_ptrs.argtypes = [_i, _p]
         _lib.ref_image_ptrs.argtypes = [_i, _p]
@@ -43,11 +45,9 @@ def ptr(t):
 def _from_dev(p, nbytes, dtype, shape):
     """Copy `nbytes` from raw device pointer p into a new CUDA tensor."""
     out = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
-    cudart = torch.cuda.cudart()
     torch.cuda.synchronize()
-    rc = cudart.cudaMemcpy(out.data_ptr(), p, nbytes, 3)  # cudaMemcpyDeviceToDevice
-    assert int(rc) == 0 if not isinstance(rc, tuple) else int(rc[0]) == 0
-    torch.cuda.synchronize()
+    rc = lib().ref_copy_d2d(out.data_ptr(), p, nbytes)
+    assert rc == 0, "ref_copy_d2d failed with CUDA error %d" % rc
     return out.view(dtype).reshape(shape)
 
 

@@ -8,7 +8,7 @@ import torch
 
 import conftest  # noqa: F401  (sets sys.path)
 import minewrap
-import refshim
+from oracle import refshim
 from lodgs import synth
 
 
