@@ -1,0 +1,310 @@
+"""benchlib.py — the two arms of bench.py (kept separate so that each file stays small).
+
+run_ours      : product path (diff_gaussian_rasterization._C -> liblodgs.so).
+run_reference : the UNMODIFIED reference CUDA rasterizer rebuilt for sm_100a (oracle/_ref/libref_lodgs.so, built by
+                oracle/Makefile from /root/reference) on the same inputs through the same protocol. The reference has
+                no CPU implementation of this path, so its own code on the same B200 is the honest
+                reference arm; the CPU restatement is reported separately as cpu_baseline.
+"""
+import json
+import os
+import time
+
+import numpy as np
+import torch
+
+from bench import ClockSampler, DEG, H, M, ROOT, W, make_inputs
+
+E = lambda dev, dt=torch.float32: torch.empty(0, device=dev, dtype=dt)  # noqa: E731
+PARAM_KEYS = ("means3D", "shs", "opacities", "scales", "rotations")
+
+
+def _pin(d):
+    return {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for k, v in d.items() if isinstance(v, np.ndarray)}
+
+
+def _barrier(world):
+    if world > 1:
+        torch.distributed.barrier()
+    torch.cuda.synchronize()
+
+
+def _max_over_ranks(x, world, dev):
+    if world == 1:
+        return x
+    t = torch.tensor([x], dtype=torch.float64, device=dev)
+    torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    return float(t.item())
+
+
+def _sum_over_ranks(x, world, dev):
+    if world == 1:
+        return x
+    t = torch.tensor([x], dtype=torch.float64, device=dev)
+    torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.SUM)
+    return float(t.item())
+
+
+def _timed(step_fn, steps, warmup, world, dev, sampler=None):
+    """W untimed warm-up steps, then exactly K steps between barrier+synchronize, CUDA events on the current stream."""
+    for _ in range(warmup):
+        step_fn()
+    _barrier(world)
+    if sampler is not None:
+        sampler.start()
+        time.sleep(0.25)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    _barrier(world)
+    ev0.record()
+    for _ in range(steps):
+        step_fn()
+    ev1.record()
+    _barrier(world)
+    ms = ev0.elapsed_time(ev1)
+    return _max_over_ranks(ms, world, dev)
+
+
+class OursArm:
+    def __init__(self, sc_host, cam_host, target_host, dev):
+        from diff_gaussian_rasterization import _C
+        self._C = _C
+        self.dev = dev
+        self.host = _pin(sc_host)
+        self.target_host = torch.from_numpy(target_host).pin_memory()
+        self.cam = {k: (torch.from_numpy(v).to(dev) if isinstance(v, np.ndarray) else v) for k, v in cam_host.items()}
+        self.bg = torch.zeros(3, device=dev)
+        self.d = {k: self.host[k].to(dev) for k in PARAM_KEYS}
+        self.target = self.target_host.to(dev)
+        self.ei, self.ef = E(dev, torch.int32), E(dev)
+        self.out_host = None
+        self.last = None
+
+    def fwd_bwd(self, d, target):
+        c = self.cam
+        fa = (self.bg, self.ei, self.ei, self.ef, self.ei, d["means3D"], self.ef, d["opacities"], d["scales"], d["rotations"], 1.0,
+              self.ef, c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"], H, W, d["shs"], DEG, c["campos"], False, False,
+              True)
+        R, color, radii, geom, binning, img, invdepth, seen = self._C.rasterize_gaussians(*fa)
+        dL = (color - target) * (2.0 / color.numel())
+        dLi = torch.zeros_like(invdepth)
+        ba = (self.bg, self.ei, self.ei, self.ef, self.ei, d["means3D"], radii, self.ef, d["opacities"], d["scales"], d["rotations"],
+              1.0, self.ef, c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"], dL, dLi, d["shs"], DEG, c["campos"], geom, R,
+              binning, img, False)
+        grads = self._C.rasterize_gaussians_backward(*ba)
+        self.last = (R, color, radii, img, grads)
+        return color, grads
+
+    def step_resident(self):
+        self.fwd_bwd(self.d, self.target)
+
+    def step_e2e(self):
+        d = {k: self.host[k].to(self.dev, non_blocking=True) for k in PARAM_KEYS}
+        target = self.target_host.to(self.dev, non_blocking=True)
+        color, g = self.fwd_bwd(d, target)
+        outs = (color, g[3], g[5], g[2], g[6], g[7])  # image, dL_dmeans3D, dL_dsh, dL_dopacity, dL_dscales, dL_drotations
+        if self.out_host is None:
+            self.out_host = [torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in outs]
+        for h, o in zip(self.out_host, outs):
+            h.copy_(o, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    def io_bytes(self):
+        h2d = sum(self.host[k].numel() * 4 for k in PARAM_KEYS) + self.target_host.numel() * 4
+        d2h = sum(h.numel() * 4 for h in self.out_host) if self.out_host else 0
+        return h2d, d2h
+
+
+class RefArm(OursArm):
+    """Same protocol over the reference CUDA build (oracle/_ref)."""
+
+    def __init__(self, sc_host, cam_host, target_host, dev):
+        from oracle import refshim
+        if not refshim.available():
+            raise FileNotFoundError(refshim.REF_LIB)
+        self.ref = refshim
+        self.dev = dev
+        self.host = _pin(sc_host)
+        self.target_host = torch.from_numpy(target_host).pin_memory()
+        self.cam = {k: (torch.from_numpy(v).to(dev) if isinstance(v, np.ndarray) else v) for k, v in cam_host.items()}
+        self.bg = torch.zeros(3, device=dev)
+        self.d = {k: self.host[k].to(dev) for k in PARAM_KEYS}
+        self.target = self.target_host.to(dev)
+        self.out_host = None
+        self.last = None
+
+    def fwd_bwd(self, d, target):
+        L, ptr, c = self.ref.lib(), self.ref.ptr, self.cam
+        P = d["means3D"].size(0)
+        dev = self.dev
+        # allocations + zero fills exactly as RasterizeGaussiansCUDA / ...BackwardCUDA do (HR/rasterize_points.cu:73-92,178-187)
+        color = torch.zeros(3, H, W, device=dev)
+        invdepth = torch.zeros(1, H, W, device=dev)
+        radii = torch.zeros(P, dtype=torch.int32, device=dev)
+        rects = torch.zeros(P, 2, dtype=torch.int32, device=dev)
+        seen = torch.zeros(P, dtype=torch.int32, device=dev)
+        R = L.ref_forward(P, DEG, M, ptr(self.bg), W, H, None, None, None, None, ptr(d["means3D"]), ptr(d["shs"]), None,
+                          ptr(d["opacities"]), ptr(d["scales"]), 1.0, ptr(d["rotations"]), None, ptr(c["viewmatrix"]),
+                          ptr(c["projmatrix"]), ptr(c["campos"]), c["tanfovx"], c["tanfovy"], 0, ptr(color), ptr(invdepth), ptr(radii),
+                          ptr(rects), 0, ptr(seen))
+        dL = (color - target) * (2.0 / color.numel())
+        dLi = torch.zeros_like(invdepth)
+        z = lambda *s: torch.zeros(*s, device=dev)  # noqa: E731
+        g2, gc, go, gcol, gi = z(P, 3), z(P, 2, 2), z(P, 1), z(P, 3), z(P, 1)
+        g3, gcov, gsh, gs, gr = z(P, 3), z(P, 6), z(P, M, 3), z(P, 3), z(P, 4)
+        L.ref_backward(P, DEG, M, R, ptr(self.bg), W, H, None, None, None, None, ptr(d["means3D"]), ptr(d["shs"]), None,
+                       ptr(d["opacities"]), ptr(d["scales"]), 1.0, ptr(d["rotations"]), None, ptr(c["viewmatrix"]), ptr(c["projmatrix"]),
+                       ptr(c["campos"]), c["tanfovx"], c["tanfovy"], ptr(radii), ptr(dL), ptr(dLi), ptr(g2), ptr(gc), ptr(go), ptr(gcol),
+                       ptr(gi), ptr(g3), ptr(gcov), ptr(gsh), ptr(gs), ptr(gr), 0)
+        grads = (g2, gcol, go, g3, gcov, gsh, gs, gr)
+        self.last = (R, color, radii, None, grads)
+        return color, grads
+
+
+# ------------------------------------------------------------------------------------------------ roofline
+def _peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            p = json.load(fh)
+        return float(p.get("hbm_gbs", 6650.0)), float(p.get("sm_max_mhz", 1965.0)), "measured"
+    return 6650.0, 1965.0, "fallback"
+
+
+def _work_model(arm, n_gauss):
+    """Algorithmic work per step of every kernel (DESIGN.md 'Kernels and rooflines')."""
+    import ctypes as C
+
+    import lodgs
+    R, color, radii, img, grads = arm.last
+    p_vis = int((radii > 0).sum().item())
+    cnt = torch.zeros(3, dtype=torch.int64, device=arm.dev)
+    # counters need the buffers of the last forward: redo one forward and count on its buffers
+    c, d = arm.cam, arm.d
+    fa = (arm.bg, arm.ei, arm.ei, arm.ef, arm.ei, d["means3D"], arm.ef, d["opacities"], d["scales"], d["rotations"], 1.0, arm.ef,
+          c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"], H, W, d["shs"], DEG, c["campos"], False, False, True)
+    R, color, radii, geom, binning, imgb, invdepth, seen = arm._C.rasterize_gaussians(*fa)
+    lodgs.check(lodgs.lib.lodgs_blend_stats(W, H, R, 0, binning.data_ptr(), imgb.data_ptr(), cnt.data_ptr(), lodgs.current_stream()))
+    torch.cuda.synchronize()
+    n_test, n_alpha, n_blend = (int(x) for x in cnt.tolist())
+    work = {
+        "preprocess_fwd_kernel": ("hbm", 20.0 * n_gauss + p_vis * (115.0 + 12.0 * M)),
+        "emit_keys_kernel": ("hbm", 24.0 * n_gauss + 12.0 * R),
+        "sort_histogram_kernel": ("hbm", 8.0 * R),
+        "sort_onesweep_kernel": ("hbm", 24.0 * R),          # per launch (one digit pass)
+        "tile_ranges_kernel": ("hbm", 8.0 * R),
+        "build_records_kernel": ("hbm", (4.0 + 44.0 + 48.0) * R),
+        "blend_fwd_kernel": ("fp32", 11.0 * n_test + 2.0 * n_alpha + 14.0 * n_blend),
+        "blend_bwd_kernel": ("fp32", 70.0 * n_blend),
+        "preprocess_bwd_kernel": ("hbm", p_vis * (115.0 + 68.0 + 24.0 * M)),
+    }
+    return work, {"num_rendered": R, "p_visible": p_vis, "n_test": n_test, "n_alpha": n_alpha, "n_blend": n_blend}
+
+
+def _roofline(prof, steps, work, sm_count):
+    hbm_peak, sm_max_mhz, which = _peaks()
+    fp32_peak = sm_count * 128 * 2 * sm_max_mhz * 1e6 / 1e12  # TFLOP/s at max clock
+    per_kernel = []
+    for name, (ms, n) in prof.items():
+        avg_ms = ms / max(n, 1)
+        ent = {"kernel": name, "launches_per_step": n / steps, "avg_ms": round(avg_ms, 5), "ms_per_step": round(ms / steps, 5)}
+        if name in work:
+            bound, amount = work[name]
+            if bound == "hbm":
+                ach = amount / (avg_ms * 1e-3) / 1e9
+                ent.update({"bound": "hbm", "achieved": round(ach, 1), "peak": hbm_peak, "unit": "GB/s", "frac": round(ach / hbm_peak, 4)})
+            else:
+                ach = amount / (avg_ms * 1e-3) / 1e12
+                ent.update({"bound": "fp32", "achieved": round(ach, 3), "peak": round(fp32_peak, 1), "unit": "TFLOP/s",
+                            "frac": round(ach / fp32_peak, 4)})
+        per_kernel.append(ent)
+    per_kernel.sort(key=lambda e: -e["ms_per_step"])
+    dom = next((e for e in per_kernel if "bound" in e), None)
+    roof = None
+    if dom is not None:
+        roof = {"kernel": dom["kernel"], "bound": dom["bound"], "achieved": dom["achieved"], "peak": dom["peak"], "unit": dom["unit"],
+                "frac": dom["frac"], "traffic": None,
+                "peak_source": ("%s HBM copy bandwidth (MEASURED_PEAKS.json)" % which) if dom["bound"] == "hbm" else
+                "nominal FP32 pipe: SMs x 128 lanes x 2 x max SM clock (no tensor cores on this path)"}
+    return roof, per_kernel
+
+
+def _cpu_baseline(no_cpu):
+    """Oracle port (oracle/raster_oracle.c, OpenMP) timed on a bounded sample of workload A."""
+    if no_cpu:
+        return None
+    try:
+        from oracle import oracle as orc
+        return orc.bench_sample(W, H)
+    except Exception as e:  # noqa: BLE001
+        return {"value": None, "unit": "Mpix/s", "cores": 0, "kind": "port", "sample": "unavailable: %s" % str(e)[:120]}
+
+
+def _line(args, world, value, ms_per_step, clocks, extra):
+    line = {"metric": "fwd+bwd Mpix/s @1080p", "value": round(value, 2), "unit": "Mpix/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "A: configs/vanilla.json fwd+bwd rasterization, %d synthetic Gaussians (SH deg 3), one 1920x1080 view "
+                                   "per GPU" % args.P, "gaussians": args.P, "width": W, "height": H, "sh_degree": DEG,
+                       "parallelism": "views sharded across GPUs, no collective", "l2": "inputs larger than L2 (params 236 MB + "
+                       "grads 236 MB + binning state per step)"},
+            "clocks": clocks}
+    line.update(extra)
+    return line
+
+
+def run_ours(args, rank, world, dev):
+    import lodgs
+    sc, cam, target = make_inputs(rank, args.P)
+    arm = OursArm(sc, cam, target, dev)
+    sampler = ClockSampler(dev.index) if rank == 0 else None
+    launches0 = lodgs.launch_count()
+    for _ in range(args.warmup):
+        arm.step_resident()
+    torch.cuda.synchronize()
+    lodgs.profile(True)
+    launches0 = lodgs.launch_count()
+    ms = _timed(arm.step_resident, args.steps, 0, world, dev, sampler)
+    launches = lodgs.launch_count() - launches0
+    prof = lodgs.profile_dump()
+    lodgs.profile(False)
+    clocks = sampler.stop() if sampler else None
+    ms_e2e = _timed(arm.step_e2e, args.steps, max(3, args.warmup // 2), world, dev)
+    h2d, d2h = arm.io_bytes()
+    mpix = W * H / 1e6
+    value = world * mpix * args.steps / (ms * 1e-3)
+    e2e = world * mpix * args.steps / (ms_e2e * 1e-3)
+    if rank != 0:
+        return None
+    sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
+    work, counters = _work_model(arm, args.P)
+    roof, per_kernel = _roofline(prof, args.steps, work, sm_count)
+    extra = {"impl": "ours", "e2e": {"value": round(e2e, 2), "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                                     "ms_per_step": round(ms_e2e / args.steps, 4)},
+             "gpu_launches": int(launches), "roofline": roof, "per_kernel": per_kernel, "workload_counters": counters,
+             "cpu_baseline": _cpu_baseline(args.no_cpu_baseline)}
+    return _line(args, world, value, ms / args.steps, clocks, extra)
+
+
+def run_reference(args, rank, world, dev):
+    sc, cam, target = make_inputs(rank, args.P)
+    try:
+        arm = RefArm(sc, cam, target, dev)
+    except (FileNotFoundError, OSError) as e:
+        return {"impl": "reference", "unavailable": "oracle/_ref/libref_lodgs.so missing or not loadable (%s)" % str(e)[:80]}
+    sampler = ClockSampler(dev.index) if rank == 0 else None
+    ms = _timed(arm.step_resident, args.steps, args.warmup, world, dev, sampler)
+    clocks = sampler.stop() if sampler else None
+    ms_e2e = _timed(arm.step_e2e, args.steps, max(3, args.warmup // 2), world, dev)
+    h2d, d2h = arm.io_bytes()
+    mpix = W * H / 1e6
+    value = world * mpix * args.steps / (ms * 1e-3)
+    e2e = world * mpix * args.steps / (ms_e2e * 1e-3)
+    if rank != 0:
+        return None
+    extra = {"impl": "reference",
+             "e2e": {"value": round(e2e, 2), "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                     "ms_per_step": round(ms_e2e / args.steps, 4)},
+             "cpu_baseline": {"value": round(e2e, 2), "unit": "Mpix/s", "cores": 0, "kind": "reference",
+                              "sample": "full workload; the reference has no CPU implementation of this path, so this arm runs its "
+                                        "unmodified CUDA kernels (oracle/_ref, sm_100a rebuild) on the same B200"}}
+    return _line(args, world, value, ms / args.steps, clocks, extra)

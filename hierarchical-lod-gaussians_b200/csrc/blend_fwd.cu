@@ -176,4 +176,59 @@ int launch_blend_fwd(bool lod, bool depth, const ImageState& img, const BinningS
     return launch_blend_seen<false, false>(hs, grid, block, s, img.ranges, bin.recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
 }
 
+// Work counters of the blend (bench.py roofline): replays the forward's per-pixel decisions and counts
+// N_test (pairs whose quadratic form is evaluated), N_alpha (pairs that reach the exponential) and N_blend
+// (pairs that are blended). Not on any product path.
+template <bool LOD>
+__global__ void __launch_bounds__(TILE_PIX) blend_stats_kernel(const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs, int W,
+                                                              int H, unsigned long long* __restrict__ counters) {
+    const unsigned horizontal_blocks = (W + TILE_X - 1) / TILE_X;
+    const uint2 pix = {blockIdx.x * TILE_X + threadIdx.x, blockIdx.y * TILE_Y + threadIdx.y};
+    const float2 pixf = {(float)pix.x, (float)pix.y};
+    const bool inside = pix.x < (unsigned)W && pix.y < (unsigned)H;
+    const uint2 range = ranges[blockIdx.y * horizontal_blocks + blockIdx.x];
+    unsigned n_test = 0, n_alpha = 0, n_blend = 0;
+    float T = 1.0f;
+    if (inside) {
+        for (unsigned i = range.x; i < range.y; i++) {
+            const float4 q0 = __ldg(reinterpret_cast<const float4*>(recs + i));
+            const float4 q1 = __ldg(reinterpret_cast<const float4*>(recs + i) + 1);
+            n_test++;
+            const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
+            const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
+            if (power > 0.0f) continue;
+            n_alpha++;
+            const float my_alpha = min(0.99f, q1.y * expf(power));
+            float alpha = my_alpha;
+            if (LOD) {
+                const float4 q2 = __ldg(reinterpret_cast<const float4*>(recs + i) + 2);
+                alpha = q2.z * my_alpha + (1.0f - q2.z) * (1.0f - __powf(1.0f - my_alpha, q2.w));
+            }
+            if (alpha < 1.0f / 255.0f) continue;
+            const float test_T = T * (1 - alpha);
+            if (test_T < 0.0001f) break;
+            n_blend++;
+            T = test_T;
+        }
+    }
+    n_test = __reduce_add_sync(0xffffffffu, n_test);
+    n_alpha = __reduce_add_sync(0xffffffffu, n_alpha);
+    n_blend = __reduce_add_sync(0xffffffffu, n_blend);
+    if (((threadIdx.y * TILE_X + threadIdx.x) & 31) == 0) {
+        atomicAdd(counters + 0, (unsigned long long)n_test);
+        atomicAdd(counters + 1, (unsigned long long)n_alpha);
+        atomicAdd(counters + 2, (unsigned long long)n_blend);
+    }
+}
+
+int launch_blend_stats(bool lod, const ImageState& img, const BinningState& bin, int W, int H, unsigned long long* counters,
+                       cudaStream_t s) {
+    dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1), block(TILE_X, TILE_Y, 1);
+    LODGS_CUDA(cudaMemsetAsync(counters, 0, 3 * sizeof(unsigned long long), s));
+    if (lod) blend_stats_kernel<true><<<grid, block, 0, s>>>(img.ranges, bin.recs, W, H, counters);
+    else blend_stats_kernel<false><<<grid, block, 0, s>>>(img.ranges, bin.recs, W, H, counters);
+    LODGS_LAUNCHED("blend_stats_kernel");
+    return LODGS_OK;
+}
+
 }  // namespace lodgs

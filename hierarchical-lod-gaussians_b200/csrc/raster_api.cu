@@ -157,3 +157,16 @@ extern "C" int lodgs_backward(int P, int fullP, int D, int M, int R, int W, int 
                               tan_fovy, dL_dmean2D, dL_dconic, dL_dinvdepth, dL_dcolor, dL_dopacity, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale,
                               dL_drot, s);
 }
+
+namespace lodgs {
+int launch_blend_stats(bool lod, const ImageState& img, const BinningState& bin, int W, int H, unsigned long long* counters,
+                       cudaStream_t s);
+}
+extern "C" int lodgs_blend_stats(int W, int H, int R, int lod, void* binning_buffer, void* image_buffer, uint64_t* counters3_dev,
+                                 void* stream) {
+    if (W <= 0 || H <= 0 || R <= 0 || !binning_buffer || !image_buffer || !counters3_dev) { set_error("lodgs_blend_stats: bad argument"); return LODGS_E_ARG; }
+    cudaStream_t s = (cudaStream_t)stream;
+    prof_stage_begin(s);
+    return launch_blend_stats(lod != 0, image_from_chunk(image_buffer, W, H), binning_from_chunk(binning_buffer, R), W, H,
+                              (unsigned long long*)counters3_dev, s);
+}

@@ -165,6 +165,12 @@ int lodgs_geom_layout(int P, size_t* offsets9);
 int lodgs_binning_layout(int R, size_t* offsets5);
 int lodgs_image_layout(int W, int H, size_t* offsets3);
 
+/* Work counters of the blend for roofline reports (bench.py): after a forward, counts over all pixels the pairs
+ * whose quadratic form is evaluated (N_test), that reach the exponential (N_alpha) and that are blended (N_blend)
+ * into counters3_dev[0..2] (device u64). Not used by any product path. */
+int lodgs_blend_stats(int W, int H, int R, int lod, void* binning_buffer, void* image_buffer, uint64_t* counters3_dev,
+                      void* stream);
+
 /* Stand-alone stable LSD radix sort of (u64 key, u32 value) pairs on bits [0,end_bit) — the onesweep
  * kernel used inside lodgs_forward_render, exported for the CUB cross-check tests.
  * ws must be lodgs_sort_workspace_bytes(n). Result is in keys_out/values_out. */
