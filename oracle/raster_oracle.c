@@ -128,7 +128,7 @@ static uint32_t preprocess_one(const orc_scene* sc, orc_state* st, int t_idx, in
     float p[3] = {own[0], own[1], own[2]};
     if (lod) {
         const float* pa = sc->means3D + 3 * (long)p_idx;
-        for (int i = 0; i < 3; i++) p[i] = t * p[i] + (1.0f - t) * pa[i];
+        for (int i = 0; i < 3; i++) p[i] = fmaf(t, p[i], (1.0f - t) * pa[i]); /* nvcc contracts the lerp this way */
     }
     const float* pm = sc->projmatrix;
     float hom[4] = {pm[0] * p[0] + pm[4] * p[1] + pm[8] * p[2] + pm[12], pm[1] * p[0] + pm[5] * p[1] + pm[9] * p[2] + pm[13],
@@ -144,11 +144,11 @@ static uint32_t preprocess_one(const orc_scene* sc, orc_state* st, int t_idx, in
     for (int i = 0; i < 4; i++) q[i] = sc->rotations[4 * (long)r_idx + i];
     if (lod) {
         float o[4];
-        for (int i = 0; i < 3; i++) s[i] = t * s[i] + (1.0f - t) * sc->scales[3 * (long)p_idx + i];
+        for (int i = 0; i < 3; i++) s[i] = fmaf(t, s[i], (1.0f - t) * sc->scales[3 * (long)p_idx + i]);
         for (int i = 0; i < 4; i++) o[i] = sc->rotations[4 * (long)p_idx + i];
         float dot = (q[0] * o[0] + q[1] * o[1]) + (q[2] * o[2] + q[3] * o[3]);
         if (dot < 0.0) for (int i = 0; i < 4; i++) o[i] = -o[i];
-        for (int i = 0; i < 4; i++) q[i] = t * q[i] + (1.0f - t) * o[i];
+        for (int i = 0; i < 4; i++) q[i] = fmaf(t, q[i], (1.0f - t) * o[i]);
     }
     float* c6 = st->cov3D + 6 * (long)t_idx;
     cov3d(s, sc->scale_modifier, q, c6);
@@ -180,7 +180,7 @@ static uint32_t preprocess_one(const orc_scene* sc, orc_state* st, int t_idx, in
         const float* a = sc->shs + (long)r_idx * sc->M * 3;
         const float* b = lod ? sc->shs + (long)p_idx * sc->M * 3 : NULL;
         for (int k = 0; k < nco; k++)
-            for (int c = 0; c < 3; c++) sh[k][c] = lod ? t * a[3 * k + c] + (1.0f - t) * b[3 * k + c] : a[3 * k + c];
+            for (int c = 0; c < 3; c++) sh[k][c] = lod ? fmaf(t, a[3 * k + c], (1.0f - t) * b[3 * k + c]) : a[3 * k + c];
         float rgb[3];
         sh_rgb(sc->D, sh, d, rgb);
         for (int c = 0; c < 3; c++) {
@@ -192,7 +192,7 @@ static uint32_t preprocess_one(const orc_scene* sc, orc_state* st, int t_idx, in
     st->radii[t_idx] = (int)my_radius;
     st->means2D[2 * (long)t_idx] = pt[0]; st->means2D[2 * (long)t_idx + 1] = pt[1];
     float op = sc->opacities[r_idx];
-    if (lod) op = t * op + (1.0f - t) * sc->opacities[p_idx];
+    if (lod) op = fmaf(t, op, (1.0f - t) * sc->opacities[p_idx]);
     float* co = st->conic_opacity + 4 * (long)t_idx;
     co[0] = conic[0]; co[1] = conic[1]; co[2] = conic[2]; co[3] = op * h_conv;
     return (uint32_t)((rmax[1] - rmin[1]) * (rmax[0] - rmin[0]));

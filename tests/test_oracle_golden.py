@@ -1,0 +1,68 @@
+"""CPU: pins the oracle (oracle/*.c) against golden outputs of the reference's own CUDA kernels (tests/golden/*.npz,
+produced by tests/golden/make_golden.py on a B200). Integer outputs of the cut must be bit-exact; float-derived integer
+outputs of the rasterizer may differ in isolated entries (libm vs CUDA rounding), images/gradients within BASELINE tolerances."""
+import os
+
+import numpy as np
+import pytest
+
+import cases
+from lodgs import synth
+from oracle import oracle as orc
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def rel_l2(a, b):
+    a, b = a.astype(np.float64).ravel(), b.astype(np.float64).ravel()
+    return float(np.linalg.norm(a - b) / (np.linalg.norm(b) + 1e-30))
+
+
+def test_cut_oracle_matches_reference_bit_exact():
+    g = np.load(os.path.join(GOLD, "cut.npz"))
+    nodes, boxes, views = cases.make_cut_case()
+    n = 0
+    for vi, v in enumerate(views):
+        for tau_px in (0, 3, 6, 15, 60):
+            tau = synth.tau_to_threshold(tau_px, 0.8, 1920)
+            ri, pi, ni = orc.expand_to_size(nodes, boxes, np.float32(tau), v)
+            key = "v%d_t%d" % (vi, tau_px)
+            assert np.array_equal(ri, g[key + "_ri"]), key
+            assert np.array_equal(pi, g[key + "_pi"]), key
+            assert np.array_equal(ni, g[key + "_ni"]), key
+            ts, kids = orc.get_interpolation_weights(ni, np.float32(tau), nodes, boxes, v)
+            assert np.array_equal(kids, g[key + "_kids"]), key
+            assert np.array_equal(ts.view(np.uint32), g[key + "_ts"].view(np.uint32)), key  # bit-exact floats too
+            n += len(ri)
+    assert n > 10000
+
+
+@pytest.mark.parametrize("name", list(cases.CASES))
+def test_raster_oracle_matches_reference(name):
+    g = np.load(os.path.join(GOLD, "raster_%s.npz" % name))
+    sc, cam, bg, kw, dL, dLi = cases.make_case(name)
+    f = orc.forward(sc, cam, bg, want_state=True, **kw)
+    P = f["P"]
+    # integers behind float chains: allow isolated differences (<= 0.2 % of entries), everything else equal
+    assert (f["radii"] != g["radii"]).mean() <= 2e-3
+    same_geom = (f["radii"] == g["radii"]) & (f["tiles_touched"].astype(np.int64) == g["tiles_touched"])
+    assert same_geom.mean() >= 0.998
+    if same_geom.all():
+        assert f["R"] == int(g["R"])
+        assert np.array_equal(f["keys_unsorted"].view(np.int64), g["keys_unsorted"])
+        assert np.array_equal(f["keys"].view(np.int64), g["keys"])
+        assert np.array_equal(f["point_list"].astype(np.int32), g["point_list"])
+        assert np.array_equal(f["ranges"].astype(np.int32), g["ranges"])
+        assert (f["n_contrib"].astype(np.int32) != g["n_contrib"]).mean() <= 1e-3
+        assert np.array_equal(f["seen"], g["seen"])
+    vis = g["radii"] > 0
+    assert np.abs(f["means2D"][vis] - g["means2D"][vis]).max() < 1e-3
+    assert rel_l2(f["conic_opacity"][vis], g["conic_opacity"][vis]) < 1e-5
+    assert np.abs(f["color"] - g["color"]).max() < 1e-4
+    assert np.abs(f["invdepth"] - g["invdepth"]).max() < 1e-4
+    gr = orc.backward(f, dL, dLi)
+    orc.free(f)
+    for k in ("dL_dmean2D", "dL_dcolor", "dL_dopacity", "dL_dcov3D", "dL_dsh", "dL_dscale", "dL_drot"):
+        assert rel_l2(gr[k], g[k]) < 1e-3, k
+    if name != "lod":  # reference LOD mean gradients are racy / read uninitialised flags
+        assert rel_l2(gr["dL_dmean3D"], g["dL_dmean3D"]) < 1e-3
