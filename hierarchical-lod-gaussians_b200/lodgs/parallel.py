@@ -1,0 +1,44 @@
+"""Multi-GPU plumbing. One process per GPU, torch.distributed for the only exchange the path has.
+
+* Eval / viewer: frames are independent -> `shard_range` gives each rank a contiguous camera range; the hierarchy and the
+  Gaussians are replicated; no collective on the data path (only `gather_timings` for reports).
+* Multi-view training of one chunk: views are split across ranks, parameters replicated; after backward the dense
+  parameter gradients are summed with ONE all-reduce over a flat bucket (`allreduce_gradients`), then every rank applies
+  the same fused Adam step on identical sums (visibility = dL_dopacity != 0 after the reduce, train_single.py:171-172).
+"""
+import torch
+import torch.distributed as dist
+
+
+def shard_range(n_items, rank, world):
+    """Contiguous [lo, hi) of rank's share of n_items (first n_items % world ranks get one extra)."""
+    if world <= 0 or not (0 <= rank < world):
+        raise ValueError("bad rank/world")
+    base, extra = divmod(n_items, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def allreduce_gradients(grads, group=None):
+    """Sum a list of gradient tensors across ranks through one flat bucket (one NCCL all-reduce over NVLink on a B200 box,
+    gloo on CPU in the tests). Tensors are updated in place; returns the bucket size in bytes."""
+    grads = [g for g in grads if g is not None]
+    if not grads or not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return 0
+    flat = torch.cat([g.reshape(-1) for g in grads])
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    off = 0
+    for g in grads:
+        n = g.numel()
+        g.copy_(flat[off:off + n].view_as(g))
+        off += n
+    return flat.numel() * flat.element_size()
+
+
+def gather_timings(values, group=None):
+    """All ranks contribute a 1-D float64 tensor of per-frame timings; rank 0 gets the list of all."""
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return [values]
+    out = [None] * dist.get_world_size(group)
+    dist.all_gather_object(out, values.tolist(), group=group)
+    return [torch.tensor(o, dtype=torch.float64) for o in out]

@@ -1,0 +1,174 @@
+"""GPU: LOD cut, interpolation weights, onesweep sort and sparse Adam through the C ABI, checked against the oracle,
+the golden vectors of the reference build, the reference CUDA build itself and CUB (torch.sort) respectively."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import cases
+import lodgs
+from gaussian_hierarchy import _C as gh
+from lodgs import synth
+from oracle import oracle as orc
+from oracle import refshim
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+DEV = "cuda"
+
+
+def _cut(nodes_t, boxes_t, tau, v, mode):
+    N = nodes_t.size(0)
+    ri, pi, ni = (torch.full((N,), -7, dtype=torch.int32, device=DEV) for _ in range(3))
+    K = gh.expand_to_size(nodes_t, boxes_t, float(tau), torch.from_numpy(v).to(DEV), torch.zeros(3), ri, pi, ni, mode=mode)
+    return K, ri, pi, ni
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_cut_bit_exact_vs_golden_and_oracle(mode):
+    g = np.load(os.path.join(GOLD, "cut.npz"))
+    nodes, boxes, views = cases.make_cut_case()
+    n_t, b_t = torch.from_numpy(nodes).to(DEV), torch.from_numpy(boxes).to(DEV)
+    if mode == 1:
+        assert gh.prepare_hierarchy(n_t, b_t), "synthetic kd-tree must be traversable"
+    for vi, v in enumerate(views):
+        for tau_px in (0, 3, 6, 15, 60):
+            tau = np.float32(synth.tau_to_threshold(tau_px, 0.8, 1920))
+            K, ri, pi, ni = _cut(n_t, b_t, tau, v, mode)
+            key = "v%d_t%d" % (vi, tau_px)
+            assert K == len(g[key + "_ri"]), key
+            assert np.array_equal(ri[:K].cpu().numpy(), g[key + "_ri"]), key
+            assert np.array_equal(pi[:K].cpu().numpy(), g[key + "_pi"]), key
+            assert np.array_equal(ni[:K].cpu().numpy(), g[key + "_ni"]), key
+            assert (ri[K:] == -7).all()  # nothing written past K
+            ts, kids = torch.zeros(K, device=DEV), torch.zeros(K, dtype=torch.int32, device=DEV)
+            gh.get_interpolation_weights(ni[:K], float(tau), n_t, b_t, torch.from_numpy(v), torch.zeros(3), ts, kids)
+            assert np.array_equal(kids.cpu().numpy(), g[key + "_kids"])
+            assert np.array_equal(ts.cpu().numpy().view(np.uint32), g[key + "_ts"].view(np.uint32))
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_cut_large_random_vs_oracle_and_reference(mode):
+    nodes, boxes, _ = cases.make_cut_case(L=60000, seed=4)
+    n_t, b_t = torch.from_numpy(nodes).to(DEV), torch.from_numpy(boxes).to(DEV)
+    N = nodes.shape[0]
+    rng = np.random.default_rng(9)
+    for trial in range(6):
+        v = (rng.uniform(-1, 1, 3) * np.array([60, 60, 30])).astype(np.float32)
+        tau = np.float32(synth.tau_to_threshold(float(rng.choice([0, 3, 6, 15, 40, 200])), 0.8, 1920))
+        K, ri, pi, ni = _cut(n_t, b_t, tau, v, mode)
+        o_ri, o_pi, o_ni = orc.expand_to_size(nodes, boxes, tau, v)
+        assert K == len(o_ri)
+        assert np.array_equal(ri[:K].cpu().numpy(), o_ri) and np.array_equal(pi[:K].cpu().numpy(), o_pi)
+        assert np.array_equal(ni[:K].cpu().numpy(), o_ni)
+        assert (np.diff(o_ni) > 0).all()  # ascending node ids: the order the stable sort downstream depends on
+        if refshim.available():
+            r_ri, r_pi, r_ni = (torch.zeros(N, dtype=torch.int32, device=DEV) for _ in range(3))
+            vp = torch.from_numpy(v).to(DEV)
+            Kr = refshim.lib().ref_expand_to_size(N, float(tau), n_t.data_ptr(), b_t.data_ptr(), vp.data_ptr(), 0.0, 0.0, 0.0,
+                                                  r_ri.data_ptr(), r_pi.data_ptr(), r_ni.data_ptr())
+            torch.cuda.synchronize()
+            assert Kr == K and torch.equal(r_ri[:K], ri[:K]) and torch.equal(r_pi[:K], pi[:K]) and torch.equal(r_ni[:K], ni[:K])
+
+
+def test_cut_edge_cases():
+    # single root leaf, viewpoint inside the box (size = FLT_MAX) and outside
+    nodes = torch.tensor([[0, -1, 0, 1, 0, -1, 0]], dtype=torch.int32, device=DEV)
+    boxes = torch.tensor([[[-1, -1, -1, 0.0], [1, 1, 1, 0.0]]], device=DEV)
+    for mode in (0, 1):
+        K, ri, pi, ni = _cut(nodes, boxes, 0.01, np.zeros(3, np.float32), mode)
+        assert K == 1 and ri[0] == 0 and pi[0] == -1 and ni[0] == 0
+        K, _, _, _ = _cut(nodes, boxes, 0.01, np.array([5, 0, 0], np.float32), mode)
+        assert K == 0  # a leaf has w = 0 -> size 0 < tau and no parent
+    # capacity overflow is reported, not written past the buffers
+    nodes_np, boxes_np, views = cases.make_cut_case(L=500, seed=2)
+    n_t, b_t = torch.from_numpy(nodes_np).to(DEV), torch.from_numpy(boxes_np).to(DEV)
+    small = torch.zeros(10, dtype=torch.int32, device=DEV)
+    with pytest.raises(lodgs.LodgsError, match="capacity"):
+        gh.expand_to_size(n_t, b_t, 1e-4, torch.from_numpy(views[0]).to(DEV), torch.zeros(3), small, small.clone(), small.clone())
+    # a non-monotone hierarchy is refused by the traversal check (and then served by the flat rule)
+    bad = boxes_np.copy()
+    bad[5, 0, 3] = bad[5, 1, 3] = 1e6
+    assert gh.prepare_hierarchy(n_t, torch.from_numpy(bad).to(DEV)) is False
+
+
+@pytest.mark.parametrize("n,end_bit", [(1, 45), (31, 8), (4096, 45), (4097, 45), (100003, 45), (1 << 20, 64), (777777, 33), (50000, 16)])
+def test_onesweep_sort_matches_stable_sort(n, end_bit):
+    g = torch.Generator(device=DEV).manual_seed(n)
+    keys = torch.randint(0, 1 << 62, (n,), generator=g, device=DEV, dtype=torch.int64)
+    if end_bit < 64:
+        keys &= (1 << end_bit) - 1
+    keys[::3] = keys[0]  # many duplicates: stability matters
+    vals = torch.arange(n, device=DEV, dtype=torch.int32)
+    ko, vo, kt, vt = torch.empty_like(keys), torch.empty_like(vals), torch.empty_like(keys), torch.empty_like(vals)
+    ws = torch.empty(lodgs.lib.lodgs_sort_workspace_bytes(n), dtype=torch.uint8, device=DEV)
+    lodgs.check(lodgs.lib.lodgs_sort_pairs(keys.data_ptr(), vals.data_ptr(), ko.data_ptr(), vo.data_ptr(), kt.data_ptr(), vt.data_ptr(), n,
+                                           end_bit, ws.data_ptr(), ws.numel(), lodgs.current_stream()))
+    want_k, order = torch.sort(keys, stable=True)  # CUB radix sort underneath: the cross-check the north star allows
+    assert torch.equal(ko, want_k)
+    assert torch.equal(vo.long(), order)
+
+
+def test_sort_structured_tile_depth_keys():
+    n = 300000
+    g = torch.Generator(device=DEV).manual_seed(1)
+    tile = torch.randint(0, 8160, (n,), generator=g, device=DEV, dtype=torch.int64)
+    depth = (torch.rand(n, generator=g, device=DEV) * 40 + 0.2).view(torch.int32).long()
+    keys = (tile << 32) | depth
+    vals = torch.arange(n, device=DEV, dtype=torch.int32)
+    ko, vo, kt, vt = torch.empty_like(keys), torch.empty_like(vals), torch.empty_like(keys), torch.empty_like(vals)
+    ws = torch.empty(lodgs.lib.lodgs_sort_workspace_bytes(n), dtype=torch.uint8, device=DEV)
+    lodgs.check(lodgs.lib.lodgs_sort_pairs(keys.data_ptr(), vals.data_ptr(), ko.data_ptr(), vo.data_ptr(), kt.data_ptr(), vt.data_ptr(), n,
+                                           45, ws.data_ptr(), ws.numel(), lodgs.current_stream()))
+    assert (ko[1:] >= ko[:-1]).all() and torch.equal(ko, keys[vo.long()])
+    assert torch.equal(torch.sort(vo).values, vals)  # a permutation
+
+
+def _torch_adam(p, g, m, v, rel, lr, b1, b2, eps, step):
+    """scene/OurAdam.py:_single_tensor_adam, non-capturable branch, restated with torch ops."""
+    import math
+    gi, mi, vi, pi = g[rel], m[rel], v[rel], p[rel]
+    mi.mul_(b1).add_(gi, alpha=1 - b1)
+    vi.mul_(b2).addcmul_(gi, gi, value=1 - b2)
+    bc1, bc2 = 1 - b1 ** step, 1 - b2 ** step
+    denom = (vi.sqrt() / math.sqrt(bc2)).add_(eps)
+    pi.addcdiv_(mi, denom, value=-(lr / bc1))
+    m[rel], v[rel], p[rel] = mi, vi, pi
+
+
+@pytest.mark.parametrize("width", [1, 3, 4, 45])
+def test_sparse_adam_matches_ouradam(width):
+    rows = 5000
+    g = torch.Generator(device=DEV).manual_seed(width)
+    p = torch.randn(rows, width, generator=g, device=DEV)
+    grad = torch.randn(rows, width, generator=g, device=DEV) * 1e-3
+    m, v = torch.randn(rows, width, generator=g, device=DEV) * 1e-3, torch.rand(rows, width, generator=g, device=DEV) * 1e-6
+    rel = torch.randperm(rows, generator=g, device=DEV)[:1700].sort().values
+    p0, m0, v0 = p.clone(), m.clone(), v.clone()
+    pr, mr, vr = p.clone(), m.clone(), v.clone()
+    _torch_adam(pr, grad, mr, vr, rel, 1.6e-4, 0.9, 0.999, 1e-15, 7)
+    lodgs.check(lodgs.lib.lodgs_adam_step(p.data_ptr(), grad.data_ptr(), m.data_ptr(), v.data_ptr(), rel.data_ptr(), rel.numel(), None, rows,
+                                          width, 1.6e-4, 0.9, 0.999, 1e-15, 7, 1, lodgs.current_stream()))
+    torch.cuda.synchronize()
+    mask = torch.ones(rows, dtype=torch.bool, device=DEV)
+    mask[rel] = False
+    assert torch.equal(p[mask], p0[mask]) and torch.equal(m[mask], m0[mask]) and torch.equal(v[mask], v0[mask])  # untouched rows
+    assert torch.allclose(m, mr, rtol=1e-6, atol=0) and torch.allclose(v, vr, rtol=1e-6, atol=0)
+    assert torch.allclose(p, pr, rtol=2e-6, atol=1e-9)
+
+
+def test_adam_visibility_mask_no_bias_correction():
+    rows, width = 3000, 3
+    g = torch.Generator(device=DEV).manual_seed(5)
+    p, grad = torch.randn(rows, width, generator=g, device=DEV), torch.randn(rows, width, generator=g, device=DEV)
+    m, v = torch.zeros(rows, width, device=DEV), torch.zeros(rows, width, device=DEV)
+    vis = torch.rand(rows, generator=g, device=DEV) < 0.3
+    p0 = p.clone()
+    lodgs.check(lodgs.lib.lodgs_adam_step(p.data_ptr(), grad.data_ptr(), m.data_ptr(), v.data_ptr(), None, 0, vis.data_ptr(), rows, width,
+                                          1e-2, 0.9, 0.999, 1e-15, 1, 0, lodgs.current_stream()))
+    mm, vv = 0.1 * grad, 0.001 * grad * grad
+    want = p0 - 1e-2 * mm / (vv.sqrt() + 1e-15)
+    assert torch.equal(p[~vis], p0[~vis])
+    assert torch.allclose(p[vis], want[vis], rtol=1e-5, atol=1e-7)

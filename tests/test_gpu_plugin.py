@@ -1,0 +1,132 @@
+"""GPU: the Python drop-in surface — autograd through GaussianRasterizer, the render()/render_post() façade on a stand-in
+GaussianModel, per-frame hierarchical pipeline (cut -> weights -> in-kernel LOD render), smoke()."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+import cases
+from lodgs import synth
+
+pytestmark = pytest.mark.gpu
+
+
+class FakeCam:
+    def __init__(self, cam):
+        self.image_width, self.image_height = cam["W"], cam["H"]
+        self.FoVx, self.FoVy = 2 * math.atan(cam["tanfovx"]), 2 * math.atan(cam["tanfovy"])
+        self.world_view_transform = torch.from_numpy(cam["viewmatrix"]).cuda()
+        self.full_proj_transform = torch.from_numpy(cam["projmatrix"]).cuda()
+        self.camera_center = torch.from_numpy(cam["campos"]).cuda()
+        self.image_name = "x"
+
+
+class FakeModel:
+    """The getters of scene/gaussian_model.py that the façade touches."""
+    def __init__(self, sc):
+        t = {k: torch.from_numpy(v).cuda() for k, v in sc.items() if isinstance(v, np.ndarray)}
+        self._xyz = t["means3D"].requires_grad_(True)
+        self._opacity = torch.logit(t["opacities"].clamp(1e-4, 1 - 1e-4)).requires_grad_(True)
+        self._scaling = torch.log(t["scales"]).requires_grad_(True)
+        self._rotation = t["rotations"].clone().requires_grad_(True)
+        self._features = t["shs"].requires_grad_(True)
+        self.active_sh_degree, self.max_sh_degree, self.skybox_points = 3, 3, 0
+    get_xyz = property(lambda s: s._xyz)
+    get_opacity = property(lambda s: torch.sigmoid(s._opacity))
+    get_scaling = property(lambda s: torch.exp(s._scaling))
+    get_rotation = property(lambda s: torch.nn.functional.normalize(s._rotation))
+    get_features = property(lambda s: s._features)
+
+    def get_exposure_from_name(self, name):
+        return torch.eye(3, 4, device="cuda")
+
+
+class Pipe:
+    debug, compute_cov3D_python, convert_SHs_python = False, False, False
+
+
+def test_render_facade_and_autograd():
+    from gaussian_renderer import render
+    sc, cam, bg, _, _, _ = cases.make_case("small")
+    pc, vc = FakeModel(sc), FakeCam(cam)
+    out = render(vc, pc, Pipe(), torch.from_numpy(bg).cuda(), use_trained_exp=True)
+    img = out["render"]
+    assert img.shape == (3, cam["H"], cam["W"]) and out["depth"].shape == (1, cam["H"], cam["W"])
+    assert float(img.min()) >= 0 and float(img.max()) <= 1
+    loss = (img * torch.linspace(0, 1, img.numel(), device="cuda").view_as(img)).sum() + out["depth"].sum() * 0.1
+    loss.backward()
+    for p in (pc._xyz, pc._opacity, pc._scaling, pc._rotation, pc._features):
+        assert p.grad is not None and torch.isfinite(p.grad).all() and float(p.grad.abs().sum()) > 0
+    assert out["viewspace_points"].grad is not None
+    vis = out["visibility_filter"]
+    assert vis.dtype == torch.int64 and out["radii"].numel() == vis.numel()
+    # train_single.py:171-172: the sparse Adam rows are the Gaussians with a non-zero opacity gradient
+    relevant = (pc._opacity.grad.flatten() != 0).nonzero().flatten()
+    assert set(relevant.tolist()) <= set(vis.tolist())
+    # indices= path gathers a subset
+    idx = torch.arange(0, 600, 2, device="cuda")
+    out2 = render(vc, pc, Pipe(), torch.from_numpy(bg).cuda(), indices=idx)
+    assert out2["radii"].numel() <= idx.numel()
+
+
+def test_gradcheck_against_finite_differences():
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    sc, cam, bg, _, _, _ = cases.make_case("small")
+    t = {k: torch.from_numpy(v).cuda() for k, v in sc.items() if isinstance(v, np.ndarray)}
+    e_i, e_f = torch.empty(0, dtype=torch.int32, device="cuda"), torch.empty(0, device="cuda")
+    rs = GaussianRasterizationSettings(cam["H"], cam["W"], cam["tanfovx"], cam["tanfovy"], torch.from_numpy(bg).cuda(), 1.0,
+                                       torch.from_numpy(cam["viewmatrix"]).cuda(), torch.from_numpy(cam["projmatrix"]).cuda(), 3,
+                                       torch.from_numpy(cam["campos"]).cuda(), False, False, e_i, e_i, e_f, e_i, False)
+    w = torch.rand(3, cam["H"], cam["W"], device="cuda", generator=torch.Generator(device="cuda").manual_seed(0))
+
+    def loss(op):
+        c, _, _ = GaussianRasterizer(rs)(t["means3D"], torch.zeros_like(t["means3D"]), op, shs=t["shs"], scales=t["scales"],
+                                         rotations=t["rotations"])
+        return (c.double() * w).sum()
+    op = t["opacities"].clone().requires_grad_(True)
+    loss(op).backward()
+    g = op.grad.flatten()
+    for i in g.abs().topk(5).indices.tolist():
+        d = torch.zeros_like(op)
+        d[i] = 1e-3
+        fd = (loss(op.detach() + d) - loss(op.detach() - d)) / 2e-3
+        assert abs(float(fd) - float(g[i])) <= 2e-2 * abs(float(g[i])) + 1e-4
+
+
+def test_hierarchical_frame_in_kernel_lod_matches_python_interpolation():
+    """render_hierarchy.py:48-82: cut -> weights -> render_post; interp_python=False (kernel LOD) == interp_python=True."""
+    from gaussian_hierarchy import _C as gh
+    from gaussian_renderer import render_post
+    rng = np.random.default_rng(0)
+    L = 3000
+    pts = (rng.uniform(-1, 1, (L, 3)) * np.array([8.0, 5.0, 6.0]) + np.array([0, 0, 14.0])).astype(np.float32)
+    rad = np.exp(rng.normal(np.log(0.05), 0.4, L)).astype(np.float32)
+    nodes, boxes, gpos, grad = synth.build_hierarchy(pts, rad)
+    N = nodes.shape[0]
+    cam = synth.make_camera(W=320, H=192, fx=200.0, fy=200.0)
+    base = synth.make_gaussians(N, seed=2, tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"])
+    base["means3D"] = gpos
+    base["scales"] = np.repeat(grad[:, None], 3, 1).astype(np.float32)
+    pc, vc = FakeModel(base), FakeCam(cam)
+    n_t, b_t = torch.from_numpy(nodes).cuda(), torch.from_numpy(boxes).cuda()
+    tau = synth.tau_to_threshold(6.0, cam["tanfovx"], cam["W"])
+    ri, pi, ni = (torch.zeros(N, dtype=torch.int32, device="cuda") for _ in range(3))
+    K = gh.expand_to_size(n_t, b_t, tau, vc.camera_center, torch.zeros(3), ri, pi, ni)
+    assert 0 < K < N
+    ts, kids = torch.zeros(N, device="cuda"), torch.zeros(N, dtype=torch.int32, device="cuda")
+    gh.get_interpolation_weights(ni[:K], tau, n_t, b_t, vc.camera_center.cpu(), torch.zeros(3), ts, kids)
+    pi_safe = torch.where(pi[:K] < 0, ri[:K], pi[:K])  # the python path indexes with the parent; roots have t == 1
+    bg = torch.zeros(3, device="cuda")
+    with torch.no_grad():
+        a = render_post(vc, pc, Pipe(), bg, render_indices=ri[:K], parent_indices=pi_safe, interpolation_weights=ts[:K],
+                        num_node_siblings=kids[:K], interp_python=True)["render"]
+        b = render_post(vc, pc, Pipe(), bg, render_indices=ri[:K], parent_indices=pi[:K], interpolation_weights=ts[:K],
+                        num_node_siblings=kids[:K], interp_python=False)["render"]
+    assert float(a.max()) > 0.05
+    assert float((a - b).abs().max()) <= 2e-3  # torch's lerp rounds differently from the in-kernel one
+
+
+def test_smoke_entry():
+    import __graft_entry__ as ge
+    ge.smoke()

@@ -1,0 +1,166 @@
+"""GPU: rasterizer forward/backward through the plugin surface vs (1) golden outputs of the reference build, (2) the
+reference CUDA build run side by side, (3) the CPU oracle, plus size-independent properties at the full 1080p / 1 M size.
+Tolerances are BASELINE.json's: integers bit-exact, images <= 1e-4 max-abs, gradients <= 1e-3 relative L2."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import cases
+import minewrap
+from lodgs import synth
+from oracle import oracle as orc
+from oracle import refshim
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+INT_KEYS = ("radii", "tiles_touched", "point_offsets", "keys_unsorted", "vals_unsorted", "keys", "point_list", "ranges", "n_contrib", "seen")
+GRAD_KEYS = ("dL_dmean2D", "dL_dcolor", "dL_dopacity", "dL_dmean3D", "dL_dcov3D", "dL_dsh", "dL_dscale", "dL_drot")
+
+
+def rel_l2(a, b):
+    a, b = a.double().reshape(-1), b.double().reshape(-1)
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+def cu(d):
+    return {k: (torch.from_numpy(v).cuda() if isinstance(v, np.ndarray) else v) for k, v in d.items()}
+
+
+def run_mine(name):
+    sc, cam, bg, kw, dL, dLi = cases.make_case(name)
+    scg, camg, kwg, bgg = cu(sc), cu(cam), cu(kw), torch.from_numpy(bg).cuda()
+    f = minewrap.forward(scg, camg, bgg, **kwg)
+    g = minewrap.backward(scg, camg, bgg, f, torch.from_numpy(dL).cuda(), torch.from_numpy(dLi).cuda(), **kwg)
+    return f, g
+
+
+@pytest.mark.parametrize("name", list(cases.CASES))
+def test_against_golden_reference_outputs(name):
+    gold = np.load(os.path.join(GOLD, "raster_%s.npz" % name))
+    f, g = run_mine(name)
+    assert f["R"] == int(gold["R"])
+    for k in INT_KEYS:
+        assert np.array_equal(f[k].cpu().numpy().astype(np.int64), gold[k].astype(np.int64)), k
+    vis = gold["radii"] > 0
+    assert np.array_equal(f["rects"].cpu().numpy()[vis], gold["rects"][vis])
+    assert np.array_equal(f["depths"].cpu().numpy()[vis].view(np.uint32), gold["depths"][vis].view(np.uint32))
+    assert np.array_equal(f["means2D"].cpu().numpy()[vis].view(np.uint32), gold["means2D"][vis].view(np.uint32))
+    assert np.abs(f["color"].cpu().numpy() - gold["color"]).max() <= 1e-4
+    assert np.abs(f["invdepth"].cpu().numpy() - gold["invdepth"]).max() <= 1e-4
+    for k in GRAD_KEYS:
+        if name == "lod" and k == "dL_dmean3D":
+            continue  # racy + uninitialised clamp flags in the reference; checked against the oracle below
+        assert rel_l2(g[k], torch.from_numpy(gold[k]).cuda()) <= 1e-3, k
+
+
+@pytest.mark.parametrize("name", ["small", "lod"])
+def test_against_cpu_oracle(name):
+    sc, cam, bg, kw, dL, dLi = cases.make_case(name)
+    f, g = run_mine(name)
+    o = orc.forward(sc, cam, bg, want_state=True, **kw)
+    og = orc.backward(o, dL, dLi)
+    orc.free(o)
+    assert f["R"] == o["R"]
+    assert np.array_equal(f["keys"].cpu().numpy(), o["keys"].view(np.int64))
+    assert np.array_equal(f["point_list"].cpu().numpy(), o["point_list"].astype(np.int32))
+    assert np.abs(f["color"].cpu().numpy() - o["color"]).max() <= 1e-4
+    for k in GRAD_KEYS:
+        assert rel_l2(g[k], torch.from_numpy(og[k]).cuda()) <= 1e-3, k  # includes the LOD parent redirect of dL_dmean3D
+
+
+@pytest.mark.skipif(not refshim.available(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("P,W,H,lod", [(50000, 640, 360, False), (30000, 500, 300, True), (200000, 1280, 720, False)])
+def test_side_by_side_with_reference_build(P, W, H, lod):
+    cam_np = synth.make_camera(W=W, H=H, fx=1200.0 * W / 1920, fy=1200.0 * W / 1920)
+    sc = cu(synth.make_gaussians(P, seed=P % 97, tanfovx=cam_np["tanfovx"], tanfovy=cam_np["tanfovy"]))
+    cam, bg = cu(cam_np), torch.tensor([0.3, 0.1, 0.0], device="cuda")
+    kw = {}
+    if lod:
+        g = torch.Generator().manual_seed(3)
+        K = P // 2
+        par = torch.randint(0, P, (K,), generator=g).int()
+        par[torch.rand(K, generator=g) < 0.25] = -1
+        kw = {"indices": torch.randperm(P, generator=g)[:K].sort().values.int().cuda(), "parent_indices": par.cuda(),
+              "ts": torch.rand(K, generator=g).cuda(), "kids": torch.randint(1, 6, (K,), generator=g).int().cuda()}
+    m = minewrap.forward(sc, cam, bg, **kw)
+    r = refshim.forward(sc, cam, bg, **kw)
+    assert m["R"] == r["R"]
+    bad = sum(int((m[k].long() != r[k].long()).sum()) for k in INT_KEYS)
+    # FMA contraction inside the 3D covariance differs from nvcc's choice for the reference in ~1e-6 of the entries
+    # (profiles/r1_parity_diag_first.log); everything downstream of an identical radius is identical.
+    assert bad <= max(2, int(3e-6 * P * 12)), bad
+    assert float((m["color"] - r["color"]).abs().max()) <= 1e-4
+    assert float((m["invdepth"] - r["invdepth"]).abs().max()) <= 1e-4
+    torch.manual_seed(0)
+    dL = (torch.rand(3, H, W, device="cuda") - 0.5) / (H * W)
+    dLi = (torch.rand(1, H, W, device="cuda") - 0.5) / (H * W)
+    gm = minewrap.backward(sc, cam, bg, m, dL, dLi, **kw)
+    gr = refshim.backward(sc, cam, bg, r, dL, dLi, **kw)
+    for k in GRAD_KEYS:
+        if lod and k == "dL_dmean3D":
+            continue
+        assert rel_l2(gm[k], gr[k]) <= 1e-3, k
+
+
+def test_full_size_properties():
+    """1 M Gaussians at 1080p (BASELINE configs[1]): size-independent invariants of every stage."""
+    cam_np = synth.make_camera()
+    sc = cu(synth.make_gaussians(1_000_000, seed=0, tanfovx=cam_np["tanfovx"], tanfovy=cam_np["tanfovy"]))
+    cam, bg = cu(cam_np), torch.zeros(3, device="cuda")
+    f = minewrap.forward(sc, cam, bg)
+    R, P = f["R"], f["P"]
+    tt, po = f["tiles_touched"].long(), f["point_offsets"].long()
+    assert torch.equal(po, torch.cumsum(tt, 0)) and int(po[-1]) == R            # fused scan == prefix sum
+    assert ((f["radii"] > 0) == (tt > 0)).all()
+    ku, ks, pl = f["keys_unsorted"], f["keys"], f["point_list"].long()
+    assert (ks[1:] >= ks[:-1]).all()                                             # sorted
+    want_k, order = torch.sort(ku, stable=True)
+    assert torch.equal(ks, want_k) and torch.equal(pl, f["vals_unsorted"].long()[order])  # identical to a stable (CUB) sort
+    tiles = (ks >> 32)
+    counts = torch.bincount(tiles, minlength=f["ranges"].size(0))
+    rng = f["ranges"].long()
+    assert torch.equal(rng[:, 1] - rng[:, 0], counts)                            # ranges partition the list by tile
+    depth_bits = (ks & 0xffffffff).int().view(torch.float32) if False else None
+    assert torch.equal((ks & 0xffffffff).int(), f["depths"][pl].view(torch.int32))  # key depth == depth of its Gaussian
+    assert (f["n_contrib"].long().view(-1) <= 0x7fffffff).all()
+    color = f["color"]
+    assert torch.isfinite(color).all() and float(color.min()) >= 0.0
+    T = f["final_T"]
+    assert float(T.min()) >= 0.0 and float(T.max()) <= 1.0
+    # idempotence: a second forward on the same inputs gives bit-identical integer state and image
+    f2 = minewrap.forward(sc, cam, bg)
+    assert torch.equal(f2["keys"], ks) and torch.equal(f2["n_contrib"], f["n_contrib"]) and torch.equal(f2["color"], color)
+    # linearity of the backward in dL_dpixels
+    dL = torch.rand(3, cam["H"], cam["W"], device="cuda") / color.numel()
+    z = torch.zeros(1, cam["H"], cam["W"], device="cuda")
+    g1 = minewrap.backward(sc, cam, bg, f, dL, z)
+    g2 = minewrap.backward(sc, cam, bg, f, 2.0 * dL, z)
+    for k in ("dL_dmean3D", "dL_dsh", "dL_dopacity", "dL_dscale", "dL_drot"):
+        assert rel_l2(g2[k], 2.0 * g1[k]) <= 1e-5, k
+    vis = f["radii"] > 0
+    assert float(g1["dL_dsh"][~vis].abs().max()) == 0.0                          # culled Gaussians get no gradient
+
+
+def test_empty_and_degenerate_inputs():
+    cam_np = synth.make_camera(W=64, H=48, fx=40.0, fy=40.0)
+    cam, bg = cu(cam_np), torch.tensor([0.5, 0.25, 0.125], device="cuda")
+    sc = cu(synth.make_gaussians(16, seed=1, tanfovx=cam_np["tanfovx"], tanfovy=cam_np["tanfovy"]))
+    behind = dict(sc)
+    behind["means3D"] = sc["means3D"].clone()
+    behind["means3D"][:, 2] = -5.0                      # everything behind the camera: R == 0
+    f = minewrap.forward(behind, cam, bg)
+    assert f["R"] == 0 and int(f["radii"].abs().sum()) == 0
+    assert float(f["color"].abs().max()) == 0.0         # reference returns before rendering (rasterizer_impl.cu:332-333)
+    g = minewrap.backward(behind, cam, bg, f, torch.ones(3, 48, 64, device="cuda"), None)
+    assert all(float(v.abs().max()) == 0.0 for v in g.values())
+    empty = {k: (v[:0] if torch.is_tensor(v) else v) for k, v in sc.items()}
+    f0 = minewrap.forward(empty, cam, bg)
+    assert f0["R"] == 0 and f0["radii"].numel() == 0
+    one = {k: (v[:1].clone() if torch.is_tensor(v) else v) for k, v in sc.items()}
+    one["means3D"][0] = torch.tensor([0.0, 0.0, 3.0])
+    one["scales"][0] = 1e-4                             # a single instance: the reference's range quirk keeps it unrendered
+    f1 = minewrap.forward(one, cam, bg)
+    if f1["R"] == 1:
+        assert int(f1["ranges"][:, 1].sum()) == 0

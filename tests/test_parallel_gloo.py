@@ -1,0 +1,57 @@
+"""CPU, world_size 2 over gloo: the host-side multi-GPU logic (camera sharding, gradient bucket all-reduce)."""
+import os
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from lodgs import parallel
+
+
+def test_shard_range_partitions_exactly():
+    for n in (0, 1, 7, 1000, 1001):
+        for world in (1, 2, 3, 8):
+            cover = []
+            for r in range(world):
+                lo, hi = parallel.shard_range(n, r, world)
+                cover += list(range(lo, hi))
+                assert hi - lo in (n // world, n // world + 1)
+            assert cover == list(range(n))
+
+
+def _worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    g = torch.Generator().manual_seed(100 + rank)
+    grads = [torch.randn(50, 3, generator=g), None, torch.randn(50, 16, 3, generator=g), torch.randn(50, 1, generator=g)]
+    want = None
+    nbytes = parallel.allreduce_gradients(grads)
+    lo, hi = parallel.shard_range(11, rank, world)
+    t = parallel.gather_timings(torch.arange(lo, hi, dtype=torch.float64))
+    q.put((rank, [None if x is None else x.clone() for x in grads], nbytes, [x.tolist() for x in t]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_gradient_allreduce_two_ranks():
+    world, port = 2, 29513
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in range(world)], key=lambda x: x[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    exp = []
+    for r in range(world):
+        g = torch.Generator().manual_seed(100 + r)
+        exp.append([torch.randn(50, 3, generator=g), torch.randn(50, 16, 3, generator=g), torch.randn(50, 1, generator=g)])
+    sums = [exp[0][i] + exp[1][i] for i in range(3)]
+    for rank, grads, nbytes, timings in res:
+        got = [x for x in grads if x is not None]
+        assert nbytes == 4 * (150 + 2400 + 50)
+        for a, b in zip(got, sums):
+            assert torch.allclose(a, b, atol=0, rtol=0)
+        assert timings == [[0.0, 1.0, 2.0, 3.0, 4.0, 5.0], [6.0, 7.0, 8.0, 9.0, 10.0]]
