@@ -46,51 +46,88 @@ __device__ __forceinline__ mat3 quat_to_mat(float r, float x, float y, float z) 
                 2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
 }
 
-// Sigma = (S R)^T (S R), upper triangle (forward.cu:181-215).
-__device__ __forceinline__ void cov3d_from_scale_rot(float sx, float sy, float sz, float mod, float4 q, float* cov6) {
-    mat3 S(1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f, 1.0f);
-    S[0][0] = mod * sx;
-    S[1][1] = mod * sy;
-    S[2][2] = mod * sz;
-    mat3 R = quat_to_mat(q.x, q.y, q.z, q.w);
-    mat3 M = mul(S, R);
-    mat3 Sigma = mul(transpose(M), M);
-    cov6[0] = Sigma[0][0];
-    cov6[1] = Sigma[0][1];
-    cov6[2] = Sigma[0][2];
-    cov6[3] = Sigma[1][1];
-    cov6[4] = Sigma[1][2];
-    cov6[5] = Sigma[2][2];
+// Explicitly rounded FP32 ops: the per-Gaussian chain below decides integer outputs (radii, rects, tile counts), so the
+// placement of every fused multiply-add is pinned with intrinsics instead of being left to the compiler's
+// contraction heuristics. The placement is the one nvcc 12.9 chooses for the reference's glm expressions
+// (HR/cuda_rasterizer/forward.cu:141-215, checked with tools/ptx_expr.py against the sm_100a PTX of the reference
+// build), which is what makes these outputs bit-identical to oracle/_ref.
+#define FM(a, b) __fmul_rn((a), (b))
+#define FA(a, b) __fadd_rn((a), (b))
+#define FS(a, b) __fsub_rn((a), (b))
+#define FF(a, b, c) __fmaf_rn((a), (b), (c))
+
+// Sigma = (S R)^T (S R), upper triangle (forward.cu:181-215). q = (r,x,y,z), not normalised (forward.cu:190).
+__device__ __forceinline__ void cov3d_from_scale_rot(float s0, float s1, float s2, float mod, float4 q, float* cov6) {
+    const float r = q.x, x = q.y, y = q.z, z = q.w;
+    const float sx = FM(mod, s0), sy = FM(mod, s1), sz = FM(mod, s2);
+    const float yy = FM(y, y), zz = FM(z, z);
+    const float xy = FM(x, y), rz = FM(r, z), xz = FM(x, z), ry = FM(r, y), yz = FM(y, z), rx = FM(r, x);
+    const float a00 = FA(yy, zz), a11 = FF(x, x, zz), a22 = FF(x, x, yy);
+    const float b01 = FS(xy, rz), b02 = FA(ry, xz), b10 = FA(xy, rz), b12 = FS(yz, rx), b20 = FS(xz, ry), b21 = FA(rx, yz);
+    const float R00 = FS(1.0f, FA(a00, a00)), R01 = FA(b01, b01), R02 = FA(b02, b02);
+    const float R10 = FA(b10, b10), R11 = FS(1.0f, FA(a11, a11)), R12 = FA(b12, b12);
+    const float R20 = FA(b20, b20), R21 = FA(b21, b21), R22 = FS(1.0f, FA(a22, a22));
+    // M = S * R with S = diag(sx,sy,sz); the products with S's literal zeros stay (they are not foldable under IEEE rules)
+    const float z0 = FM(R00, 0.0f), z1 = FM(R11, 0.0f), z2 = FM(R21, 0.0f);
+    const float M00 = FF(R02, 0.0f, FF(R01, 0.0f, FM(sx, R00)));
+    const float M01 = FF(R02, 0.0f, FF(sy, R01, z0));
+    const float M02 = FF(R02, sz, FF(R01, 0.0f, z0));
+    const float M10 = FF(R12, 0.0f, FF(sx, R10, z1));
+    const float M11 = FF(R12, 0.0f, FF(R10, 0.0f, FM(sy, R11)));
+    const float M12 = FF(R12, sz, FF(R10, 0.0f, z1));
+    const float M20 = FF(R22, 0.0f, FF(sx, R20, z2));
+    const float M21 = FF(R22, 0.0f, FF(R20, 0.0f, FM(sy, R21)));
+    const float M22 = FF(R22, sz, FF(R20, 0.0f, z2));
+    cov6[0] = FF(M02, M02, FF(M00, M00, FM(M01, M01)));
+    cov6[1] = FF(M12, M02, FF(M10, M00, FM(M11, M01)));
+    cov6[2] = FF(M22, M02, FF(M20, M00, FM(M21, M01)));
+    cov6[3] = FF(M12, M12, FF(M10, M10, FM(M11, M11)));
+    cov6[4] = FF(M22, M12, FF(M20, M10, FM(M21, M11)));
+    cov6[5] = FF(M22, M22, FF(M20, M20, FM(M21, M21)));
 }
 
 struct Cov2DCtx {
     float3 t;       // view-space mean with the 1.3*fov clamp applied to x,y
     float txtz, tytz;
-    mat3 T;         // W * J
+    mat3 T;         // W * J (third column is zero and never read)
 };
 
 // EWA projection of the 3D covariance (forward.cu:141-176). Returns (cov[0][0], cov[0][1], cov[1][1]).
 __device__ __forceinline__ float3 project_cov(const float3 mean, float fx, float fy, float tan_fovx, float tan_fovy,
                                               const float* cov6, const float* view, Cov2DCtx* ctx) {
-    float3 t = xform4x3(mean, view);
-    const float limx = 1.3f * tan_fovx;
-    const float limy = 1.3f * tan_fovy;
-    const float txtz = t.x / t.z;
-    const float tytz = t.y / t.z;
-    t.x = min(limx, max(-limx, txtz)) * t.z;
-    t.y = min(limy, max(-limy, tytz)) * t.z;
-    mat3 J(fx / t.z, 0.0f, -(fx * t.x) / (t.z * t.z), 0.0f, fy / t.z, -(fy * t.y) / (t.z * t.z), 0, 0, 0);
-    mat3 Wm(view[0], view[4], view[8], view[1], view[5], view[9], view[2], view[6], view[10]);
-    mat3 T = mul(Wm, J);
-    mat3 Vrk(cov6[0], cov6[1], cov6[2], cov6[1], cov6[3], cov6[4], cov6[2], cov6[4], cov6[5]);
-    mat3 cov = mul(mul(transpose(T), transpose(Vrk)), T);
+    const float v0 = view[0], v1 = view[1], v2 = view[2], v4 = view[4], v5 = view[5], v6 = view[6], v8 = view[8], v9 = view[9],
+                v10 = view[10];
+    const float tx = FA(view[12], FF(mean.z, v8, FF(mean.x, v0, FM(mean.y, v4))));
+    const float ty = FA(view[13], FF(mean.z, v9, FF(mean.x, v1, FM(mean.y, v5))));
+    const float tz = FA(view[14], FF(mean.z, v10, FF(mean.x, v2, FM(mean.y, v6))));
+    const float limx = FM(tan_fovx, 1.3f), limy = FM(tan_fovy, 1.3f);
+    const float txtz = __fdiv_rn(tx, tz), tytz = __fdiv_rn(ty, tz);
+    const float cx = fminf(limx, fmaxf(-limx, txtz)), cy = fminf(limy, fmaxf(-limy, tytz));
+    const float ntz = -tz, tz2 = FM(tz, tz);
+    const float J00 = __fdiv_rn(fx, tz), J02 = __fdiv_rn(FM(fx, FM(cx, ntz)), tz2);
+    const float J11 = __fdiv_rn(fy, tz), J12 = __fdiv_rn(FM(fy, FM(cy, ntz)), tz2);
+    // T = W * J, W = view rotation (glm columns (v0,v4,v8) (v1,v5,v9) (v2,v6,v10)), J = ((J00,0,J02),(0,J11,J12),0)
+    const float T00 = FF(v2, J02, FF(v0, J00, FM(v1, 0.0f)));
+    const float T01 = FF(v6, J02, FF(v4, J00, FM(v5, 0.0f)));
+    const float T02 = FF(J02, v10, FF(v8, J00, FM(v9, 0.0f)));
+    const float T10 = FF(v2, J12, FF(v0, 0.0f, FM(J11, v1)));
+    const float T11 = FF(v6, J12, FF(v4, 0.0f, FM(J11, v5)));
+    const float T12 = FF(J12, v10, FF(v8, 0.0f, FM(J11, v9)));
+    const float c0 = cov6[0], c1 = cov6[1], c2 = cov6[2], c3 = cov6[3], c4 = cov6[4], c5 = cov6[5];
+    // A = T^T * Vrk^T, cov = A * T
+    const float A00 = FF(T02, c2, FF(T00, c0, FM(T01, c1))), A01 = FF(T12, c2, FF(T10, c0, FM(T11, c1)));
+    const float A10 = FF(T02, c4, FF(T00, c1, FM(T01, c3))), A11 = FF(T12, c4, FF(T10, c1, FM(T11, c3)));
+    const float A20 = FF(T02, c5, FF(T00, c2, FM(T01, c4))), A21 = FF(T12, c5, FF(T10, c2, FM(T11, c4)));
+    const float cov00 = FF(T02, A20, FF(T00, A00, FM(T01, A10)));
+    const float cov01 = FF(T02, A21, FF(T00, A01, FM(T01, A11)));
+    const float cov11 = FF(T12, A21, FF(T10, A01, FM(T11, A11)));
     if (ctx) {
-        ctx->t = t;
+        ctx->t = {FM(cx, tz), FM(cy, tz), tz};
         ctx->txtz = txtz;
         ctx->tytz = tytz;
-        ctx->T = T;
+        ctx->T = mat3(T00, T01, T02, T10, T11, T12, 0.f, 0.f, 0.f);
     }
-    return {cov[0][0], cov[0][1], cov[1][1]};
+    return {cov00, cov01, cov11};
 }
 
 // SH -> RGB for coefficients already in registers (sh[k] = k-th coefficient, RGB triple), direction `d`

@@ -127,24 +127,27 @@ __device__ __forceinline__ uint32_t preprocess_one(const PreParams& p, const Geo
 
     float3 cov = project_cov(p_orig, p.focal_x, p.focal_y, p.tan_fovx, p.tan_fovy, cov6, view, nullptr);
 
+    // (forward.cu:362-392) same pinned rounding as gaussmath.cuh: no contraction in the determinants
     constexpr float h_var = 0.3f;
-    const float det_cov = cov.x * cov.z - cov.y * cov.y;
-    cov.x += h_var;
-    cov.z += h_var;
-    const float det_cov_plus_h_cov = cov.x * cov.z - cov.y * cov.y;
-    const float h_convolution_scaling = sqrtf(max(0.000025f, det_cov / det_cov_plus_h_cov));
+    const float cov01sq = FM(cov.y, cov.y);
+    const float det_cov = FS(FM(cov.x, cov.z), cov01sq);
+    cov.x = FA(cov.x, h_var);
+    cov.z = FA(cov.z, h_var);
+    const float det_cov_plus_h_cov = FS(FM(cov.x, cov.z), cov01sq);
+    const float h_convolution_scaling = __fsqrt_rn(fmaxf(__fdiv_rn(det_cov, det_cov_plus_h_cov), 0.000025f));
     const float det = det_cov_plus_h_cov;
     if (det == 0.0f) return 0;
-    float det_inv = 1.f / det;
-    float3 conic = {cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv};
+    const float det_inv = __frcp_rn(det);
+    const float3 conic = {FM(cov.z, det_inv), FM(det_inv, -cov.y), FM(cov.x, det_inv)};
 
-    float mid = 0.5f * (cov.x + cov.z);
-    float lambda1 = mid + sqrtf(max(0.1f, mid * mid - det));
-    float lambda2 = mid - sqrtf(max(0.1f, mid * mid - det));
-    float my_radius = ceilf(3.f * sqrtf(max(lambda1, lambda2)));
+    const float mid = FM(FA(cov.x, cov.z), 0.5f);
+    const float disc = __fsqrt_rn(fmaxf(FS(FM(mid, mid), det), 0.1f));
+    const float lambda1 = FA(mid, disc);
+    const float lambda2 = FS(mid, disc);
+    const float my_radius = ceilf(FM(__fsqrt_rn(fmaxf(lambda1, lambda2)), 3.f));
     float2 point_image = {ndc_to_pix(p_proj.x, p.W), ndc_to_pix(p_proj.y, p.H)};
     uint2 rmin, rmax;
-    const int2 my_rect = {(int)ceilf(3.f * sqrtf(cov.x)), (int)ceilf(3.f * sqrtf(cov.z))};
+    const int2 my_rect = {(int)ceilf(FM(__fsqrt_rn(cov.x), 3.f)), (int)ceilf(FM(__fsqrt_rn(cov.z), 3.f))};
     g.rects[t_idx] = my_rect;
     tile_rect(point_image, my_rect, rmin, rmax, p.grid_x, p.grid_y);
     if ((rmax.x - rmin.x) * (rmax.y - rmin.y) == 0) return 0;
@@ -171,7 +174,7 @@ __device__ __forceinline__ uint32_t preprocess_one(const PreParams& p, const Geo
     g.means2D[t_idx] = point_image;
     float opacity = __ldg(p.opacities + r_idx);
     if (has_parent) opacity = t * opacity + (1.0f - t) * __ldg(p.opacities + p_idx);
-    g.conic_opacity[t_idx] = {conic.x, conic.y, conic.z, opacity * h_convolution_scaling};
+    g.conic_opacity[t_idx] = {conic.x, conic.y, conic.z, FM(h_convolution_scaling, opacity)};
     return (rmax.y - rmin.y) * (rmax.x - rmin.x);
 }
 

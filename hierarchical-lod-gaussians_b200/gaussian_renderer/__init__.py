@@ -121,8 +121,9 @@ def render_post(viewpoint_camera, gaussians, pipe, bg_color: torch.Tensor, scali
         interpolation_weights = torch.cat((ones_f, interpolation_weights[:n].detach().float()))
         num_node_siblings = torch.cat((ones_i, num_node_siblings[:n].int()))
         render_indices = parent_indices = _empty(torch.int32)
-        # with the interpolation done here the kernel must not lerp again, but it still needs t and kids for the alpha
-        lod_ts, lod_kids = interpolation_weights.contiguous(), num_node_siblings.contiguous()
+        # as the reference (GR:348-350): indices and weights are cleared, only num_node_kids reaches the kernel, whose
+        # LOD alpha blend is therefore off (ts == nullptr, forward.cu:505)
+        lod_ts, lod_kids = _empty(torch.float32), num_node_siblings.contiguous()
     elif n != 0:
         render_indices = render_indices[:n].int().contiguous()
         parent_indices = parent_indices[:n].int().contiguous()
