@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(256) build_records_kernel(int R, int P, const 
     const float4 co = __ldg(conic_opacity + id);
     float4 a = {xy.x, xy.y, co.x, co.y};
     float4 b = {co.z, co.w, __ldg(colors + 3 * (size_t)id), __ldg(colors + 3 * (size_t)id + 1)};
-    float4 c = {__ldg(colors + 3 * (size_t)id + 2), __ldg(depths + id), 1.0f, 1.0f};
+    float4 c = {__ldg(colors + 3 * (size_t)id + 2), __frcp_rn(__ldg(depths + id)), 1.0f, 1.0f};  // rcp.rn == the reference's 1/depth per pair
     if (ts != nullptr && kids != nullptr) {
         c.z = __ldg(ts + id);
         c.w = 1.0f / (float)__ldg(kids + id);

@@ -12,7 +12,8 @@
 
 namespace lodgs {
 
-constexpr int BWD_BATCH = 256;
+constexpr int BWD_BATCH = 128;
+constexpr int BWD_THREADS = 128;  // 16 x 8 threads, two vertically adjacent pixels each (a warp covers a 16x4 block)
 constexpr int NV = 10;  // dmean.x dmean.y dconic.xx dconic.xy dconic.yy dopacity dcol.r dcol.g dcol.b dinvdepth
 
 struct BwdSmem {
@@ -20,7 +21,19 @@ struct BwdSmem {
     float acc[2][BWD_BATCH * NV];
     uint32_t ids[2][BWD_BATCH + 8];
     uint64_t bar[2];
-    unsigned warp_max[TILE_PIX / 32];
+    unsigned warp_max[BWD_THREADS / 32];
+};
+
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+// Per-pixel replay state of the back-to-front pass.
+struct BwdPix {
+    float px, py, T, T_final, last_alpha, lc0, lc1, lc2, ar0, ar1, ar2, last_invd, ar_invd, g0, g1, g2, gd, bg_dot;
+    unsigned last_contributor;
 };
 
 // Sum v[0..9] over the warp. On return lanes with even lane id and a valid slot hold the total of value
@@ -60,42 +73,115 @@ __device__ __forceinline__ float warp_reduce10(const float (&v)[NV], unsigned la
     return t[0];
 }
 
+// One (pixel, splat) pair of the replay (backward.cu:600-716); adds this pixel's ten partial gradients to v.
 template <bool LOD, bool DEPTH>
-__global__ void __launch_bounds__(TILE_PIX) blend_bwd_kernel(const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
-                                                            const uint32_t* __restrict__ point_list, int W, int H,
-                                                            const float* __restrict__ bg_color, const int32_t* __restrict__ indices,
-                                                            const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
-                                                            const float* __restrict__ dL_dpixels, const float* __restrict__ dL_invdepths,
-                                                            float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic2D,
-                                                            float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolors,
-                                                            float* __restrict__ dL_dinvdepths) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
-    const unsigned tid = threadIdx.y * TILE_X + threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const unsigned horizontal_blocks = (W + TILE_X - 1) / TILE_X;
-    const uint2 pix = {blockIdx.x * TILE_X + threadIdx.x, blockIdx.y * TILE_Y + threadIdx.y};
-    const uint32_t pix_id = W * pix.y + pix.x;
-    const float2 pixf = {(float)pix.x, (float)pix.y};
-    const bool inside = pix.x < (unsigned)W && pix.y < (unsigned)H;
-    const uint2 range = ranges[blockIdx.y * horizontal_blocks + blockIdx.x];
+__device__ __forceinline__ bool bwd_pair(BwdPix& p, const float4 q0, const float4 q1, const float4 q2, float ddelx_dx, float ddely_dy,
+                                         float (&v)[NV]) {
+    const float dx = __fsub_rn(q0.x, p.px), dy = __fsub_rn(q0.y, p.py);
+    const float quad = __fmaf_rn(dx, __fmul_rn(dx, q0.z), __fmul_rn(dy, __fmul_rn(dy, q1.x)));
+    const float power = __fsub_rn(__fmul_rn(quad, -0.5f), __fmul_rn(dy, __fmul_rn(dx, q0.w)));
+    if (power > 0.0f) return false;
+    const float G = expf(power);  // same expf as the forward: the contributor set is decided by identical alphas
+    const float test_alpha = __fmul_rn(q1.y, G);
+    const bool nullalpha = test_alpha > 0.99f;
+    const float my_alpha = fminf(0.99f, test_alpha);
+    float alpha = my_alpha, t = 1.f, frac = 1.f;
+    if (LOD) {
+        t = q2.z;
+        frac = q2.w;
+        const float kidsqrt_alpha = __fsub_rn(1.0f, __powf(__fsub_rn(1.0f, my_alpha), frac));
+        alpha = __fmaf_rn(my_alpha, t, __fmul_rn(__fsub_rn(1.0f, t), kidsqrt_alpha));
+    }
+    if (alpha < 1.0f / 255.0f) return false;
+    const float rcp1ma = rcp_approx(1.f - alpha);  // 1-alpha in [0.01,1]: one MUFU instead of two IEEE divides per pair
+    p.T *= rcp1ma;
+    const float weight = alpha * p.T;
+    const float oml = 1.f - p.last_alpha;
+    p.ar0 = p.last_alpha * p.lc0 + oml * p.ar0;
+    p.ar1 = p.last_alpha * p.lc1 + oml * p.ar1;
+    p.ar2 = p.last_alpha * p.lc2 + oml * p.ar2;
+    p.lc0 = q1.z; p.lc1 = q1.w; p.lc2 = q2.x;
+    float dL_dalpha = (q1.z - p.ar0) * p.g0 + (q1.w - p.ar1) * p.g1 + (q2.x - p.ar2) * p.g2;
+    v[6] += weight * p.g0;
+    v[7] += weight * p.g1;
+    v[8] += weight * p.g2;
+    if (DEPTH) {
+        p.ar_invd = p.last_alpha * p.last_invd + oml * p.ar_invd;
+        p.last_invd = q2.y;
+        dL_dalpha += (q2.y - p.ar_invd) * p.gd;
+        v[9] += weight * p.gd;
+    }
+    dL_dalpha *= p.T;
+    p.last_alpha = alpha;
+    dL_dalpha -= p.T_final * rcp1ma * p.bg_dot;
+    dL_dalpha = nullalpha ? 0.f : dL_dalpha;
+    const float dL_dG = q1.y * dL_dalpha;
+    const float gdx = G * dx, gdy = G * dy;
+    const float dG_ddelx = -gdx * q0.z - gdy * q0.w;
+    const float dG_ddely = -gdy * q1.x - gdx * q0.w;
+    v[0] += dL_dG * dG_ddelx * ddelx_dx;
+    v[1] += dL_dG * dG_ddely * ddely_dy;
+    v[2] += -0.5f * gdx * dx * dL_dG;
+    v[3] += -0.5f * gdx * dy * dL_dG;
+    v[4] += -0.5f * gdy * dy * dL_dG;
+    float opac_grad_mult = 1.0f;
+    if (LOD) opac_grad_mult = t - __powf(1.0f - my_alpha, frac - 1.0f) * (t - 1.0f) * frac;
+    v[5] += opac_grad_mult * G * dL_dalpha;
+    return true;
+}
 
-    const float T_final = inside ? final_Ts[pix_id] : 0;
-    float T = T_final;
-    const unsigned last_contributor = inside ? n_contrib[pix_id] : 0;
+template <bool LOD, bool DEPTH>
+__global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
+                                                               const uint32_t* __restrict__ point_list, int W, int H,
+                                                               const float* __restrict__ bg_color, const int32_t* __restrict__ indices,
+                                                               const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
+                                                               const float* __restrict__ dL_dpixels, const float* __restrict__ dL_invdepths,
+                                                               float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic2D,
+                                                               float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolors,
+                                                               float* __restrict__ dL_dinvdepths) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
+    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, tx = tid & 15u, ty = tid >> 4;
+    const unsigned horizontal_blocks = (W + TILE_X - 1) / TILE_X;
+    const unsigned pix_x = blockIdx.x * TILE_X + tx, pix_y0 = blockIdx.y * TILE_Y + 2u * ty;
+    const uint2 range = ranges[blockIdx.y * horizontal_blocks + blockIdx.x];
+    const size_t HW = (size_t)H * W;
+    const float bg0 = bg_color[0], bg1 = bg_color[1], bg2 = bg_color[2];
+
+    BwdPix px[2];
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        BwdPix& p = px[h];
+        const unsigned y = pix_y0 + h;
+        const bool inside = pix_x < (unsigned)W && y < (unsigned)H;
+        const uint32_t pix_id = W * y + pix_x;
+        p.px = (float)pix_x;
+        p.py = (float)y;
+        p.T_final = inside ? final_Ts[pix_id] : 0.f;
+        p.T = p.T_final;
+        p.last_contributor = inside ? n_contrib[pix_id] : 0u;
+        p.last_alpha = 0.f;
+        p.lc0 = p.lc1 = p.lc2 = p.ar0 = p.ar1 = p.ar2 = p.last_invd = p.ar_invd = 0.f;
+        p.g0 = inside ? dL_dpixels[0 * HW + pix_id] : 0.f;
+        p.g1 = inside ? dL_dpixels[1 * HW + pix_id] : 0.f;
+        p.g2 = inside ? dL_dpixels[2 * HW + pix_id] : 0.f;
+        p.gd = (DEPTH && inside) ? dL_invdepths[pix_id] : 0.f;
+        p.bg_dot = bg0 * p.g0 + bg1 * p.g1 + bg2 * p.g2;
+    }
 
     // the replay only has to cover splats up to the tile's deepest contributor
-    const unsigned wmax = __reduce_max_sync(0xffffffffu, last_contributor);
+    const unsigned wmax = __reduce_max_sync(0xffffffffu, max(px[0].last_contributor, px[1].last_contributor));
     if (lane == 0) sm.warp_max[warp] = wmax;
     if (tid == 0) {
         mbar_init(&sm.bar[0], 1);
         mbar_init(&sm.bar[1], 1);
         mbar_fence_init();
     }
-    for (int i = tid; i < 2 * BWD_BATCH * NV; i += TILE_PIX) (&sm.acc[0][0])[i] = 0.f;
+    for (int i = tid; i < 2 * BWD_BATCH * NV; i += BWD_THREADS) (&sm.acc[0][0])[i] = 0.f;
     __syncthreads();
     unsigned L = 0;
 #pragma unroll
-    for (int w = 0; w < TILE_PIX / 32; w++) L = max(L, sm.warp_max[w]);
+    for (int w = 0; w < BWD_THREADS / 32; w++) L = max(L, sm.warp_max[w]);
     L = min(L, range.y - range.x);
     const int rounds = (int)((L + BWD_BATCH - 1) / BWD_BATCH);
 
@@ -115,24 +201,8 @@ __global__ void __launch_bounds__(TILE_PIX) blend_bwd_kernel(const uint2* __rest
     };
     if (tid == 0 && rounds > 0) issue(0);
 
-    float accum_rec[3] = {0.f, 0.f, 0.f};
-    float dL_dpixel[3] = {0.f, 0.f, 0.f};
-    float dL_invdepth = 0.f;
-    float accum_invdepth_rec = 0.f;
-    if (inside) {
-        const size_t HW = (size_t)H * W;
-#pragma unroll
-        for (int i = 0; i < 3; i++) dL_dpixel[i] = dL_dpixels[i * HW + pix_id];
-        if (DEPTH) dL_invdepth = dL_invdepths[pix_id];
-    }
-    float last_alpha = 0.f;
-    float last_color[3] = {0.f, 0.f, 0.f};
-    float last_invdepth = 0.f;
-    const float ddelx_dx = 0.5 * W;
-    const float ddely_dy = 0.5 * H;
-    float bg_dot_dpixel = 0;
-#pragma unroll
-    for (int i = 0; i < 3; i++) bg_dot_dpixel += bg_color[i] * dL_dpixel[i];
+    const float ddelx_dx = 0.5f * W;
+    const float ddely_dy = 0.5f * H;
 
     int pending = -1;
     int my_gid = -1;
@@ -143,9 +213,11 @@ __global__ void __launch_bounds__(TILE_PIX) blend_bwd_kernel(const uint2* __rest
             float v[NV];
             bool any = false;
 #pragma unroll
-            for (int k = 0; k < NV; k++) {
-                v[k] = a[k];
-                any |= (v[k] != 0.f);
+            for (int k = 0; k < NV; k += 2) {
+                const float2 t2 = *reinterpret_cast<const float2*>(a + k);
+                v[k] = t2.x;
+                v[k + 1] = t2.y;
+                any |= (t2.x != 0.f) | (t2.y != 0.f);
             }
             if (any) {
                 atomicAdd(&dL_dmean2D[3 * (size_t)my_gid + 0], v[0]);
@@ -159,7 +231,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_bwd_kernel(const uint2* __rest
                 atomicAdd(&dL_dcolors[3 * (size_t)my_gid + 2], v[8]);
                 if (DEPTH) atomicAdd(&dL_dinvdepths[my_gid], v[9]);
 #pragma unroll
-                for (int k = 0; k < NV; k++) a[k] = 0.f;
+                for (int k = 0; k < NV; k += 2) *reinterpret_cast<float2*>(a + k) = make_float2(0.f, 0.f);
             }
         }
         pending = -1;
@@ -183,82 +255,24 @@ __global__ void __launch_bounds__(TILE_PIX) blend_bwd_kernel(const uint2* __rest
             }
             pending = b;
         }
-        const SplatRec* __restrict__ rb = sm.recs[s];
-        float* acc = sm.acc[s];
         if (lo >= wmax) continue;  // nothing in this batch reaches any pixel of this warp
-        for (int j = cnt - 1; j >= 0; j--) {
-            const unsigned pos = lo + (unsigned)j;  // 0-based position in the tile's list == contributor index
-            if (pos >= wmax) continue;
+        const int jtop = (int)min((unsigned)cnt, wmax - lo) - 1;
+        const float4* __restrict__ rp = reinterpret_cast<const float4*>(&sm.recs[s][0]) + 3 * jtop;
+        float* accp = &sm.acc[s][jtop * NV];
+        unsigned pos = lo + (unsigned)jtop;  // 0-based position in the tile's list == contributor index - 1
+        for (int j = jtop; j >= 0; j--, rp -= 3, accp -= NV, pos--) {
+            const bool act0 = pos < px[0].last_contributor, act1 = pos < px[1].last_contributor;
             float v[NV];
 #pragma unroll
             for (int k = 0; k < NV; k++) v[k] = 0.f;
+            const float4 q0 = rp[0], q1 = rp[1], q2 = rp[2];
             bool contrib = false;
-            if (pos < last_contributor) {
-                const float4 q0 = *reinterpret_cast<const float4*>(&rb[j].x);
-                const float4 q1 = *reinterpret_cast<const float4*>(&rb[j].conz);
-                const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
-                const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
-                if (power <= 0.0f) {
-                    const float G = expf(power);
-                    const float test_alpha = q1.y * G;
-                    const bool nullalpha = test_alpha > 0.99f;
-                    const float my_alpha = min(0.99f, test_alpha);
-                    const float4 q2 = *reinterpret_cast<const float4*>(&rb[j].b);
-                    float alpha, t = 1.f, frac = 1.f;
-                    if (LOD) {
-                        t = q2.z;
-                        frac = q2.w;
-                        const float kidsqrt_alpha = 1.0f - powf(1.0f - my_alpha, frac);
-                        alpha = t * my_alpha + (1.0f - t) * kidsqrt_alpha;
-                    } else {
-                        alpha = my_alpha;
-                    }
-                    if (alpha >= 1.0f / 255.0f) {
-                        contrib = true;
-                        T = T / (1.f - alpha);
-                        const float weight = alpha * T;
-                        float dL_dalpha = 0.0f;
-                        const float col[3] = {q1.z, q1.w, q2.x};
-#pragma unroll
-                        for (int ch = 0; ch < 3; ch++) {
-                            const float c = col[ch];
-                            accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-                            last_color[ch] = c;
-                            const float dL_dchannel = dL_dpixel[ch];
-                            dL_dalpha += (c - accum_rec[ch]) * dL_dchannel;
-                            v[6 + ch] = weight * dL_dchannel;
-                        }
-                        if (DEPTH) {
-                            const float invd = 1.f / q2.y;
-                            accum_invdepth_rec = last_alpha * last_invdepth + (1.f - last_alpha) * accum_invdepth_rec;
-                            last_invdepth = invd;
-                            dL_dalpha += (invd - accum_invdepth_rec) * dL_invdepth;
-                            v[9] = weight * dL_invdepth;
-                        }
-                        dL_dalpha *= T;
-                        last_alpha = alpha;
-                        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
-                        dL_dalpha = nullalpha ? 0 : dL_dalpha;
-                        const float dL_dG = q1.y * dL_dalpha;
-                        const float gdx = G * d.x;
-                        const float gdy = G * d.y;
-                        const float dG_ddelx = -gdx * q0.z - gdy * q0.w;
-                        const float dG_ddely = -gdy * q1.x - gdx * q0.w;
-                        v[0] = dL_dG * dG_ddelx * ddelx_dx;
-                        v[1] = dL_dG * dG_ddely * ddely_dy;
-                        v[2] = -0.5f * gdx * d.x * dL_dG;
-                        v[3] = -0.5f * gdx * d.y * dL_dG;
-                        v[4] = -0.5f * gdy * d.y * dL_dG;
-                        float opac_grad_mult = 1.0f;
-                        if (LOD) opac_grad_mult = t - powf(1.0f - my_alpha, frac - 1.0f) * (t - 1.0f) * frac;
-                        v[5] = opac_grad_mult * G * dL_dalpha;
-                    }
-                }
-            }
+            if (act0) contrib |= bwd_pair<LOD, DEPTH>(px[0], q0, q1, q2, ddelx_dx, ddely_dy, v);
+            if (act1) contrib |= bwd_pair<LOD, DEPTH>(px[1], q0, q1, q2, ddelx_dx, ddely_dy, v);
             if (!__any_sync(0xffffffffu, contrib)) continue;
             int slot;
             const float total = warp_reduce10(v, lane, slot);
-            if (slot >= 0 && (DEPTH || slot < 9) && total != 0.f) atomicAdd(&acc[j * NV + slot], total);
+            if (slot >= 0 && (DEPTH || slot < 9) && total != 0.f) atomicAdd(accp + slot, total);
         }
     }
     __syncthreads();
@@ -268,7 +282,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_bwd_kernel(const uint2* __rest
 int launch_blend_bwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, int W, int H, const float* bg,
                      const int32_t* indices, const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic,
                      float* dL_dopacity, float* dL_dcolor, float* dL_dinvdepth, cudaStream_t s) {
-    dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1), block(TILE_X, TILE_Y, 1);
+    dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1), block(BWD_THREADS, 1, 1);
     static bool attr_set = false;
     if (!attr_set) {
         LODGS_CUDA(cudaFuncSetAttribute(blend_bwd_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmem)));

@@ -13,6 +13,7 @@
 namespace lodgs {
 
 constexpr int BLEND_BATCH = 256;
+constexpr int BLEND_THREADS = 128;  // 16 x 8 threads, two vertically adjacent pixels each: a warp covers a 16x4 pixel block
 
 struct BlendSmem {
     SplatRec recs[2][BLEND_BATCH];
@@ -21,20 +22,56 @@ struct BlendSmem {
     uint64_t bar[2];
 };
 
+struct PixState {
+    float px, py, T, C0, C1, C2, D;
+    uint32_t last;
+};
+
+// One (pixel, splat) pair; rounding pinned to the reference build's PTX for renderCUDA (forward.cu:529-585):
+// power = (dx*(dx*con.x) + dy*(dy*con.z)) * -0.5 - dy*(dx*con.y), C += T * (alpha * c).
 template <bool LOD, bool DEPTH, bool SEEN>
-__global__ void __launch_bounds__(TILE_PIX) blend_fwd_kernel(const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
-                                                            const uint32_t* __restrict__ point_list, int W, int H,
-                                                            const float* __restrict__ bg_color, float* __restrict__ final_T,
-                                                            uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
-                                                            float* __restrict__ out_invdepth, int32_t* __restrict__ seen) {
-    __shared__ BlendSmem sm;
-    const unsigned tid = threadIdx.y * TILE_X + threadIdx.x;
+__device__ __forceinline__ void blend_pair(PixState& p, unsigned& done, const float4 q0, const float4 q1, const float4 q2, uint32_t contributor,
+                                           uint8_t* flagp) {
+    const float dx = __fsub_rn(q0.x, p.px), dy = __fsub_rn(q0.y, p.py);
+    const float quad = __fmaf_rn(dx, __fmul_rn(dx, q0.z), __fmul_rn(dy, __fmul_rn(dy, q1.x)));
+    const float power = __fsub_rn(__fmul_rn(quad, -0.5f), __fmul_rn(dy, __fmul_rn(dx, q0.w)));
+    if (power > 0.0f) return;
+    float alpha = fminf(0.99f, __fmul_rn(q1.y, expf(power)));
+    if (LOD) {
+        const float kidsqrt_alpha = __fsub_rn(1.0f, __powf(__fsub_rn(1.0f, alpha), q2.w));
+        alpha = __fmaf_rn(alpha, q2.z, __fmul_rn(__fsub_rn(1.0f, q2.z), kidsqrt_alpha));
+    }
+    if (alpha < 1.0f / 255.0f) return;
+    const float test_T = __fmul_rn(p.T, __fsub_rn(1.0f, alpha));
+    if (test_T < 0.0001f) {
+        done = 1u;
+        return;
+    }
+    if (SEEN) *flagp = 1;
+    p.C0 = __fmaf_rn(p.T, __fmul_rn(alpha, q1.z), p.C0);
+    p.C1 = __fmaf_rn(p.T, __fmul_rn(alpha, q1.w), p.C1);
+    p.C2 = __fmaf_rn(p.T, __fmul_rn(alpha, q2.x), p.C2);
+    if (DEPTH) p.D = __fmaf_rn(p.T, __fmul_rn(alpha, q2.y), p.D);  // q2.y = rcp.rn(depth), precomputed per instance
+    p.T = test_T;
+    p.last = contributor;
+}
+
+template <bool LOD, bool DEPTH, bool SEEN>
+__global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
+                                                                 const uint32_t* __restrict__ point_list, int W, int H,
+                                                                 const float* __restrict__ bg_color, float* __restrict__ final_T,
+                                                                 uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
+                                                                 float* __restrict__ out_invdepth, int32_t* __restrict__ seen) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    BlendSmem& sm = *reinterpret_cast<BlendSmem*>(smem_raw);
+    const unsigned tid = threadIdx.x, tx = tid & 15u, ty = tid >> 4;
     const unsigned horizontal_blocks = (W + TILE_X - 1) / TILE_X;
-    const uint2 pix = {blockIdx.x * TILE_X + threadIdx.x, blockIdx.y * TILE_Y + threadIdx.y};
-    const uint32_t pix_id = W * pix.y + pix.x;
-    const float2 pixf = {(float)pix.x, (float)pix.y};
-    const bool inside = pix.x < (unsigned)W && pix.y < (unsigned)H;
-    bool done = !inside;
+    const unsigned pix_x = blockIdx.x * TILE_X + tx, pix_y0 = blockIdx.y * TILE_Y + 2u * ty;
+    const bool inside0 = pix_x < (unsigned)W && pix_y0 < (unsigned)H;
+    const bool inside1 = pix_x < (unsigned)W && pix_y0 + 1u < (unsigned)H;
+    unsigned done0 = inside0 ? 0u : 1u, done1 = inside1 ? 0u : 1u;
+    PixState p0 = {(float)pix_x, (float)pix_y0, 1.0f, 0.f, 0.f, 0.f, 0.f, 0u};
+    PixState p1 = {(float)pix_x, (float)(pix_y0 + 1u), 1.0f, 0.f, 0.f, 0.f, 0.f, 0u};
 
     const uint2 range = ranges[blockIdx.y * horizontal_blocks + blockIdx.x];
     const int total = (int)(range.y - range.x);
@@ -46,8 +83,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_fwd_kernel(const uint2* __rest
         mbar_fence_init();
     }
     if (SEEN) {
-        sm.flag[0][tid] = 0;
-        sm.flag[1][tid] = 0;
+        for (int i = tid; i < 2 * BLEND_BATCH; i += BLEND_THREADS) (&sm.flag[0][0])[i] = 0;
     }
     __syncthreads();
 
@@ -65,19 +101,19 @@ __global__ void __launch_bounds__(TILE_PIX) blend_fwd_kernel(const uint2* __rest
     };
     if (tid == 0 && rounds > 0) issue(0);
 
-    float T = 1.0f;
-    uint32_t last_contributor = 0;
-    float C[3] = {0.f, 0.f, 0.f};
-    float expected_invdepth = 0.0f;
-    uint32_t my_id = 0;    // id of the splat this thread flushes `seen` for (previous batch)
-    int pending = -1;      // batch whose seen flags still have to be flushed
+    uint32_t my_id[2] = {0, 0};  // ids of the two splats this thread flushes `seen` for (previous batch)
+    int pending = -1;            // batch whose seen flags still have to be flushed
 
     auto flush_seen = [&]() {
         if (SEEN && pending >= 0) {
             const int ps = pending & 1;
-            if (sm.flag[ps][tid]) {
-                seen[my_id] = 1;
-                sm.flag[ps][tid] = 0;
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const unsigned slot = tid + h * BLEND_THREADS;
+                if (sm.flag[ps][slot]) {
+                    seen[my_id[h]] = 1;
+                    sm.flag[ps][slot] = 0;
+                }
             }
         }
     };
@@ -85,11 +121,11 @@ __global__ void __launch_bounds__(TILE_PIX) blend_fwd_kernel(const uint2* __rest
     int toDo = total;
     for (int b = 0; b < rounds; b++, toDo -= BLEND_BATCH) {
         // barrier: everyone has left batch b-1, so its ring slot may be refilled; also the CTA-wide exit vote
-        const int num_done = __syncthreads_count(done);
+        const int num_done = __syncthreads_count((done0 & done1) != 0u);
         flush_seen();
         pending = -1;
         const int s = b & 1;
-        if (num_done == TILE_PIX) {
+        if (num_done == BLEND_THREADS) {
             // batch b's bulk copy is still in flight: it must land before the CTA (and its smem) goes away
             mbar_wait(&sm.bar[s], (unsigned)(b >> 1) & 1u);
             break;
@@ -99,71 +135,72 @@ __global__ void __launch_bounds__(TILE_PIX) blend_fwd_kernel(const uint2* __rest
         const int cnt = min(BLEND_BATCH, toDo);
         if (SEEN) {
             const unsigned mis = (range.x + (unsigned)b * BLEND_BATCH) & 3u;
-            if ((int)tid < cnt) my_id = sm.ids[s][mis + tid];
+#pragma unroll
+            for (int h = 0; h < 2; h++)
+                if ((int)(tid + h * BLEND_THREADS) < cnt) my_id[h] = sm.ids[s][mis + tid + h * BLEND_THREADS];
             pending = b;
         }
-        const SplatRec* __restrict__ rb = sm.recs[s];
-        const uint32_t base = (uint32_t)b * BLEND_BATCH;
-        for (int j = 0; j < cnt; j++) {
-            // ballot-based early termination: the warp stops scanning once all 32 pixels are saturated
-            if (__all_sync(0xffffffffu, done)) break;
-            if (done) continue;
-            const float4 q0 = *reinterpret_cast<const float4*>(&rb[j].x);     // x y conx cony
-            const float4 q1 = *reinterpret_cast<const float4*>(&rb[j].conz);  // conz opac r g
-            const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
-            const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
-            if (power > 0.0f) continue;
-            const float my_alpha = min(0.99f, q1.y * expf(power));
-            float alpha;
-            float4 q2;
-            if (LOD || DEPTH) q2 = *reinterpret_cast<const float4*>(&rb[j].b);  // b depth t invkids
-            if (LOD) {
-                const float kidsqrt_alpha = 1.0f - __powf(1.0f - my_alpha, q2.w);
-                alpha = q2.z * my_alpha + (1.0f - q2.z) * kidsqrt_alpha;
-            } else {
-                alpha = my_alpha;
-            }
-            if (alpha < 1.0f / 255.0f) continue;
-            const float test_T = T * (1 - alpha);
-            if (test_T < 0.0001f) {
-                done = true;
-                continue;
-            }
-            if (SEEN) sm.flag[s][j] = 1;
-            const float cb = (LOD || DEPTH) ? q2.x : rb[j].b;
-            C[0] += q1.z * alpha * T;
-            C[1] += q1.w * alpha * T;
-            C[2] += cb * alpha * T;
-            if (DEPTH) expected_invdepth += (1 / q2.y) * alpha * T;
-            T = test_T;
-            last_contributor = base + (uint32_t)j + 1u;
+        const float4* __restrict__ rp = reinterpret_cast<const float4*>(&sm.recs[s][0]);
+        uint8_t* fl = &sm.flag[s][0];
+        uint32_t contributor = (uint32_t)b * BLEND_BATCH;
+        for (int j = 0; j < cnt; j++, rp += 3, fl++) {
+            contributor++;
+            // ballot-based early termination: the warp stops scanning once all of its 64 pixels are saturated
+            if (__all_sync(0xffffffffu, (done0 & done1) != 0u)) break;
+            const float4 q0 = rp[0];  // x y conx cony
+            const float4 q1 = rp[1];  // conz opac r g
+            const float4 q2 = rp[2];  // b 1/depth t 1/kids
+            if (!done0) blend_pair<LOD, DEPTH, SEEN>(p0, done0, q0, q1, q2, contributor, fl);
+            if (!done1) blend_pair<LOD, DEPTH, SEEN>(p1, done1, q0, q1, q2, contributor, fl);
         }
     }
     if (SEEN) {
         __syncthreads();
         flush_seen();
     }
-    if (inside) {
-        final_T[pix_id] = T;
-        n_contrib[pix_id] = last_contributor;
-        const size_t HW = (size_t)H * W;
-        out_color[0 * HW + pix_id] = C[0] + T * bg_color[0];
-        out_color[1 * HW + pix_id] = C[1] + T * bg_color[1];
-        out_color[2 * HW + pix_id] = C[2] + T * bg_color[2];
-        if (DEPTH) out_invdepth[pix_id] = expected_invdepth;
+    const size_t HW = (size_t)H * W;
+    const float bg0 = bg_color[0], bg1 = bg_color[1], bg2 = bg_color[2];
+    if (inside0) {
+        const uint32_t pix_id = W * pix_y0 + pix_x;
+        final_T[pix_id] = p0.T;
+        n_contrib[pix_id] = p0.last;
+        out_color[0 * HW + pix_id] = __fmaf_rn(p0.T, bg0, p0.C0);
+        out_color[1 * HW + pix_id] = __fmaf_rn(p0.T, bg1, p0.C1);
+        out_color[2 * HW + pix_id] = __fmaf_rn(p0.T, bg2, p0.C2);
+        if (DEPTH) out_invdepth[pix_id] = p0.D;
     }
+    if (inside1) {
+        const uint32_t pix_id = W * (pix_y0 + 1u) + pix_x;
+        final_T[pix_id] = p1.T;
+        n_contrib[pix_id] = p1.last;
+        out_color[0 * HW + pix_id] = __fmaf_rn(p1.T, bg0, p1.C0);
+        out_color[1 * HW + pix_id] = __fmaf_rn(p1.T, bg1, p1.C1);
+        out_color[2 * HW + pix_id] = __fmaf_rn(p1.T, bg2, p1.C2);
+        if (DEPTH) out_invdepth[pix_id] = p1.D;
+    }
+}
+
+template <bool LOD, bool DEPTH, bool SEEN>
+static int launch_blend_one(dim3 grid, cudaStream_t s, const uint2* ranges, const SplatRec* recs, const uint32_t* point_list, int W, int H,
+                            const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_invdepth, int32_t* seen) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        LODGS_CUDA(cudaFuncSetAttribute(blend_fwd_kernel<LOD, DEPTH, SEEN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BlendSmem)));
+        attr_set = true;
+    }
+    blend_fwd_kernel<LOD, DEPTH, SEEN><<<grid, BLEND_THREADS, sizeof(BlendSmem), s>>>(ranges, recs, point_list, W, H, bg, final_T, n_contrib,
+                                                                                  out_color, out_invdepth, seen);
+    LODGS_LAUNCHED("blend_fwd_kernel");
+    return LODGS_OK;
 }
 
 template <bool LOD, bool DEPTH>
 static int launch_blend_seen(bool has_seen, dim3 grid, dim3 block, cudaStream_t s, const uint2* ranges, const SplatRec* recs,
                              const uint32_t* point_list, int W, int H, const float* bg, float* final_T, uint32_t* n_contrib,
                              float* out_color, float* out_invdepth, int32_t* seen) {
-    if (has_seen)
-        blend_fwd_kernel<LOD, DEPTH, true><<<grid, block, 0, s>>>(ranges, recs, point_list, W, H, bg, final_T, n_contrib, out_color, out_invdepth, seen);
-    else
-        blend_fwd_kernel<LOD, DEPTH, false><<<grid, block, 0, s>>>(ranges, recs, point_list, W, H, bg, final_T, n_contrib, out_color, out_invdepth, seen);
-    LODGS_LAUNCHED("blend_fwd_kernel");
-    return LODGS_OK;
+    (void)block;
+    if (has_seen) return launch_blend_one<LOD, DEPTH, true>(grid, s, ranges, recs, point_list, W, H, bg, final_T, n_contrib, out_color, out_invdepth, seen);
+    return launch_blend_one<LOD, DEPTH, false>(grid, s, ranges, recs, point_list, W, H, bg, final_T, n_contrib, out_color, out_invdepth, seen);
 }
 
 int launch_blend_fwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, int W, int H, const float* bg,

@@ -48,9 +48,9 @@ __device__ __forceinline__ mat3 quat_to_mat(float r, float x, float y, float z) 
 
 // Explicitly rounded FP32 ops: the per-Gaussian chain below decides integer outputs (radii, rects, tile counts), so the
 // placement of every fused multiply-add is pinned with intrinsics instead of being left to the compiler's
-// contraction heuristics. The placement is the one nvcc 12.9 chooses for the reference's glm expressions
-// (HR/cuda_rasterizer/forward.cu:141-215, checked with tools/ptx_expr.py against the sm_100a PTX of the reference
-// build), which is what makes these outputs bit-identical to oracle/_ref.
+// contraction heuristics. The placement is the one nvcc/ptxas 12.9 choose for the reference's glm expressions
+// (HR/cuda_rasterizer/forward.cu:141-215): nvcc's fma.rn in the PTX (tools/ptx_expr.py) plus the mul/add pairs ptxas
+// fuses afterwards (cuobjdump -sass of oracle/_ref), which is what makes these outputs bit-identical to oracle/_ref.
 #define FM(a, b) __fmul_rn((a), (b))
 #define FA(a, b) __fadd_rn((a), (b))
 #define FS(a, b) __fsub_rn((a), (b))
@@ -61,9 +61,10 @@ __device__ __forceinline__ void cov3d_from_scale_rot(float s0, float s1, float s
     const float r = q.x, x = q.y, y = q.z, z = q.w;
     const float sx = FM(mod, s0), sy = FM(mod, s1), sz = FM(mod, s2);
     const float yy = FM(y, y), zz = FM(z, z);
-    const float xy = FM(x, y), rz = FM(r, z), xz = FM(x, z), ry = FM(r, y), yz = FM(y, z), rx = FM(r, x);
+    // ptxas fuses the second product of each off-diagonal pair (SASS of the reference build): xy -+ rz, ry +- xz, yz -+ rx
+    const float rz = FM(r, z), xz = FM(x, z), rx = FM(r, x);
     const float a00 = FA(yy, zz), a11 = FF(x, x, zz), a22 = FF(x, x, yy);
-    const float b01 = FS(xy, rz), b02 = FA(ry, xz), b10 = FA(xy, rz), b12 = FS(yz, rx), b20 = FS(xz, ry), b21 = FA(rx, yz);
+    const float b01 = FF(x, y, -rz), b10 = FF(x, y, rz), b02 = FF(r, y, xz), b20 = FF(y, -r, xz), b12 = FF(y, z, -rx), b21 = FF(y, z, rx);
     const float R00 = FS(1.0f, FA(a00, a00)), R01 = FA(b01, b01), R02 = FA(b02, b02);
     const float R10 = FA(b10, b10), R11 = FS(1.0f, FA(a11, a11)), R12 = FA(b12, b12);
     const float R20 = FA(b20, b20), R21 = FA(b21, b21), R22 = FS(1.0f, FA(a22, a22));

@@ -127,13 +127,13 @@ __device__ __forceinline__ uint32_t preprocess_one(const PreParams& p, const Geo
 
     float3 cov = project_cov(p_orig, p.focal_x, p.focal_y, p.tan_fovx, p.tan_fovy, cov6, view, nullptr);
 
-    // (forward.cu:362-392) same pinned rounding as gaussmath.cuh: no contraction in the determinants
+    // (forward.cu:362-392) same pinned rounding as gaussmath.cuh: the determinants are single FMAs in the reference SASS
     constexpr float h_var = 0.3f;
     const float cov01sq = FM(cov.y, cov.y);
-    const float det_cov = FS(FM(cov.x, cov.z), cov01sq);
+    const float det_cov = FF(cov.x, cov.z, -cov01sq);
     cov.x = FA(cov.x, h_var);
     cov.z = FA(cov.z, h_var);
-    const float det_cov_plus_h_cov = FS(FM(cov.x, cov.z), cov01sq);
+    const float det_cov_plus_h_cov = FF(cov.x, cov.z, -cov01sq);
     const float h_convolution_scaling = __fsqrt_rn(fmaxf(__fdiv_rn(det_cov, det_cov_plus_h_cov), 0.000025f));
     const float det = det_cov_plus_h_cov;
     if (det == 0.0f) return 0;
@@ -141,7 +141,7 @@ __device__ __forceinline__ uint32_t preprocess_one(const PreParams& p, const Geo
     const float3 conic = {FM(cov.z, det_inv), FM(det_inv, -cov.y), FM(cov.x, det_inv)};
 
     const float mid = FM(FA(cov.x, cov.z), 0.5f);
-    const float disc = __fsqrt_rn(fmaxf(FS(FM(mid, mid), det), 0.1f));
+    const float disc = __fsqrt_rn(fmaxf(FF(mid, mid, -det), 0.1f));
     const float lambda1 = FA(mid, disc);
     const float lambda2 = FS(mid, disc);
     const float my_radius = ceilf(FM(__fsqrt_rn(fmaxf(lambda1, lambda2)), 3.f));

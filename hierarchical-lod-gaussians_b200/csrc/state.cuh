@@ -64,7 +64,7 @@ static inline GeomState geom_from_chunk(void* chunk, size_t P) {
 struct __align__(16) SplatRec {
     float x, y, conx, cony;      // projected mean, conic xx, xy
     float conz, opac, r, g;      // conic yy, opacity (AA-compensated), colour
-    float b, depth, t, invkids;  // colour, view depth, LOD weight, 1/kids
+    float b, invdepth, t, invkids;  // colour, 1/view depth (rcp.rn), LOD weight, 1/kids
 };
 static_assert(sizeof(SplatRec) == 48, "SplatRec must be 48 bytes");
 

@@ -87,12 +87,15 @@ def test_side_by_side_with_reference_build(P, W, H, lod):
     m = minewrap.forward(sc, cam, bg, **kw)
     r = refshim.forward(sc, cam, bg, **kw)
     assert m["R"] == r["R"]
-    bad = sum(int((m[k].long() != r[k].long()).sum()) for k in INT_KEYS)
-    # FMA contraction inside the 3D covariance differs from nvcc's choice for the reference in ~1e-6 of the entries
-    # (profiles/r1_parity_diag_first.log); everything downstream of an identical radius is identical.
-    assert bad <= max(2, int(3e-6 * P * 12)), bad
-    assert float((m["color"] - r["color"]).abs().max()) <= 1e-4
-    assert float((m["invdepth"] - r["invdepth"]).abs().max()) <= 1e-4
+    # the FMA placement of the covariance / conic / blend chains is pinned to the reference build's SASS:
+    # every integer output AND the float state and image are bit-identical, not merely within tolerance
+    for k in INT_KEYS:
+        assert torch.equal(m[k].long(), r[k].long()), k
+    vis = r["radii"] > 0
+    for k in ("conic_opacity", "cov3D", "depths", "means2D", "rgb"):
+        assert torch.equal(m[k][vis], r[k][vis]), k
+    assert torch.equal(m["final_T"], r["final_T"])
+    assert torch.equal(m["color"], r["color"]) and torch.equal(m["invdepth"], r["invdepth"])
     torch.manual_seed(0)
     dL = (torch.rand(3, H, W, device="cuda") - 0.5) / (H * W)
     dLi = (torch.rand(1, H, W, device="cuda") - 0.5) / (H * W)
