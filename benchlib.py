@@ -227,11 +227,14 @@ def _work_model(arm, n_gauss):
     n_test, n_alpha, n_blend = (int(x) for x in cnt.tolist())
     work = {
         "preprocess_fwd_kernel": ("hbm", 20.0 * n_gauss + p_vis * (115.0 + 12.0 * M)),
-        "emit_keys_kernel": ("hbm", 24.0 * n_gauss + 12.0 * R),
-        "sort_histogram_kernel": ("hbm", 8.0 * R),
-        "sort_onesweep_kernel": ("hbm", 24.0 * R),          # per launch (one digit pass)
-        "tile_ranges_kernel": ("hbm", 8.0 * R),
-        "build_records_kernel": ("hbm", (4.0 + 44.0 + 48.0) * R),
+        "sort_depth_hist_kernel": ("hbm", 4.0 * n_gauss),
+        "sort_depth_pass_kernel": ("hbm", 16.0 * n_gauss),     # per launch (one 8-bit digit of the depth bits)
+        "scan_sorted_kernel": ("hbm", 12.0 * n_gauss),
+        "emit_tiles_kernel": ("hbm", 28.0 * n_gauss + 8.0 * R),
+        "sort_tile_hist_kernel": ("hbm", 4.0 * R),
+        "sort_tile_pass_kernel": ("hbm", 16.0 * R),            # per launch (one 8-bit digit of the tile id)
+        "tile_ranges_kernel": ("hbm", 4.0 * R),
+        "build_records_kernel": ("hbm", (4.0 + 4.0 + 8.0 + 44.0 + 48.0) * R),
         "blend_fwd_kernel": ("fp32", 11.0 * n_test + 2.0 * n_alpha + 14.0 * n_blend),
         "blend_bwd_kernel": ("fp32", 70.0 * n_blend),
         "preprocess_bwd_kernel": ("hbm", p_vis * (115.0 + 68.0 + 24.0 * M)),

@@ -12,6 +12,11 @@
 
 namespace lodgs {
 
+int sort_pairs32_device(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* keys_out, uint32_t* vals_out, uint32_t* keys_tmp,
+                        uint32_t* vals_tmp, int n, int begin_bit, int end_bit, void* ws, cudaStream_t s, const char* pass_name,
+                        const char* hist_name);
+int launch_scan_sorted(int P, const GeomState& g, cudaStream_t s);
+
 struct PreParams {
     int P, D, M, W, H;
     const int32_t* indices;
@@ -193,6 +198,8 @@ __global__ void __launch_bounds__(PRE_BLOCK) preprocess_fwd_kernel(const PrePara
     if (t_idx < p.P) {
         tiles = preprocess_one(p, g, t_idx, s_view, s_proj);
         g.tiles_touched[t_idx] = tiles;
+        // sort key of the depth-ordered emission: culled Gaussians go to the end of the order and emit nothing
+        g.depth_keys[t_idx] = tiles ? __float_as_uint(g.depths[t_idx]) : 0xffffffffu;
     }
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned incl = tiles;
@@ -286,10 +293,21 @@ extern "C" int lodgs_forward_preprocess(int P, int D, int M, int W, int H, const
     int tiles = (P + PRE_BLOCK - 1) / PRE_BLOCK;
     preprocess_fwd_kernel<<<tiles, PRE_BLOCK, 0, s>>>(p, g);
     LODGS_LAUNCHED("preprocess_fwd_kernel");
+    // The count goes back to the host (the caller sizes the binning buffer from it, rasterizer_impl.cu:330-333) while the
+    // GPU already orders the Gaussians by depth for the emission stage: the host waits on an event recorded right after
+    // the 4-byte copy, not on the stream.
+    static thread_local cudaEvent_t ev = nullptr;
     if (num_rendered_host) {
+        if (!ev) LODGS_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
         LODGS_CUDA(cudaMemcpyAsync(num_rendered_host, &g.hdr->num_rendered, sizeof(int), cudaMemcpyDeviceToHost, s));
-        LODGS_CUDA(cudaStreamSynchronize(s));
+        LODGS_CUDA(cudaEventRecord(ev, s));
     }
+    int rc = sort_pairs32_device(g.depth_keys, nullptr, g.depth_keys_sorted, g.order, g.sort_tmp_k, g.sort_tmp_v, P, 0, 32, g.sort_ws, s, "sort_depth_pass_kernel",
+                                 "sort_depth_hist_kernel");
+    if (rc) return rc;
+    rc = launch_scan_sorted(P, g, s);
+    if (rc) return rc;
+    if (num_rendered_host) LODGS_CUDA(cudaEventSynchronize(ev));
     return LODGS_OK;
 }
 

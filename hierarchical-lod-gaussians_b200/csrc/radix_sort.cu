@@ -5,6 +5,10 @@
 // kernel per digit does rank -> decoupled look-back -> scatter, reading and writing every pair exactly once
 // per pass. Stability (and therefore bit-identical output to CUB) comes from ranking keys in index order:
 // warp-striped tiles, per-warp match-any ranking, warps and tiles chained in order.
+//
+// The kernels are templated on the key type: u64 keys serve the exported lodgs_sort_pairs (the reference's tile|depth
+// sort, kept for the CUB cross-check), u32 keys serve the two sorts of the forward pass (Gaussians by depth bits, then
+// instances by tile id — see raster_api.cu). vals_in == nullptr means "value = element index" (saves the iota pass).
 #include "state.cuh"
 
 namespace lodgs {
@@ -14,7 +18,9 @@ constexpr int SORT_ITEMS = SORT_TILE / SORT_THREADS;  // 16
 constexpr int SORT_WARPS = SORT_THREADS / 32;
 
 // ---- global histograms for all passes in one read of the keys
-__global__ void __launch_bounds__(256) sort_histogram_kernel(const uint64_t* __restrict__ keys, int n, int passes, unsigned* hist) {
+template <typename KeyT>
+__global__ void __launch_bounds__(256) sort_histogram_kernel(const KeyT* __restrict__ keys, int n, int passes, int begin_bit,
+                                                            unsigned* hist) {
     __shared__ unsigned s_hist[SORT_MAX_PASSES * SORT_RADIX];
     for (int i = threadIdx.x; i < passes * SORT_RADIX; i += blockDim.x) s_hist[i] = 0;
     __syncthreads();
@@ -24,10 +30,10 @@ __global__ void __launch_bounds__(256) sort_histogram_kernel(const uint64_t* __r
     for (int base = blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < n; base += stride) {
         const int i = base + lane;
         const bool valid = i < n;
-        const uint64_t key = valid ? __ldg(keys + i) : 0ull;
+        const KeyT key = valid ? __ldg(keys + i) : (KeyT)0;
         const unsigned vmask = __ballot_sync(0xffffffffu, valid);
         for (int p = 0; p < passes; p++) {
-            const unsigned d = (unsigned)(key >> (8 * p)) & 255u;
+            const unsigned d = (unsigned)(key >> (begin_bit + 8 * p)) & 255u;
             const unsigned d0 = __shfl_sync(0xffffffffu, d, 0);
             // degenerate digits (tile high byte, float exponent) are warp-uniform almost always: one add
             if (__all_sync(0xffffffffu, !valid || d == d0)) {
@@ -63,8 +69,9 @@ __global__ void __launch_bounds__(SORT_RADIX) sort_scan_hist_kernel(unsigned* hi
     h[threadIdx.x] = woff + incl - v;
 }
 
+template <typename KeyT>
 struct SortSmem {
-    uint64_t keys[SORT_TILE];
+    KeyT keys[SORT_TILE];
     uint32_t vals[SORT_TILE];
     unsigned warp_hist[SORT_WARPS][SORT_RADIX];  // per-warp digit counts -> exclusive offsets across warps
     unsigned digit_start[SORT_RADIX];            // exclusive scan of the tile's digit counts
@@ -73,15 +80,15 @@ struct SortSmem {
     int tile;
 };
 
-__global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const uint64_t* __restrict__ keys_in,
+template <typename KeyT>
+__global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const KeyT* __restrict__ keys_in,
                                                                     const uint32_t* __restrict__ vals_in,
-                                                                    uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
-                                                                    int n, int pass, const unsigned* __restrict__ hist_base,
+                                                                    KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
+                                                                    int n, int shift, const unsigned* __restrict__ hist_base,
                                                                     int* ticket, unsigned* lookback /* [tiles][256] */) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    SortSmem& sm = *reinterpret_cast<SortSmem*>(smem_raw);
+    SortSmem<KeyT>& sm = *reinterpret_cast<SortSmem<KeyT>*>(smem_raw);
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int shift = 8 * pass;
     if (tid == 0) sm.tile = atomicAdd(ticket, 1);
     for (int i = tid; i < SORT_WARPS * SORT_RADIX; i += SORT_THREADS) (&sm.warp_hist[0][0])[i] = 0;
     __syncthreads();
@@ -90,7 +97,7 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const uint6
     const int tile_n = (int)min((long long)SORT_TILE, (long long)n - tile_base);
 
     // ---- load, warp-striped: item k of lane l in warp w is element w*512 + k*32 + l of the tile
-    uint64_t key[SORT_ITEMS];
+    KeyT key[SORT_ITEMS];
     uint32_t val[SORT_ITEMS];
     unsigned rank[SORT_ITEMS];
     const int wbase = warp * (32 * SORT_ITEMS);
@@ -99,9 +106,9 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const uint6
         const int e = wbase + k * 32 + lane;
         if (e < tile_n) {
             key[k] = __ldg(keys_in + tile_base + e);
-            val[k] = __ldg(vals_in + tile_base + e);
+            val[k] = vals_in ? __ldg(vals_in + tile_base + e) : (uint32_t)(tile_base + e);
         } else {
-            key[k] = ~0ull;
+            key[k] = ~(KeyT)0;
             val[k] = 0;
         }
     }
@@ -184,7 +191,7 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const uint6
     __syncthreads();
     // ---- scatter: runs of equal digits go to consecutive global addresses
     for (int i = tid; i < tile_n; i += SORT_THREADS) {
-        const uint64_t kk = sm.keys[i];
+        const KeyT kk = sm.keys[i];
         const unsigned d = (unsigned)(kk >> shift) & 255u;
         const unsigned dst = sm.out_off[d] + (unsigned)i;
         keys_out[dst] = kk;
@@ -192,10 +199,12 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const uint6
     }
 }
 
-int sort_pairs_device(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, uint64_t* keys_tmp,
-                      uint32_t* vals_tmp, int n, int end_bit, void* ws, cudaStream_t s) {
+template <typename KeyT>
+int sort_pairs_device_t(const KeyT* keys_in, const uint32_t* vals_in, KeyT* keys_out, uint32_t* vals_out, KeyT* keys_tmp,
+                        uint32_t* vals_tmp, int n, int begin_bit, int end_bit, void* ws, cudaStream_t s, const char* pass_name,
+                        const char* hist_name) {
     if (n <= 0) return LODGS_OK;
-    int passes = (end_bit + 7) / 8;
+    int passes = (end_bit - begin_bit + 7) / 8;
     if (passes < 1) passes = 1;
     if (passes > SORT_MAX_PASSES) passes = SORT_MAX_PASSES;
     SortWs w = sort_from_chunk(ws, n);
@@ -203,28 +212,39 @@ int sort_pairs_device(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t
     LODGS_CUDA(cudaMemsetAsync(ws, 0, (size_t)((char*)(w.lookback + (size_t)passes * tiles * SORT_RADIX) - (char*)ws), s));
     static bool attr_set = false;
     if (!attr_set) {
-        LODGS_CUDA(cudaFuncSetAttribute(sort_onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem)));
+        LODGS_CUDA(cudaFuncSetAttribute(sort_onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem<KeyT>)));
         attr_set = true;
     }
     int hist_blocks = (int)min((size_t)148 * 8, ((size_t)n + 255) / 256);
-    sort_histogram_kernel<<<hist_blocks, 256, 0, s>>>(keys_in, n, passes, w.hist);
-    LODGS_LAUNCHED("sort_histogram_kernel");
+    sort_histogram_kernel<KeyT><<<hist_blocks, 256, 0, s>>>(keys_in, n, passes, begin_bit, w.hist);
+    LODGS_LAUNCHED(hist_name);
     sort_scan_hist_kernel<<<passes, SORT_RADIX, 0, s>>>(w.hist);
     LODGS_LAUNCHED("sort_scan_hist_kernel");
-    const uint64_t* kin = keys_in;
+    const KeyT* kin = keys_in;
     const uint32_t* vin = vals_in;
     for (int p = 0; p < passes; p++) {
         const bool to_out = ((passes - 1 - p) % 2) == 0;
-        uint64_t* kout = to_out ? keys_out : keys_tmp;
+        KeyT* kout = to_out ? keys_out : keys_tmp;
         uint32_t* vout = to_out ? vals_out : vals_tmp;
-        sort_onesweep_kernel<<<(unsigned)tiles, SORT_THREADS, sizeof(SortSmem), s>>>(kin, vin, kout, vout, n, p, w.hist + p * SORT_RADIX,
-                                                                                  w.tickets + p,
-                                                                                  w.lookback + (size_t)p * tiles * SORT_RADIX);
-        LODGS_LAUNCHED("sort_onesweep_kernel");
+        sort_onesweep_kernel<KeyT><<<(unsigned)tiles, SORT_THREADS, sizeof(SortSmem<KeyT>), s>>>(
+            kin, vin, kout, vout, n, begin_bit + 8 * p, w.hist + p * SORT_RADIX, w.tickets + p, w.lookback + (size_t)p * tiles * SORT_RADIX);
+        LODGS_LAUNCHED(pass_name);
         kin = kout;
         vin = vout;
     }
     return LODGS_OK;
+}
+
+int sort_pairs_device(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, uint64_t* keys_tmp,
+                      uint32_t* vals_tmp, int n, int end_bit, void* ws, cudaStream_t s) {
+    return sort_pairs_device_t<uint64_t>(keys_in, vals_in, keys_out, vals_out, keys_tmp, vals_tmp, n, 0, end_bit, ws, s,
+                                         "sort_onesweep_kernel", "sort_histogram_kernel");
+}
+int sort_pairs32_device(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* keys_out, uint32_t* vals_out, uint32_t* keys_tmp,
+                        uint32_t* vals_tmp, int n, int begin_bit, int end_bit, void* ws, cudaStream_t s, const char* pass_name,
+                        const char* hist_name) {
+    return sort_pairs_device_t<uint32_t>(keys_in, vals_in, keys_out, vals_out, keys_tmp, vals_tmp, n, begin_bit, end_bit, ws, s, pass_name,
+                                         hist_name);
 }
 
 }  // namespace lodgs

@@ -9,10 +9,21 @@ namespace lodgs {
 
 constexpr int PRE_BLOCK = 256;  // Gaussians per preprocess tile (one look-back state each)
 
+constexpr int SORT_RADIX = 256;
+constexpr int SORT_MAX_PASSES = 8;
+constexpr int SORT_TILE = 4096;  // keys per onesweep tile (256 threads x 16 keys)
+static inline size_t sort_tiles(size_t n) { return (n + SORT_TILE - 1) / SORT_TILE; }
+// histograms [8][256] u32 + tickets [8] i32 + look-back [8][tiles][256] u32, each 128-byte aligned (see sort_from_chunk)
+static inline size_t sort_ws_bytes(size_t n) {
+    return align_up(SORT_MAX_PASSES * SORT_RADIX * 4, 128) + align_up(SORT_MAX_PASSES * 4, 128) +
+           align_up((size_t)SORT_MAX_PASSES * sort_tiles(n) * SORT_RADIX * 4, 128);
+}
+
 struct GeomHeader {
     unsigned num_rendered;  // total (Gaussian,tile) instances, written by the last preprocess tile
     int ticket;             // dynamic tile dispenser for the fused scan
-    int pad[30];
+    int ticket2;            // same for the depth-order scan
+    int pad[29];
 };
 
 struct GeomState {
@@ -27,6 +38,15 @@ struct GeomState {
     uint32_t* tiles_touched;         // [P]
     uint32_t* point_offsets;         // [P] inclusive prefix sum of tiles_touched
     int2* rects;                     // [P]
+    // depth-ordered emission (raster_api.cu): Gaussians sorted by depth bits, then their tile counts scanned in that order
+    uint32_t* depth_keys;            // [P] depth bits, 0xffffffff for culled Gaussians
+    uint32_t* depth_keys_sorted;     // [P]
+    uint32_t* order;                 // [P] list positions in (depth bits, index) order
+    uint32_t* sort_tmp_k;            // [P] ping-pong
+    uint32_t* sort_tmp_v;            // [P]
+    uint32_t* sorted_offsets;        // [P] inclusive scan of tiles_touched[order[.]]
+    unsigned long long* scan2_state; // [ceil(P/PRE_BLOCK)+1] look-back states of that scan
+    void* sort_ws;                   // radix sort workspace for P pairs
     size_t offsets[9];
     size_t bytes;
     size_t zero_bytes;  // header + scan states: cleared at the start of every forward
@@ -46,6 +66,7 @@ static inline GeomState geom_from_chunk(void* chunk, size_t P) {
     size_t off = 0;
     g.hdr = carve_arr<GeomHeader>(b, off, 1);
     g.scan_state = carve_arr<unsigned long long>(b, off, (P + PRE_BLOCK - 1) / PRE_BLOCK + 1);
+    g.scan2_state = carve_arr<unsigned long long>(b, off, (P + PRE_BLOCK - 1) / PRE_BLOCK + 1);
     g.zero_bytes = off;
     g.depths = carve_arr<float>(b, off, P);            g.offsets[0] = (char*)g.depths - b;
     g.means2D = carve_arr<float2>(b, off, P);          g.offsets[1] = (char*)g.means2D - b;
@@ -56,6 +77,15 @@ static inline GeomState geom_from_chunk(void* chunk, size_t P) {
     g.tiles_touched = carve_arr<uint32_t>(b, off, P);  g.offsets[6] = (char*)g.tiles_touched - b;
     g.point_offsets = carve_arr<uint32_t>(b, off, P);  g.offsets[7] = (char*)g.point_offsets - b;
     g.rects = carve_arr<int2>(b, off, P);              g.offsets[8] = (char*)g.rects - b;
+    g.depth_keys = carve_arr<uint32_t>(b, off, P);
+    g.depth_keys_sorted = carve_arr<uint32_t>(b, off, P);
+    g.order = carve_arr<uint32_t>(b, off, P);
+    g.sort_tmp_k = carve_arr<uint32_t>(b, off, P);
+    g.sort_tmp_v = carve_arr<uint32_t>(b, off, P);
+    g.sorted_offsets = carve_arr<uint32_t>(b, off, P);
+    off = align_up(off, 128);
+    g.sort_ws = b + off;
+    off += sort_ws_bytes(P);
     g.bytes = align_up(off, 128);
     return g;
 }
@@ -68,10 +98,6 @@ struct __align__(16) SplatRec {
 };
 static_assert(sizeof(SplatRec) == 48, "SplatRec must be 48 bytes");
 
-constexpr int SORT_RADIX = 256;
-constexpr int SORT_MAX_PASSES = 8;
-constexpr int SORT_TILE = 4096;  // keys per onesweep tile (256 threads x 16 keys)
-
 struct SortWs {
     unsigned* hist;                  // [SORT_MAX_PASSES][256] global digit histograms -> exclusive bases
     int* tickets;                    // [SORT_MAX_PASSES]
@@ -79,7 +105,6 @@ struct SortWs {
     size_t bytes;
     size_t zero_bytes;
 };
-static inline size_t sort_tiles(size_t n) { return (n + SORT_TILE - 1) / SORT_TILE; }
 static inline SortWs sort_from_chunk(void* chunk, size_t n) {
     SortWs w;
     char* b = (char*)chunk;
@@ -93,11 +118,12 @@ static inline SortWs sort_from_chunk(void* chunk, size_t n) {
 }
 
 struct BinningState {
-    uint64_t* keys_unsorted;  // [R]
-    uint32_t* vals_unsorted;  // [R]
-    uint64_t* keys;           // [R] sorted
-    uint32_t* point_list;     // [R] sorted
-    SplatRec* recs;           // [R] sorted splat records
+    uint32_t* tiles_unsorted;  // [R] tile id of every instance, emitted in (depth, index) order of the Gaussians
+    uint32_t* vals_unsorted;   // [R] list position of the instance's Gaussian, same order
+    uint32_t* tiles_sorted;    // [R] tile ids after the stable sort by tile
+    uint64_t* keys;            // [R] sorted tile|depth keys (identical to the reference's sorted key list)
+    uint32_t* point_list;      // [R] sorted
+    SplatRec* recs;            // [R] sorted splat records
     void* sort_ws;
     size_t offsets[5];
     size_t bytes;
@@ -106,8 +132,9 @@ static inline BinningState binning_from_chunk(void* chunk, size_t R) {
     BinningState s;
     char* b = (char*)chunk;
     size_t off = 0;
-    s.keys_unsorted = carve_arr<uint64_t>(b, off, R);  s.offsets[0] = (char*)s.keys_unsorted - b;
+    s.tiles_unsorted = carve_arr<uint32_t>(b, off, R); s.offsets[0] = (char*)s.tiles_unsorted - b;
     s.vals_unsorted = carve_arr<uint32_t>(b, off, R);  s.offsets[1] = (char*)s.vals_unsorted - b;
+    s.tiles_sorted = carve_arr<uint32_t>(b, off, R);
     s.keys = carve_arr<uint64_t>(b, off, R);           s.offsets[2] = (char*)s.keys - b;
     s.point_list = carve_arr<uint32_t>(b, off, R + 8); s.offsets[3] = (char*)s.point_list - b;
     s.recs = carve_arr<SplatRec>(b, off, R);           s.offsets[4] = (char*)s.recs - b;

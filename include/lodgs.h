@@ -121,9 +121,12 @@ int lodgs_forward_preprocess(int P, int D, int M, int W, int H,
                              float tan_fovx, float tan_fovy, int32_t* radii,
                              void* geom_buffer, size_t geom_bytes, int32_t* num_rendered_host, void* stream);
 
-/* Stage 2: duplicateWithKeys (rasterizer_impl.cu:70-115) -> onesweep LSD radix sort on the 64-bit
- * tile|depth keys (replaces cub::DeviceRadixSort::SortPairs :358-363) -> identifyTileRanges (:120-142)
- * -> sorted splat records -> renderCUDA (forward.cu:450-596). R is the value stage 1 reported.
+/* Stage 2: replaces duplicateWithKeys (rasterizer_impl.cu:70-115) + cub::DeviceRadixSort::SortPairs on the 64-bit
+ * tile|depth keys (:358-363) + identifyTileRanges (:120-142) + renderCUDA (forward.cu:450-596). Stage 1 has already
+ * ordered the Gaussians by depth bits (onesweep radix sort over P u32 keys); stage 2 emits the (tile, Gaussian) instances
+ * in that order, sorts them stably by tile id alone (2 onesweep passes at 1080p instead of 6 over 64-bit keys), which
+ * yields exactly the reference's sorted list, then builds keys / tile ranges / sorted splat records and blends.
+ * R is the value stage 1 reported.
  * out_color [3,H,W]; out_invdepth [H,W] or NULL; seen [P] i32 or NULL (must be zero-filled by the caller,
  * as the reference's torch::full does). */
 int lodgs_forward_render(int P, int W, int H, int R, const float* background,
@@ -158,7 +161,8 @@ int lodgs_mark_visible(int P, const float* means3D, const float* viewmatrix, con
  * geom:   [0]=depths f32[P] [1]=means2D f32[P,2] [2]=conic_opacity f32[P,4] [3]=rgb f32[P,3]
  *         [4]=cov3D f32[P,6] [5]=clamped u8[P] (bit c = channel c clamped) [6]=tiles_touched u32[P]
  *         [7]=point_offsets u32[P] [8]=rects i32[P,2]
- * binning:[0]=keys_unsorted u64[R] [1]=values_unsorted u32[R] [2]=keys_sorted u64[R] [3]=point_list u32[R]
+ * binning:[0]=tiles_unsorted u32[R] [1]=values_unsorted u32[R]  (instances emitted in (depth bits, index) order of their
+ *         Gaussians, carrying only the tile id) [2]=keys_sorted u64[R] tile|depth [3]=point_list u32[R]
  *         [4]=splat records f32[R,12]
  * image:  [0]=final_T f32[W*H] [1]=n_contrib u32[W*H] [2]=ranges u32[tiles,2] */
 int lodgs_geom_layout(int P, size_t* offsets9);

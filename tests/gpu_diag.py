@@ -66,8 +66,6 @@ def run(P, W, H, lod=False, seed=0):
     cmp_f("rgb", m["rgb"], r["rgb"], vis)
     cmp_f("cov3D", m["cov3D"], r["cov3D"], vis)
     if m["R"] == r["R"] and r["R"] > 0:
-        bad += cmp_int("keys_unsorted", m["keys_unsorted"], r["keys_unsorted"])
-        bad += cmp_int("vals_unsorted", m["vals_unsorted"], r["vals_unsorted"])
         bad += cmp_int("keys_sorted", m["keys"], r["keys"])
         bad += cmp_int("point_list", m["point_list"], r["point_list"])
         bad += cmp_int("ranges", m["ranges"], r["ranges"])

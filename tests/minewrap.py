@@ -48,7 +48,7 @@ def forward(sc, cam, bg, indices=None, parent_indices=None, ts=None, kids=None, 
     if R > 0:
         b = (C.c_size_t * 5)()
         lodgs.lib.lodgs_binning_layout(R, b)
-        res["keys_unsorted"] = _view(binning, b[0], R * 8, torch.int64, (R,))
+        res["tiles_unsorted"] = _view(binning, b[0], R * 4, torch.int32, (R,))   # depth-ordered emission
         res["vals_unsorted"] = _view(binning, b[1], R * 4, torch.int32, (R,))
         res["keys"] = _view(binning, b[2], R * 8, torch.int64, (R,))
         res["point_list"] = _view(binning, b[3], R * 4, torch.int32, (R,))

@@ -15,7 +15,9 @@ from oracle import refshim
 
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-INT_KEYS = ("radii", "tiles_touched", "point_offsets", "keys_unsorted", "vals_unsorted", "keys", "point_list", "ranges", "n_contrib", "seen")
+# the unsorted key list of duplicateWithKeys has no counterpart here (instances are emitted in depth order carrying only
+# their tile id); its sorted result — keys, point_list, ranges — is compared bit for bit
+INT_KEYS = ("radii", "tiles_touched", "point_offsets", "keys", "point_list", "ranges", "n_contrib", "seen")
 GRAD_KEYS = ("dL_dmean2D", "dL_dcolor", "dL_dopacity", "dL_dmean3D", "dL_dcov3D", "dL_dsh", "dL_dscale", "dL_drot")
 
 
@@ -117,10 +119,14 @@ def test_full_size_properties():
     tt, po = f["tiles_touched"].long(), f["point_offsets"].long()
     assert torch.equal(po, torch.cumsum(tt, 0)) and int(po[-1]) == R            # fused scan == prefix sum
     assert ((f["radii"] > 0) == (tt > 0)).all()
-    ku, ks, pl = f["keys_unsorted"], f["keys"], f["point_list"].long()
+    ks, pl = f["keys"], f["point_list"].long()
     assert (ks[1:] >= ks[:-1]).all()                                             # sorted
-    want_k, order = torch.sort(ku, stable=True)
-    assert torch.equal(ks, want_k) and torch.equal(pl, f["vals_unsorted"].long()[order])  # identical to a stable (CUB) sort
+    assert ((ks[1:] > ks[:-1]) | (pl[1:] > pl[:-1])).all()                       # ties in list order == a stable sort of the reference's emission
+    assert torch.equal(torch.bincount(pl, minlength=P), tt)                      # every Gaussian appears once per touched tile
+    tu, vu = f["tiles_unsorted"].long(), f["vals_unsorted"].long()               # emission: Gaussians in (depth bits, index) order
+    dk = f["depths"].view(torch.int32).long()[vu]
+    assert ((dk[1:] > dk[:-1]) | ((dk[1:] == dk[:-1]) & (vu[1:] >= vu[:-1]))).all()
+    assert torch.equal(torch.sort(tu * P + vu).values, torch.sort((ks >> 32) * P + pl).values)  # same multiset of (tile, Gaussian)
     tiles = (ks >> 32)
     counts = torch.bincount(tiles, minlength=f["ranges"].size(0))
     rng = f["ranges"].long()
