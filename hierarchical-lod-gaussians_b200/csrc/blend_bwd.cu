@@ -75,8 +75,7 @@ __device__ __forceinline__ float warp_reduce10(const float (&v)[NV], unsigned la
 
 // One (pixel, splat) pair of the replay (backward.cu:600-716); adds this pixel's ten partial gradients to v.
 template <bool LOD, bool DEPTH>
-__device__ __forceinline__ bool bwd_pair(BwdPix& p, const float4 q0, const float4 q1, const float4 q2, float ddelx_dx, float ddely_dy,
-                                         float (&v)[NV]) {
+__device__ __forceinline__ bool bwd_pair(BwdPix& p, const float4 q0, const float4 q1, const float4 q2, float (&v)[NV]) {
     const float dx = __fsub_rn(q0.x, p.px), dy = __fsub_rn(q0.y, p.py);
     const float quad = __fmaf_rn(dx, __fmul_rn(dx, q0.z), __fmul_rn(dy, __fmul_rn(dy, q1.x)));
     const float power = __fsub_rn(__fmul_rn(quad, -0.5f), __fmul_rn(dy, __fmul_rn(dx, q0.w)));
@@ -115,18 +114,18 @@ __device__ __forceinline__ bool bwd_pair(BwdPix& p, const float4 q0, const float
     p.last_alpha = alpha;
     dL_dalpha -= p.T_final * rcp1ma * p.bg_dot;
     dL_dalpha = nullalpha ? 0.f : dL_dalpha;
-    const float dL_dG = q1.y * dL_dalpha;
-    const float gdx = G * dx, gdy = G * dy;
-    const float dG_ddelx = -gdx * q0.z - gdy * q0.w;
-    const float dG_ddely = -gdy * q1.x - gdx * q0.w;
-    v[0] += dL_dG * dG_ddelx * ddelx_dx;
-    v[1] += dL_dG * dG_ddely * ddely_dy;
-    v[2] += -0.5f * gdx * dx * dL_dG;
-    v[3] += -0.5f * gdx * dy * dL_dG;
-    v[4] += -0.5f * gdy * dy * dL_dG;
-    float opac_grad_mult = 1.0f;
-    if (LOD) opac_grad_mult = t - __powf(1.0f - my_alpha, frac - 1.0f) * (t - 1.0f) * frac;
-    v[5] += opac_grad_mult * G * dL_dalpha;
+    // Per pair only the moments of k = G * dL_dalpha over (dx, dy) are accumulated; the splat-constant factors (conic,
+    // opacity, 0.5*W, 0.5*H, -0.5) of backward.cu:676-702 are applied once per (tile, splat) when the sums are flushed:
+    //   dL_dmean2D.x = -opac * 0.5W * (con.x * S[k dx] + con.y * S[k dy]),   dL_dconic.xx = -0.5 * opac * S[k dx dx], ...
+    const float k = G * dL_dalpha;
+    const float kdx = k * dx, kdy = k * dy;
+    v[0] += kdx;
+    v[1] += kdy;
+    v[2] = fmaf(kdx, dx, v[2]);
+    v[3] = fmaf(kdx, dy, v[3]);
+    v[4] = fmaf(kdy, dy, v[4]);
+    if (LOD) v[5] = fmaf(t - __powf(1.0f - my_alpha, frac - 1.0f) * (t - 1.0f) * frac, k, v[5]);
+    else v[5] += k;
     return true;
 }
 
@@ -206,6 +205,7 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
 
     int pending = -1;
     int my_gid = -1;
+    float4 my_con = {0.f, 0.f, 0.f, 0.f};  // conic xx, xy, yy and opacity of the splat this thread flushes
     auto flush = [&]() {
         if (pending < 0) return;
         float* a = &sm.acc[pending & 1][tid * NV];
@@ -220,11 +220,12 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
                 any |= (t2.x != 0.f) | (t2.y != 0.f);
             }
             if (any) {
-                atomicAdd(&dL_dmean2D[3 * (size_t)my_gid + 0], v[0]);
-                atomicAdd(&dL_dmean2D[3 * (size_t)my_gid + 1], v[1]);
-                atomicAdd(&dL_dconic2D[4 * (size_t)my_gid + 0], v[2]);
-                atomicAdd(&dL_dconic2D[4 * (size_t)my_gid + 1], v[3]);
-                atomicAdd(&dL_dconic2D[4 * (size_t)my_gid + 3], v[4]);
+                const float mo = -my_con.w, ho = -0.5f * my_con.w;
+                atomicAdd(&dL_dmean2D[3 * (size_t)my_gid + 0], mo * ddelx_dx * (my_con.x * v[0] + my_con.y * v[1]));
+                atomicAdd(&dL_dmean2D[3 * (size_t)my_gid + 1], mo * ddely_dy * (my_con.z * v[1] + my_con.y * v[0]));
+                atomicAdd(&dL_dconic2D[4 * (size_t)my_gid + 0], ho * v[2]);
+                atomicAdd(&dL_dconic2D[4 * (size_t)my_gid + 1], ho * v[3]);
+                atomicAdd(&dL_dconic2D[4 * (size_t)my_gid + 3], ho * v[4]);
                 atomicAdd(&dL_dopacity[my_gid], v[5]);
                 atomicAdd(&dL_dcolors[3 * (size_t)my_gid + 0], v[6]);
                 atomicAdd(&dL_dcolors[3 * (size_t)my_gid + 1], v[7]);
@@ -252,6 +253,8 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
             if ((int)tid < cnt) {
                 const uint32_t id = sm.ids[s][mis + tid];
                 my_gid = indices ? __ldg(indices + id) : (int)id;
+                const SplatRec& r = sm.recs[s][tid];  // read now: the ring slot is refilled before this batch is flushed
+                my_con = make_float4(r.conx, r.cony, r.conz, r.opac);
             }
             pending = b;
         }
@@ -267,8 +270,8 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
             for (int k = 0; k < NV; k++) v[k] = 0.f;
             const float4 q0 = rp[0], q1 = rp[1], q2 = rp[2];
             bool contrib = false;
-            if (act0) contrib |= bwd_pair<LOD, DEPTH>(px[0], q0, q1, q2, ddelx_dx, ddely_dy, v);
-            if (act1) contrib |= bwd_pair<LOD, DEPTH>(px[1], q0, q1, q2, ddelx_dx, ddely_dy, v);
+            if (act0) contrib |= bwd_pair<LOD, DEPTH>(px[0], q0, q1, q2, v);
+            if (act1) contrib |= bwd_pair<LOD, DEPTH>(px[1], q0, q1, q2, v);
             if (!__any_sync(0xffffffffu, contrib)) continue;
             int slot;
             const float total = warp_reduce10(v, lane, slot);

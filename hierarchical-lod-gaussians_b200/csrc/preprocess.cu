@@ -37,14 +37,26 @@ struct PreParams {
     int32_t* radii;
     unsigned grid_x, grid_y;
     int sh_vec4;  // 1 when shs is 16-byte aligned and 3*M is a multiple of 4
+    int staged;   // 1 when the SH rows of a tile are staged through shared memory by one bulk copy
 };
 
 // Load the (D+1)^2 RGB coefficient triples of Gaussian `idx`, lerped with parent `pidx` by t when has_parent
 // (interp(), forward.cu:79-85: t*a + (1-t)*b per component).
-__device__ __forceinline__ void load_sh(const PreParams& p, int idx, int pidx, bool has_parent, float t, v3* sh) {
+__device__ __forceinline__ void load_sh(const PreParams& p, int idx, int pidx, bool has_parent, float t, v3* sh, const float4* sh_row,
+                                        uint64_t* bar) {
     const int ncoef = (p.D + 1) * (p.D + 1);
     const int nfloat = ncoef * 3;
     float* f = reinterpret_cast<float*>(sh);
+    if (sh_row) {  // staged by a bulk copy (see preprocess_fwd_kernel); never combined with LOD interpolation
+        mbar_wait(bar, 0);
+#pragma unroll
+        for (int k = 0; k < 12; k++)
+            if (k * 4 < nfloat) {
+                const float4 a = sh_row[k];
+                f[k * 4 + 0] = a.x; f[k * 4 + 1] = a.y; f[k * 4 + 2] = a.z; f[k * 4 + 3] = a.w;
+            }
+        return;
+    }
     const float* base = p.shs + (size_t)idx * p.M * 3;
     const float* pbase = p.shs + (size_t)pidx * p.M * 3;
     const float omt = 1.0f - t;
@@ -77,7 +89,7 @@ __device__ __forceinline__ void load_sh(const PreParams& p, int idx, int pidx, b
 
 // Everything preprocessCUDA does for one Gaussian; returns tiles_touched (0 = culled).
 __device__ __forceinline__ uint32_t preprocess_one(const PreParams& p, const GeomState& g, int t_idx, const float* view,
-                                                   const float* proj) {
+                                                   const float* proj, const float4* sh_row, uint64_t* bar) {
     const int r_idx = p.indices ? __ldg(p.indices + t_idx) : t_idx;
     p.radii[t_idx] = 0;
 
@@ -164,7 +176,7 @@ __device__ __forceinline__ uint32_t preprocess_one(const PreParams& p, const Geo
         float len = sqrtf(dx * dx + dy * dy + dz * dz);
         dx = dx / len; dy = dy / len; dz = dz / len;
         v3 sh[16];
-        load_sh(p, r_idx, p_idx, has_parent, t, sh);
+        load_sh(p, r_idx, p_idx, has_parent, t, sh, sh_row, bar);
         v3 result = sh_to_rgb(p.D, sh, dx, dy, dz);
         result.x += 0.5f; result.y += 0.5f; result.z += 0.5f;
         uint8_t cl = (result.x < 0 ? 1 : 0) | (result.y < 0 ? 2 : 0) | (result.z < 0 ? 4 : 0);
@@ -188,7 +200,21 @@ __global__ void __launch_bounds__(PRE_BLOCK) preprocess_fwd_kernel(const PrePara
     __shared__ unsigned s_warp_sum[PRE_BLOCK / 32];
     __shared__ unsigned long long s_prefix;
     __shared__ float s_view[16], s_proj[16];
-    if (threadIdx.x == 0) s_tile = atomicAdd(&g.hdr->ticket, 1);
+    __shared__ uint64_t s_bar;
+    extern __shared__ __align__(128) float4 sh_stage[];  // [256][3M/4] when p.staged
+    const int row4 = (p.M * 3) / 4;
+    if (threadIdx.x == 0) {
+        s_tile = atomicAdd(&g.hdr->ticket, 1);
+        if (p.staged) {
+            // the tile's SH rows are one contiguous block: a single bulk copy (TMA) that lands while the projection math runs
+            mbar_init(&s_bar, 1);
+            mbar_fence_init();
+            const int cnt = min(PRE_BLOCK, p.P - s_tile * PRE_BLOCK);
+            const unsigned bytes = (unsigned)cnt * (unsigned)row4 * 16u;
+            mbar_expect_tx(&s_bar, bytes);
+            bulk_g2s(sh_stage, p.shs + (size_t)s_tile * PRE_BLOCK * p.M * 3, bytes, &s_bar);
+        }
+    }
     if (threadIdx.x < 16) s_view[threadIdx.x] = __ldg(p.viewmatrix + threadIdx.x);
     else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = __ldg(p.projmatrix + threadIdx.x - 16);
     __syncthreads();
@@ -196,11 +222,12 @@ __global__ void __launch_bounds__(PRE_BLOCK) preprocess_fwd_kernel(const PrePara
     const int t_idx = tile * PRE_BLOCK + threadIdx.x;
     unsigned tiles = 0;
     if (t_idx < p.P) {
-        tiles = preprocess_one(p, g, t_idx, s_view, s_proj);
+        tiles = preprocess_one(p, g, t_idx, s_view, s_proj, p.staged ? sh_stage + threadIdx.x * row4 : nullptr, &s_bar);
         g.tiles_touched[t_idx] = tiles;
         // sort key of the depth-ordered emission: culled Gaussians go to the end of the order and emit nothing
         g.depth_keys[t_idx] = tiles ? __float_as_uint(g.depths[t_idx]) : 0xffffffffu;
     }
+    if (p.staged && threadIdx.x == 0) mbar_wait(&s_bar, 0);  // the copy must have landed before the CTA may retire
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned incl = tiles;
 #pragma unroll
@@ -291,7 +318,16 @@ extern "C" int lodgs_forward_preprocess(int P, int D, int M, int W, int H, const
     if (rotations && ((uintptr_t)rotations & 15) != 0) { set_error("lodgs_forward_preprocess: rotations must be 16-byte aligned"); return LODGS_E_ARG; }
     LODGS_CUDA(cudaMemsetAsync(geom_buffer, 0, g.zero_bytes, s));
     int tiles = (P + PRE_BLOCK - 1) / PRE_BLOCK;
-    preprocess_fwd_kernel<<<tiles, PRE_BLOCK, 0, s>>>(p, g);
+    const size_t stage_bytes = (size_t)PRE_BLOCK * M * 12;
+    p.staged = (shs && !indices && !parent_indices && p.sh_vec4 && (M * 12) % 16 == 0 && M <= 16) ? 1 : 0;
+    if (p.staged) {
+        static size_t attr_smem = 0;
+        if (stage_bytes > attr_smem) {
+            LODGS_CUDA(cudaFuncSetAttribute(preprocess_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stage_bytes));
+            attr_smem = stage_bytes;
+        }
+    }
+    preprocess_fwd_kernel<<<tiles, PRE_BLOCK, p.staged ? stage_bytes : 0, s>>>(p, g);
     LODGS_LAUNCHED("preprocess_fwd_kernel");
     // The count goes back to the host (the caller sizes the binning buffer from it, rasterizer_impl.cu:330-333) while the
     // GPU already orders the Gaussians by depth for the emission stage: the host waits on an event recorded right after

@@ -46,16 +46,57 @@ struct PreBwdParams {
 
 __device__ __forceinline__ float sq(float x) { return x * x; }
 
+template <bool STAGED>
+__device__ __forceinline__ void preprocess_bwd_one(const PreBwdParams& p, int t_idx, const float* view, const float* proj, float4* sh_row,
+                                                   uint64_t* bar);
+
+// STAGED (no index list, SH rows a multiple of 16 bytes): the CTA's 256 SH rows are one contiguous block of the parameter
+// array, so they arrive in shared memory by ONE bulk copy (TMA) issued before the covariance math, and the dL_dsh rows
+// leave the same buffer by ONE bulk store — instead of 12+12 strided 16-byte accesses per thread (192-byte stride).
+template <bool STAGED>
 __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams p) {
+    extern __shared__ __align__(128) float4 sh_stage[];  // [256][3M/4] when STAGED
     __shared__ float s_view[16], s_proj[16];
+    __shared__ uint64_t s_bar;
+    const int row4 = (p.M * 3) / 4;  // float4 per SH row
+    const int tile_base = blockIdx.x * blockDim.x;
+    const int tile_cnt = min((int)blockDim.x, p.P - tile_base);
     if (threadIdx.x < 16) s_view[threadIdx.x] = __ldg(p.viewmatrix + threadIdx.x);
     else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = __ldg(p.projmatrix + threadIdx.x - 16);
+    if (STAGED && threadIdx.x == 0) {
+        mbar_init(&s_bar, 1);
+        mbar_fence_init();
+        const unsigned bytes = (unsigned)tile_cnt * (unsigned)row4 * 16u;
+        mbar_expect_tx(&s_bar, bytes);
+        bulk_g2s(sh_stage, p.shs + (size_t)tile_base * p.M * 3, bytes, &s_bar);
+    }
     __syncthreads();
-    const int t_idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t_idx >= p.P || !(__ldg(p.radii + t_idx) > 0)) return;
+    const int t_idx = tile_base + threadIdx.x;
+    const bool active = t_idx < p.P && (__ldg(p.radii + t_idx) > 0);
+    if (STAGED) {
+        if (!active) {
+            // culled rows still travel with the block store: they carry the zeros the caller's zero-fill put there
+            mbar_wait(&s_bar, 0);
+            if (t_idx < p.P)
+                for (int k = 0; k < row4; k++) sh_stage[threadIdx.x * row4 + k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        } else {
+            preprocess_bwd_one<STAGED>(p, t_idx, s_view, s_proj, sh_stage + threadIdx.x * row4, &s_bar);
+        }
+        fence_async_smem();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            bulk_s2g(p.dL_dsh + (size_t)tile_base * p.M * 3, sh_stage, (unsigned)tile_cnt * (unsigned)row4 * 16u);
+            bulk_commit_wait_all();
+        }
+    } else {
+        if (active) preprocess_bwd_one<STAGED>(p, t_idx, s_view, s_proj, nullptr, nullptr);
+    }
+}
+
+template <bool STAGED>
+__device__ __forceinline__ void preprocess_bwd_one(const PreBwdParams& p, int t_idx, const float* view, const float* proj, float4* sh_row,
+                                                   uint64_t* bar) {
     const int idx = p.indices ? __ldg(p.indices + t_idx) : t_idx;
-    const float* view = s_view;
-    const float* proj = s_proj;
 
     // ---------------- 2D covariance / conic / AA-opacity backward (backward.cu:165-325) ----------------
     float cov6[6];
@@ -180,7 +221,15 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
         {
             float* f = reinterpret_cast<float*>(sh);
             const float* base = p.shs + (size_t)idx * p.M * 3;
-            if (p.sh_vec4) {
+            if (STAGED) {
+                mbar_wait(bar, 0);
+#pragma unroll
+                for (int k = 0; k < 12; k++)
+                    if (k * 4 < ncoef * 3) {
+                        float4 a = sh_row[k];
+                        f[4 * k] = a.x; f[4 * k + 1] = a.y; f[4 * k + 2] = a.z; f[4 * k + 3] = a.w;
+                    }
+            } else if (p.sh_vec4) {
 #pragma unroll
                 for (int k = 0; k < 12; k++)
                     if (k * 4 < ncoef * 3) {
@@ -223,7 +272,22 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
             }
         }
         // dL_dsh: LOD children's own SH gradient is discarded by the reference (backward.cu:489-493)
-        if (!is_child) {
+        if (STAGED) {
+            // the row is rebuilt in place (this thread is its only reader and writer); coefficients above the active degree are 0
+            float o[48];
+#pragma unroll
+            for (int k = 0; k < 16; k++) {
+                const float wk = k < ncoef ? w[k] : 0.f;
+                o[3 * k + 0] = wk * dRGB.x;
+                o[3 * k + 1] = wk * dRGB.y;
+                o[3 * k + 2] = wk * dRGB.z;
+            }
+            const int row4 = (p.M * 3) / 4;
+#pragma unroll
+            for (int k = 0; k < 12; k++)
+                if (k < row4) sh_row[k] = make_float4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
+            for (int k = 12; k < row4; k++) sh_row[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        } else if (!is_child) {
             float* out = p.dL_dsh + (size_t)idx * p.M * 3;
 #pragma unroll
             for (int k = 0; k < 16; k++)
@@ -297,7 +361,20 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
 }
 
 int launch_preprocess_bwd(const PreBwdParams& p, cudaStream_t s) {
-    preprocess_bwd_kernel<<<(p.P + 255) / 256, 256, 0, s>>>(p);
+    const size_t row_bytes = (size_t)p.M * 12;
+    const size_t smem = 256 * row_bytes;
+    const bool staged = p.shs && !p.indices && !p.parent_indices && p.sh_vec4 && row_bytes % 16 == 0 && p.M <= 16 && smem <= 160 * 1024 &&
+                        ((uintptr_t)p.dL_dsh & 15) == 0;
+    if (staged) {
+        static size_t attr_smem = 0;
+        if (smem > attr_smem) {
+            LODGS_CUDA(cudaFuncSetAttribute(preprocess_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            attr_smem = smem;
+        }
+        preprocess_bwd_kernel<true><<<(p.P + 255) / 256, 256, smem, s>>>(p);
+    } else {
+        preprocess_bwd_kernel<false><<<(p.P + 255) / 256, 256, 0, s>>>(p);
+    }
     LODGS_LAUNCHED("preprocess_bwd_kernel");
     return LODGS_OK;
 }
