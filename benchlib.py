@@ -229,11 +229,10 @@ def _work_model(arm, n_gauss):
         "preprocess_fwd_kernel": ("hbm", 20.0 * n_gauss + p_vis * (115.0 + 12.0 * M)),
         "sort_depth_hist_kernel": ("hbm", 4.0 * n_gauss),
         "sort_depth_pass_kernel": ("hbm", 16.0 * n_gauss),     # per launch (one 8-bit digit of the depth bits)
-        "scan_sorted_kernel": ("hbm", 12.0 * n_gauss),
-        "emit_tiles_kernel": ("hbm", 28.0 * n_gauss + 8.0 * R),
+        "scan_sorted_kernel": ("hbm", 16.0 * n_gauss),
+        "emit_balanced_kernel": ("hbm", 16.0 * n_gauss + 8.0 * R),
         "sort_tile_hist_kernel": ("hbm", 4.0 * R),
         "sort_tile_pass_kernel": ("hbm", 16.0 * R),            # per launch (one 8-bit digit of the tile id)
-        "tile_ranges_kernel": ("hbm", 4.0 * R),
         "build_records_kernel": ("hbm", (4.0 + 4.0 + 8.0 + 44.0 + 48.0) * R),
         "blend_fwd_kernel": ("fp32", 11.0 * n_test + 2.0 * n_alpha + 14.0 * n_blend),
         "blend_bwd_kernel": ("fp32", 70.0 * n_blend),

@@ -11,129 +11,147 @@
 
 namespace lodgs {
 
-// Inclusive scan of tiles_touched in depth order: sorted_offsets[pos] = sum_{q<=pos} tiles_touched[order[q]].
-// Single pass: 256-entry tiles in launch order (ticket), block scan, decoupled look-back.
-__global__ void __launch_bounds__(PRE_BLOCK) scan_sorted_kernel(int P, const uint32_t* __restrict__ order,
-                                                              const uint32_t* __restrict__ tiles_touched,
-                                                              uint32_t* __restrict__ sorted_offsets, unsigned long long* state,
-                                                              int* ticket) {
-    __shared__ int s_tile;
-    __shared__ unsigned s_warp_sum[PRE_BLOCK / 32];
-    __shared__ unsigned long long s_prefix;
-    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1);
-    __syncthreads();
-    const int tile = s_tile;
-    const int pos = tile * PRE_BLOCK + threadIdx.x;
-    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned v = 0;
-    if (pos < P) v = __ldg(tiles_touched + __ldg(order + pos));
-    unsigned incl = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= (unsigned)o) incl += t;
-    }
-    if (lane == 31) s_warp_sum[warp] = incl;
-    __syncthreads();
-    if (warp == 0) {
-        unsigned w = (lane < PRE_BLOCK / 32) ? s_warp_sum[lane] : 0;
-        unsigned wi = w;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            unsigned t = __shfl_up_sync(0xffffffffu, wi, o);
-            if (lane >= (unsigned)o) wi += t;
-        }
-        if (lane < PRE_BLOCK / 32) s_warp_sum[lane] = wi - w;
-        const unsigned block_total = __shfl_sync(0xffffffffu, wi, PRE_BLOCK / 32 - 1);
-        unsigned long long excl = 0;
-        if (tile == 0) {
-            if (lane == 0) st_relaxed(state, pack_state(2, block_total));
-        } else {
-            if (lane == 0) st_relaxed(state + tile, pack_state(1, block_total));
-            excl = lookback_warp(state, tile);
-            if (lane == 0) st_relaxed(state + tile, pack_state(2, excl + block_total));
-        }
-        if (lane == 0) s_prefix = excl;
-    }
-    __syncthreads();
-    if (pos < P) sorted_offsets[pos] = (unsigned)s_prefix + s_warp_sum[warp] + incl;
-}
-
 // Instance emission in depth order. The reference's duplicateWithKeys (rasterizer_impl.cu:70-115) emits 64-bit tile|depth
 // keys in index order and lets a 6-pass radix sort order them; here the P Gaussians are sorted by depth bits first (cheap:
 // P << R), instances are emitted in that order carrying only their tile id, and a stable sort on the tile id alone
 // (2 passes at 1080p) finishes the job: (tile, depth, index) order, i.e. exactly the reference's sorted list.
-// A warp flattens the rectangles of 32 consecutive Gaussians of the order into one run of output slots (their offsets are
-// consecutive in sorted_offsets), finds each slot's owner by a shuffle binary search and writes 32 consecutive entries
-// per instruction; slot -> (x,y) inside a rectangle is row-major like the reference.
-__global__ void __launch_bounds__(256) emit_tiles_kernel(int P, const uint32_t* __restrict__ order, const float2* __restrict__ means2D,
-                                                        const uint32_t* __restrict__ sorted_offsets, const uint32_t* __restrict__ tiles_touched,
-                                                        const int2* __restrict__ rects, unsigned grid_x, unsigned grid_y,
-                                                        uint32_t* __restrict__ tiles_out, uint32_t* __restrict__ vals) {
-    const unsigned lane = threadIdx.x & 31;
-    const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int base = warp_global * 32;
-    if (base >= P) return;
-    const int pos = base + lane;
-    unsigned count = 0, rminx = 0, rminy = 0, rw = 1, gid = 0;
-    if (pos < P) {
-        gid = __ldg(order + pos);
-        if (__ldg(tiles_touched + gid) > 0) {
-            uint2 rmin, rmax;
-            tile_rect(__ldg(means2D + gid), __ldg(rects + gid), rmin, rmax, grid_x, grid_y);
-            rminx = rmin.x; rminy = rmin.y;
-            rw = rmax.x - rmin.x;
-            count = rw * (rmax.y - rmin.y);
-            if (rw == 0) rw = 1;
-        }
-    }
-    // first output slot of this warp = sorted_offsets[base-1]; slots of the 32 Gaussians are consecutive
-    const unsigned warp_off = (base == 0) ? 0u : __ldg(sorted_offsets + base - 1);
-    unsigned incl = count;
+//
+//
+// Two kernels. scan_sorted_kernel: a CTA takes SCAN_TILE consecutive positions of the depth order, gathers their 8-byte
+// tile boxes and scans the tile counts (warp scans + decoupled look-back across CTAs, 32 predecessors per step) into
+// sorted_offsets. emit_balanced_kernel: work is split by OUTPUT slots, not by Gaussians — in depth order the nearest
+// Gaussians come first and cover hundreds of tiles each, so a per-Gaussian split leaves a few CTAs with most of the work.
+// A CTA owns EMIT_SLOTS consecutive output slots, finds the range of owning positions with two warp-wide 32-ary searches
+// in sorted_offsets, stages that range's offsets in shared memory, and every thread resolves its slots by a binary search
+// there. Slot -> (x,y) inside a rectangle is row-major like the reference.
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_TILE = SCAN_ITEMS * SCAN_THREADS;
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_sorted_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__ tile_box,
+                                                                  uint32_t* __restrict__ sorted_offsets, unsigned long long* state,
+                                                                  int* ticket) {
+    __shared__ int s_tile;
+    __shared__ unsigned s_warp_total[SCAN_THREADS / 32];
+    __shared__ unsigned long long s_prefix;
+    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1);
+    __syncthreads();
+    const int tile = s_tile;
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int wbase = tile * SCAN_TILE + (int)warp * (32 * SCAN_ITEMS);  // this warp owns 256 consecutive positions
+    unsigned gid[SCAN_ITEMS], cnt[SCAN_ITEMS];
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        unsigned v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= (unsigned)o) incl += v;
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        const int pos = wbase + k * 32 + (int)lane;
+        gid[k] = pos < P ? __ldg(order + pos) : 0u;
     }
-    const unsigned excl = incl - count;
-    const unsigned total = __shfl_sync(0xffffffffu, incl, 31);
-    for (unsigned s0 = 0; s0 < total; s0 += 32) {
-        const unsigned s = s0 + lane;
-        int lo = 0;
 #pragma unroll
-        for (int step = 16; step > 0; step >>= 1) {
-            int probe = lo + step;
-            unsigned v = __shfl_sync(0xffffffffu, excl, probe & 31);
-            if (probe < 32 && v <= s) lo = probe;
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        const int pos = wbase + k * 32 + (int)lane;
+        const uint2 b = pos < P ? __ldg(tile_box + gid[k]) : make_uint2(0u, 0u);
+        cnt[k] = ((b.y & 0xffffu) - (b.x & 0xffffu)) * ((b.y >> 16) - (b.x >> 16));
+    }
+    unsigned incl[SCAN_ITEMS];
+    unsigned run = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        unsigned v = cnt[k];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned t = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= (unsigned)o) v += t;
         }
-        const unsigned o_excl = __shfl_sync(0xffffffffu, excl, lo);
-        const unsigned o_minx = __shfl_sync(0xffffffffu, rminx, lo);
-        const unsigned o_miny = __shfl_sync(0xffffffffu, rminy, lo);
-        const unsigned o_w = __shfl_sync(0xffffffffu, rw, lo);
-        const unsigned o_gid = __shfl_sync(0xffffffffu, gid, lo);
-        if (s < total) {
-            const unsigned k = s - o_excl;
-            const unsigned y = o_miny + k / o_w, x = o_minx + k % o_w;
-            tiles_out[warp_off + s] = y * grid_x + x;
-            vals[warp_off + s] = o_gid;
+        incl[k] = run + v;
+        run += __shfl_sync(0xffffffffu, v, 31);
+    }
+    if (lane == 0) s_warp_total[warp] = run;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned block_total = 0;
+#pragma unroll
+        for (int w = 0; w < SCAN_THREADS / 32; w++) block_total += s_warp_total[w];
+        unsigned long long ex = 0;
+        if (tile == 0) {
+            if (lane == 0) st_relaxed(state, pack_state(2, block_total));
+        } else {
+            if (lane == 0) st_relaxed(state + tile, pack_state(1, block_total));
+            ex = lookback_warp(state, tile);
+            if (lane == 0) st_relaxed(state + tile, pack_state(2, ex + block_total));
         }
+        if (lane == 0) s_prefix = ex;
+    }
+    __syncthreads();
+    unsigned warp_off = (unsigned)s_prefix;
+    for (unsigned w = 0; w < warp; w++) warp_off += s_warp_total[w];
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        const int pos = wbase + k * 32 + (int)lane;
+        if (pos < P) sorted_offsets[pos] = warp_off + incl[k];
     }
 }
 
-__global__ void tile_ranges_kernel(int L, const uint32_t* __restrict__ tiles, uint2* __restrict__ ranges) {
-    int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= L) return;
-    const uint32_t cur = __ldg(tiles + idx);
-    if (idx == 0) {
-        ranges[cur].x = 0;
-    } else {
-        const uint32_t prev = __ldg(tiles + idx - 1);
-        if (cur != prev) {
-            ranges[prev].y = idx;
-            ranges[cur].x = idx;
+constexpr int EMIT_THREADS = 256;
+constexpr int EMIT_PER_THREAD = 8;
+constexpr int EMIT_SLOTS = EMIT_THREADS * EMIT_PER_THREAD;  // output slots per CTA; at most EMIT_SLOTS+1... owners, see below
+
+// Smallest position p in [0,P) with incl[p] > slot (incl is non-decreasing, incl[P-1] > slot guaranteed): 32-ary search by
+// one warp, 4 dependent loads for P = 1 M instead of 20.
+__device__ __forceinline__ unsigned warp_upper_bound(const uint32_t* __restrict__ incl, unsigned P, unsigned slot, unsigned lane) {
+    unsigned lo = 0, n = P;  // answer in [lo, lo+n)
+    while (n > 1) {
+        const unsigned step = (n + 31) / 32;
+        const unsigned probe = lo + min(n, (lane + 1) * step) - 1;  // last element of this lane's chunk
+        const bool gt = __ldg(incl + probe) > slot;
+        const unsigned m = __ballot_sync(0xffffffffu, gt);
+        const unsigned c = (unsigned)(__ffs(m) - 1);  // first chunk whose last element exceeds slot
+        const unsigned nlo = lo + min(n, c * step);
+        n = min(n, (c + 1) * step) - min(n, c * step);
+        lo = nlo;
+    }
+    return lo;
+}
+
+__global__ void __launch_bounds__(EMIT_THREADS) emit_balanced_kernel(int P, unsigned R, const uint32_t* __restrict__ order,
+                                                                    const uint2* __restrict__ tile_box,
+                                                                    const uint32_t* __restrict__ sorted_offsets, unsigned grid_x,
+                                                                    uint32_t* __restrict__ tiles_out, uint32_t* __restrict__ vals) {
+    __shared__ unsigned s_off[EMIT_SLOTS + 2];  // exclusive offset of every owner position in this CTA's range (+ sentinel)
+    __shared__ unsigned s_lo, s_hi;
+    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned slot0 = blockIdx.x * EMIT_SLOTS;
+    const unsigned slot1 = min(R, slot0 + EMIT_SLOTS);  // exclusive
+    if (warp == 0) {
+        const unsigned v = warp_upper_bound(sorted_offsets, (unsigned)P, slot0, lane);
+        if (lane == 0) s_lo = v;
+    } else if (warp == 1) {
+        const unsigned v = warp_upper_bound(sorted_offsets, (unsigned)P, slot1 - 1, lane);
+        if (lane == 0) s_hi = v;
+    }
+    __syncthreads();
+    const unsigned lo = s_lo, hi = s_hi;  // owners lo..hi; every visible Gaussian owns >= 1 slot, so hi - lo + 1 <= EMIT_SLOTS
+    const unsigned nown = min(hi - lo + 1, (unsigned)EMIT_SLOTS + 1u);  // (the clamp only guards against NaN-poisoned input)
+    for (unsigned i = tid; i <= nown; i += EMIT_THREADS) {
+        const unsigned p = lo + i;  // s_off[i] = exclusive offset of position lo+i = inclusive offset of lo+i-1
+        s_off[i] = (p == 0) ? 0u : __ldg(sorted_offsets + min(p, (unsigned)P) - 1);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < EMIT_PER_THREAD; k++) {
+        const unsigned s = slot0 + k * EMIT_THREADS + tid;
+        if (s >= slot1) break;
+        // largest i with s_off[i] <= s
+        unsigned a = 0, len = nown;
+        while (len > 1) {
+            const unsigned half = len >> 1;
+            if (s_off[a + half] <= s) { a += half; len -= half; } else { len = half; }
         }
-        // inside the else like the reference (:139-140): a list of exactly one instance keeps range.y == 0
-        if (idx == L - 1) ranges[cur].y = L;
+        const unsigned gid = __ldg(order + lo + a);
+        const uint2 b = __ldg(tile_box + gid);
+        const unsigned w = max((b.y & 0xffffu) - (b.x & 0xffffu), 1u);
+        const unsigned q = s - s_off[a];
+        const unsigned qy = q / w, qx = q - qy * w;
+        tiles_out[s] = ((b.x >> 16) + qy) * grid_x + (b.x & 0xffffu) + qx;
+        vals[s] = gid;
     }
 }
 
@@ -143,10 +161,26 @@ __global__ void __launch_bounds__(256) build_records_kernel(int R, int P, const 
                                                            const float2* __restrict__ means2D,
                                                            const float4* __restrict__ conic_opacity, const float* __restrict__ colors,
                                                            const float* __restrict__ depths, const float* __restrict__ ts,
-                                                           const int32_t* __restrict__ kids, SplatRec* __restrict__ recs) {
+                                                           const int32_t* __restrict__ kids, SplatRec* __restrict__ recs,
+                                                           uint2* __restrict__ ranges) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= R) return;
     const uint32_t id = __ldg(point_list + i);
+    // identifyTileRanges (rasterizer_impl.cu:120-142) on the way: ranges were cleared before the launch
+    {
+        const uint32_t cur = __ldg(tiles_sorted + i);
+        if (i == 0) {
+            ranges[cur].x = 0;
+        } else {
+            const uint32_t prev = __ldg(tiles_sorted + i - 1);
+            if (cur != prev) {
+                ranges[prev].y = i;
+                ranges[cur].x = i;
+            }
+            // inside the else like the reference (:139-140): a list of exactly one instance keeps range.y == 0
+            if (i == R - 1) ranges[cur].y = R;
+        }
+    }
     const float2 xy = __ldg(means2D + id);
     const float4 co = __ldg(conic_opacity + id);
     float4 a = {xy.x, xy.y, co.x, co.y};
@@ -157,6 +191,11 @@ __global__ void __launch_bounds__(256) build_records_kernel(int R, int P, const 
     if (ts != nullptr && kids != nullptr) {
         c.z = __ldg(ts + id);
         c.w = 1.0f / (float)__ldg(kids + id);
+    } else {
+        // without LOD the t slot carries a conservative cut-off for the quadratic form: power < cut  =>  opacity * exp(power)
+        // < 1/255, so the blend kernels skip the exponential for such pairs (margin >> the 2-ulp error of expf)
+        const float lim = -logf(255.0f * co.w);
+        c.z = lim - 1e-4f * (1.0f + fabsf(lim));
     }
     float4* out = reinterpret_cast<float4*>(recs + i);
     out[0] = a;
@@ -165,28 +204,22 @@ __global__ void __launch_bounds__(256) build_records_kernel(int R, int P, const 
 }
 
 int launch_scan_sorted(int P, const GeomState& g, cudaStream_t s) {
-    scan_sorted_kernel<<<(P + PRE_BLOCK - 1) / PRE_BLOCK, PRE_BLOCK, 0, s>>>(P, g.order, g.tiles_touched, g.sorted_offsets, g.scan2_state,
-                                                                           &g.hdr->ticket2);
+    scan_sorted_kernel<<<(P + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, s>>>(P, g.order, g.tile_box, g.sorted_offsets, g.scan2_state,
+                                                                               &g.hdr->ticket2);
     LODGS_LAUNCHED("scan_sorted_kernel");
     return LODGS_OK;
 }
-int launch_emit_tiles(int P, const GeomState& g, unsigned gx, unsigned gy, uint32_t* tiles, uint32_t* vals, cudaStream_t s) {
-    emit_tiles_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, g.order, g.means2D, g.sorted_offsets, g.tiles_touched, g.rects, gx, gy, tiles, vals);
-    LODGS_LAUNCHED("emit_tiles_kernel");
-    return LODGS_OK;
-}
-int launch_tile_ranges(int R, const uint32_t* keys, uint2* ranges, size_t ntiles, cudaStream_t s) {
-    LODGS_CUDA(cudaMemsetAsync(ranges, 0, ntiles * sizeof(uint2), s));
-    if (R > 0) {
-        tile_ranges_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, keys, ranges);
-        LODGS_LAUNCHED("tile_ranges_kernel");
-    }
+int launch_emit_balanced(int P, int R, const GeomState& g, unsigned gx, uint32_t* tiles, uint32_t* vals, cudaStream_t s) {
+    emit_balanced_kernel<<<(R + EMIT_SLOTS - 1) / EMIT_SLOTS, EMIT_THREADS, 0, s>>>(P, (unsigned)R, g.order, g.tile_box, g.sorted_offsets, gx,
+                                                                                   tiles, vals);
+    LODGS_LAUNCHED("emit_balanced_kernel");
     return LODGS_OK;
 }
 int launch_build_records(int R, int P, const BinningState& b, const GeomState& g, const float* colors, const float* ts,
-                         const int32_t* kids, cudaStream_t s) {
+                         const int32_t* kids, uint2* ranges, size_t ntiles, cudaStream_t s) {
+    LODGS_CUDA(cudaMemsetAsync(ranges, 0, ntiles * sizeof(uint2), s));
     build_records_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, P, b.point_list, b.tiles_sorted, b.keys, g.means2D, g.conic_opacity, colors,
-                                                        g.depths, ts, kids, b.recs);
+                                                        g.depths, ts, kids, b.recs, ranges);
     LODGS_LAUNCHED("build_records_kernel");
     return LODGS_OK;
 }

@@ -80,6 +80,7 @@ __device__ __forceinline__ bool bwd_pair(BwdPix& p, const float4 q0, const float
     const float quad = __fmaf_rn(dx, __fmul_rn(dx, q0.z), __fmul_rn(dy, __fmul_rn(dy, q1.x)));
     const float power = __fsub_rn(__fmul_rn(quad, -0.5f), __fmul_rn(dy, __fmul_rn(dx, q0.w)));
     if (power > 0.0f) return false;
+    if (!LOD && power < q2.z) return false;  // certainly below the 1/255 cut (see build_records_kernel)
     const float G = expf(power);  // same expf as the forward: the contributor set is decided by identical alphas
     const float test_alpha = __fmul_rn(q1.y, G);
     const bool nullalpha = test_alpha > 0.99f;

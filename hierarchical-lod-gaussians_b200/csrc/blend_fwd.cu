@@ -36,6 +36,7 @@ __device__ __forceinline__ void blend_pair(PixState& p, unsigned& done, const fl
     const float quad = __fmaf_rn(dx, __fmul_rn(dx, q0.z), __fmul_rn(dy, __fmul_rn(dy, q1.x)));
     const float power = __fsub_rn(__fmul_rn(quad, -0.5f), __fmul_rn(dy, __fmul_rn(dx, q0.w)));
     if (power > 0.0f) return;
+    if (!LOD && power < q2.z) return;  // alpha is certainly below 1/255 (cut-off precomputed per splat, see build_records_kernel)
     float alpha = fminf(0.99f, __fmul_rn(q1.y, expf(power)));
     if (LOD) {
         const float kidsqrt_alpha = __fsub_rn(1.0f, __powf(__fsub_rn(1.0f, alpha), q2.w));

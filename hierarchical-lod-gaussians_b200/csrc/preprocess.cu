@@ -15,6 +15,7 @@ namespace lodgs {
 int sort_pairs32_device(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* keys_out, uint32_t* vals_out, uint32_t* keys_tmp,
                         uint32_t* vals_tmp, int n, int begin_bit, int end_bit, void* ws, cudaStream_t s, const char* pass_name,
                         const char* hist_name);
+
 int launch_scan_sorted(int P, const GeomState& g, cudaStream_t s);
 
 struct PreParams {
@@ -89,7 +90,7 @@ __device__ __forceinline__ void load_sh(const PreParams& p, int idx, int pidx, b
 
 // Everything preprocessCUDA does for one Gaussian; returns tiles_touched (0 = culled).
 __device__ __forceinline__ uint32_t preprocess_one(const PreParams& p, const GeomState& g, int t_idx, const float* view,
-                                                   const float* proj, const float4* sh_row, uint64_t* bar) {
+                                                   const float* proj, const float4* sh_row, uint64_t* bar, uint2& box) {
     const int r_idx = p.indices ? __ldg(p.indices + t_idx) : t_idx;
     p.radii[t_idx] = 0;
 
@@ -168,6 +169,7 @@ __device__ __forceinline__ uint32_t preprocess_one(const PreParams& p, const Geo
     g.rects[t_idx] = my_rect;
     tile_rect(point_image, my_rect, rmin, rmax, p.grid_x, p.grid_y);
     if ((rmax.x - rmin.x) * (rmax.y - rmin.y) == 0) return 0;
+    box = make_uint2(rmin.x | (rmin.y << 16), rmax.x | (rmax.y << 16));
 
     if (p.colors_precomp == nullptr) {
         // view direction from the UN-interpolated mean of r_idx (forward.cu:92: means[idx])
@@ -222,8 +224,10 @@ __global__ void __launch_bounds__(PRE_BLOCK) preprocess_fwd_kernel(const PrePara
     const int t_idx = tile * PRE_BLOCK + threadIdx.x;
     unsigned tiles = 0;
     if (t_idx < p.P) {
-        tiles = preprocess_one(p, g, t_idx, s_view, s_proj, p.staged ? sh_stage + threadIdx.x * row4 : nullptr, &s_bar);
+        uint2 box = make_uint2(0u, 0u);
+        tiles = preprocess_one(p, g, t_idx, s_view, s_proj, p.staged ? sh_stage + threadIdx.x * row4 : nullptr, &s_bar, box);
         g.tiles_touched[t_idx] = tiles;
+        g.tile_box[t_idx] = tiles ? box : make_uint2(0u, 0u);
         // sort key of the depth-ordered emission: culled Gaussians go to the end of the order and emit nothing
         g.depth_keys[t_idx] = tiles ? __float_as_uint(g.depths[t_idx]) : 0xffffffffu;
     }

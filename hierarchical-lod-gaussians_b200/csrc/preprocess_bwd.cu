@@ -361,10 +361,8 @@ __device__ __forceinline__ void preprocess_bwd_one(const PreBwdParams& p, int t_
 }
 
 int launch_preprocess_bwd(const PreBwdParams& p, cudaStream_t s) {
-    const size_t row_bytes = (size_t)p.M * 12;
-    const size_t smem = 256 * row_bytes;
-    const bool staged = p.shs && !p.indices && !p.parent_indices && p.sh_vec4 && row_bytes % 16 == 0 && p.M <= 16 && smem <= 160 * 1024 &&
-                        ((uintptr_t)p.dL_dsh & 15) == 0;
+    const size_t smem = 256 * (size_t)p.M * 12;
+    const bool staged = lodgs_backward_overwrites_dsh(p.M, p.indices != nullptr, p.parent_indices != nullptr, p.shs, p.dL_dsh) != 0;
     if (staged) {
         static size_t attr_smem = 0;
         if (smem > attr_smem) {
@@ -401,3 +399,10 @@ int run_preprocess_bwd(int P, int D, int M, const int32_t* indices, const int32_
     return launch_preprocess_bwd(p, s);
 }
 }  // namespace lodgs
+
+// 1 when lodgs_backward takes the staged path of preprocess_bwd_kernel, which writes EVERY row of dL_dsh[0..P) (zeros for
+// culled Gaussians): the caller may then skip the zero-fill of that tensor (192 B per Gaussian at M = 16).
+extern "C" int lodgs_backward_overwrites_dsh(int M, int has_indices, int has_parents, const float* shs, const float* dL_dsh) {
+    return (shs && dL_dsh && !has_indices && !has_parents && M > 0 && M <= 16 && (M * 12) % 16 == 0 && ((uintptr_t)shs & 15) == 0 &&
+            ((uintptr_t)dL_dsh & 15) == 0) ? 1 : 0;
+}

@@ -77,11 +77,12 @@ struct SortSmem {
     unsigned digit_start[SORT_RADIX];            // exclusive scan of the tile's digit counts
     unsigned out_off[SORT_RADIX];                // global base of digit d minus digit_start[d]
     unsigned scan_w[SORT_WARPS];
+    unsigned scan_h[SORT_WARPS];
     int tile;
 };
 
 template <typename KeyT>
-__global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const KeyT* __restrict__ keys_in,
+__global__ void __launch_bounds__(SORT_THREADS, sizeof(KeyT) == 4 ? 4 : 2) sort_onesweep_kernel(const KeyT* __restrict__ keys_in,
                                                                     const uint32_t* __restrict__ vals_in,
                                                                     KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                                                                     int n, int shift, const unsigned* __restrict__ hist_base,
@@ -98,7 +99,6 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const KeyT*
 
     // ---- load, warp-striped: item k of lane l in warp w is element w*512 + k*32 + l of the tile
     KeyT key[SORT_ITEMS];
-    uint32_t val[SORT_ITEMS];
     unsigned rank[SORT_ITEMS];
     const int wbase = warp * (32 * SORT_ITEMS);
 #pragma unroll
@@ -106,10 +106,8 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const KeyT*
         const int e = wbase + k * 32 + lane;
         if (e < tile_n) {
             key[k] = __ldg(keys_in + tile_base + e);
-            val[k] = vals_in ? __ldg(vals_in + tile_base + e) : (uint32_t)(tile_base + e);
         } else {
             key[k] = ~(KeyT)0;
-            val[k] = 0;
         }
     }
     // ---- rank inside the warp, item by item (index order => stable)
@@ -168,16 +166,35 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const KeyT*
             }
             atomicExch(my, (2u << 30) | (excl + count));
         }
+        // global base of digit d = exclusive scan of the pass' raw histogram, done here by every CTA (256 values) instead
+        // of a separate launch
+        const unsigned hraw = __ldg(hist_base + d);
+        unsigned hincl = hraw;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned t = __shfl_up_sync(0xffffffffu, hincl, o);
+            if (lane >= (unsigned)o) hincl += t;
+        }
+        if (lane == 31) sm.scan_h[warp] = hincl;
         __syncthreads();
-        unsigned woff = 0;
-        for (unsigned w = 0; w < warp; w++) woff += sm.scan_w[w];
+        unsigned woff = 0, hoff = 0;
+        for (unsigned w = 0; w < warp; w++) {
+            woff += sm.scan_w[w];
+            hoff += sm.scan_h[w];
+        }
         const unsigned dstart = woff + incl - count;
         sm.digit_start[d] = dstart;
-        sm.out_off[d] = __ldg(hist_base + d) + excl - dstart;  // modular arithmetic: dst = out_off[d] + local index
+        sm.out_off[d] = (hoff + hincl - hraw) + excl - dstart;  // modular arithmetic: dst = out_off[d] + local index
     }
     __syncthreads();
 
-    // ---- reorder inside the tile through shared memory
+    // ---- reorder inside the tile through shared memory; values are only read now (16 fewer live registers while ranking)
+    uint32_t val[SORT_ITEMS];
+#pragma unroll
+    for (int k = 0; k < SORT_ITEMS; k++) {
+        const int e = wbase + k * 32 + lane;
+        val[k] = (e < tile_n && vals_in) ? __ldg(vals_in + tile_base + e) : (uint32_t)(tile_base + e);
+    }
 #pragma unroll
     for (int k = 0; k < SORT_ITEMS; k++) {
         const int e = wbase + k * 32 + lane;
@@ -215,11 +232,10 @@ int sort_pairs_device_t(const KeyT* keys_in, const uint32_t* vals_in, KeyT* keys
         LODGS_CUDA(cudaFuncSetAttribute(sort_onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem<KeyT>)));
         attr_set = true;
     }
-    int hist_blocks = (int)min((size_t)148 * 8, ((size_t)n + 255) / 256);
+    // two CTAs per SM: every CTA ends with up to passes*256 global atomics, so more CTAs only add same-address contention
+    int hist_blocks = (int)min((size_t)148 * 2, ((size_t)n + 255) / 256);
     sort_histogram_kernel<KeyT><<<hist_blocks, 256, 0, s>>>(keys_in, n, passes, begin_bit, w.hist);
     LODGS_LAUNCHED(hist_name);
-    sort_scan_hist_kernel<<<passes, SORT_RADIX, 0, s>>>(w.hist);
-    LODGS_LAUNCHED("sort_scan_hist_kernel");
     const KeyT* kin = keys_in;
     const uint32_t* vin = vals_in;
     for (int p = 0; p < passes; p++) {

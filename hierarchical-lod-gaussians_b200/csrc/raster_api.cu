@@ -3,13 +3,12 @@
 #include "state.cuh"
 
 namespace lodgs {
-int launch_emit_tiles(int P, const GeomState& g, unsigned gx, unsigned gy, uint32_t* tiles, uint32_t* vals, cudaStream_t s);
-int launch_tile_ranges(int R, const uint32_t* tiles, uint2* ranges, size_t ntiles, cudaStream_t s);
+int launch_emit_balanced(int P, int R, const GeomState& g, unsigned gx, uint32_t* tiles, uint32_t* vals, cudaStream_t s);
 int sort_pairs32_device(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* keys_out, uint32_t* vals_out, uint32_t* keys_tmp,
                         uint32_t* vals_tmp, int n, int begin_bit, int end_bit, void* ws, cudaStream_t s, const char* pass_name,
                         const char* hist_name);
 int launch_build_records(int R, int P, const BinningState& b, const GeomState& g, const float* colors, const float* ts,
-                         const int32_t* kids, cudaStream_t s);
+                         const int32_t* kids, uint2* ranges, size_t ntiles, cudaStream_t s);
 int sort_pairs_device(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, uint64_t* keys_tmp,
                       uint32_t* vals_tmp, int n, int end_bit, void* ws, cudaStream_t s);
 int launch_blend_fwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, int W, int H, const float* bg,
@@ -83,17 +82,15 @@ extern "C" int lodgs_forward_render(int P, int W, int H, int R, const float* bac
         if (((uintptr_t)binning_buffer & 127) != 0) { set_error("lodgs_forward_render: binning buffer must be 128-byte aligned"); return LODGS_E_ARG; }
         GeomState g = geom_from_chunk(geom_buffer, P);
         bf = binning_full(binning_buffer, R);
-        // stage 1 left the Gaussians ordered by (depth bits, index) in g.order with their tile counts scanned in that order
-        int rc = launch_emit_tiles(P, g, gx, gy, bf.b.tiles_unsorted, bf.b.vals_unsorted, s);
+        // stage 1 left the Gaussians ordered by (depth bits, index) in g.order and their tile counts scanned in that order
+        int rc = launch_emit_balanced(P, R, g, gx, bf.b.tiles_unsorted, bf.b.vals_unsorted, s);
         if (rc) return rc;
         const int bit = (int)higher_msb(gx * gy);
         rc = sort_pairs32_device(bf.b.tiles_unsorted, bf.b.vals_unsorted, bf.b.tiles_sorted, bf.b.point_list, bf.keys_tmp, bf.vals_tmp, R, 0,
                                  bit, bf.b.sort_ws, s, "sort_tile_pass_kernel", "sort_tile_hist_kernel");
         if (rc) return rc;
-        rc = launch_tile_ranges(R, bf.b.tiles_sorted, img.ranges, (size_t)gx * gy, s);
-        if (rc) return rc;
         const float* colors = colors_precomp ? colors_precomp : g.rgb;
-        rc = launch_build_records(R, P, bf.b, g, colors, ts, kids, s);
+        rc = launch_build_records(R, P, bf.b, g, colors, ts, kids, img.ranges, (size_t)gx * gy, s);
         if (rc) return rc;
     } else {
         // The reference returns before rendering when nothing is visible (rasterizer_impl.cu:332-333), leaving the

@@ -44,8 +44,9 @@ struct GeomState {
     uint32_t* order;                 // [P] list positions in (depth bits, index) order
     uint32_t* sort_tmp_k;            // [P] ping-pong
     uint32_t* sort_tmp_v;            // [P]
-    uint32_t* sorted_offsets;        // [P] inclusive scan of tiles_touched[order[.]]
-    unsigned long long* scan2_state; // [ceil(P/PRE_BLOCK)+1] look-back states of that scan
+    uint32_t* sorted_offsets;        // [P] inclusive scan of the tile counts in depth order
+    uint2* tile_box;                 // [P] tile rectangle {min.x | min.y<<16, max.x | max.y<<16}, 0 for culled Gaussians
+    unsigned long long* scan2_state; // [ceil(P/PRE_BLOCK)+1] look-back states of the emission's scan
     void* sort_ws;                   // radix sort workspace for P pairs
     size_t offsets[9];
     size_t bytes;
@@ -83,6 +84,7 @@ static inline GeomState geom_from_chunk(void* chunk, size_t P) {
     g.sort_tmp_k = carve_arr<uint32_t>(b, off, P);
     g.sort_tmp_v = carve_arr<uint32_t>(b, off, P);
     g.sorted_offsets = carve_arr<uint32_t>(b, off, P);
+    g.tile_box = carve_arr<uint2>(b, off, P);
     off = align_up(off, 128);
     g.sort_ws = b + off;
     off += sort_ws_bytes(P);

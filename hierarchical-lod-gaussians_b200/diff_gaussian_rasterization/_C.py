@@ -34,9 +34,11 @@ def rasterize_gaussians(background, indices, parent_indices, ts, kids, means3D, 
         raise RuntimeError("lodgs rasterizer needs CUDA tensors (there is no CPU path)")
     P = means3D.size(0) if indices.numel() == 0 else indices.size(0)
     H, W = int(image_height), int(image_width)
-    out_color = torch.zeros((NUM_CHANNELS, H, W), dtype=torch.float32, device=dev)
-    out_invdepth = torch.zeros((1 if do_depth else 0, H, W), dtype=torch.float32, device=dev)
-    radii = torch.zeros((P,), dtype=torch.int32, device=dev)
+    # the blend writes every pixel and the preprocess every radius, so these are not pre-filled; they are zeroed below only
+    # when nothing is rendered (the reference returns its zero-filled tensors in that case, rasterizer_impl.cu:332-333)
+    out_color = torch.empty((NUM_CHANNELS, H, W), dtype=torch.float32, device=dev)
+    out_invdepth = torch.empty((1 if do_depth else 0, H, W), dtype=torch.float32, device=dev)
+    radii = torch.empty((P,), dtype=torch.int32, device=dev)
     seen = torch.zeros((P,), dtype=torch.int32, device=dev)
     geom = torch.empty(0, dtype=torch.uint8, device=dev)
     binning = torch.empty(0, dtype=torch.uint8, device=dev)
@@ -66,6 +68,11 @@ def rasterize_gaussians(background, indices, parent_indices, ts, kids, means3D, 
                                            ptr(out_color), ptr(out_invdepth) if do_depth else None, ptr(seen), stream))
         if debug:
             torch.cuda.synchronize()
+    if rendered == 0:
+        out_color.zero_()
+        out_invdepth.zero_()
+        if P == 0:
+            radii.zero_()
     return rendered, out_color, radii, geom, binning, img, out_invdepth, seen
 
 
@@ -81,7 +88,11 @@ def rasterize_gaussians_backward(background, indices, parent_indices, ts, kids, 
     z = lambda *shape: torch.zeros(shape, dtype=torch.float32, device=dev)  # noqa: E731
     dL_dmeans3D, dL_dmeans2D, dL_dcolors = z(fullP, 3), z(fullP, 3), z(fullP, NUM_CHANNELS)
     dL_dconic, dL_dopacity, dL_dcov3D = z(fullP, 2, 2), z(fullP, 1), z(fullP, 6)
-    dL_dsh, dL_dscales, dL_drotations = z(fullP, M, 3), z(fullP, 3), z(fullP, 4)
+    dL_dscales, dL_drotations = z(fullP, 3), z(fullP, 4)
+    dL_dsh = torch.empty((fullP, M, 3), dtype=torch.float32, device=dev)
+    if not (P != 0 and sh.numel() and sh.device == dev and sh.is_contiguous() and
+            lib.lodgs_backward_overwrites_dsh(M, int(indices.numel() != 0), int(parent_indices.numel() != 0), ptr(sh), ptr(dL_dsh))):
+        dL_dsh.zero_()
     has_depth = dL_dout_invdepth is not None and dL_dout_invdepth.numel() != 0
     dL_dinvdepths = z(fullP, 1) if has_depth else z(0, 1)
     if P != 0:

@@ -153,6 +153,11 @@ int lodgs_backward(int P, int fullP, int D, int M, int R, int W, int H, const fl
                    float* dL_dinvdepth, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
                    float* dL_dscale, float* dL_drot, void* stream);
 
+/* 1 when lodgs_backward will write every row of dL_dsh[0..P) itself (no index list, SH rows a multiple of 16 bytes, 16-byte
+ * aligned pointers): the caller may then pass an uninitialised dL_dsh instead of the zero-filled one the reference
+ * allocates (rasterize_points.cu:183). */
+int lodgs_backward_overwrites_dsh(int M, int has_indices, int has_parents, const float* shs, const float* dL_dsh);
+
 /* checkFrustum (HR rasterizer_impl.cu:54-66,145-157): present[i] = (view-space z > 0.2). present is u8[P]. */
 int lodgs_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                        uint8_t* present, void* stream);
