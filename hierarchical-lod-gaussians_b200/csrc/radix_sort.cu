@@ -25,21 +25,33 @@ __global__ void __launch_bounds__(256) sort_histogram_kernel(const KeyT* __restr
     for (int i = threadIdx.x; i < passes * SORT_RADIX; i += blockDim.x) s_hist[i] = 0;
     __syncthreads();
     const unsigned lane = threadIdx.x & 31;
-    // warp-uniform trip count so the shuffles below are always executed by full warps
-    const int stride = gridDim.x * blockDim.x;
-    for (int base = blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < n; base += stride) {
-        const int i = base + lane;
-        const bool valid = i < n;
-        const KeyT key = valid ? __ldg(keys + i) : (KeyT)0;
-        const unsigned vmask = __ballot_sync(0xffffffffu, valid);
-        for (int p = 0; p < passes; p++) {
-            const unsigned d = (unsigned)(key >> (begin_bit + 8 * p)) & 255u;
-            const unsigned d0 = __shfl_sync(0xffffffffu, d, 0);
-            // degenerate digits (tile high byte, float exponent) are warp-uniform almost always: one add
-            if (__all_sync(0xffffffffu, !valid || d == d0)) {
-                if (lane == 0) atomicAdd(&s_hist[p * SORT_RADIX + d0], __popc(vmask));
-            } else if (valid) {
-                atomicAdd(&s_hist[p * SORT_RADIX + d], 1u);
+    // warp-uniform trip count so the shuffles below are always executed by full warps; HIST_UNROLL independent loads are in
+    // flight per thread (one load per iteration leaves the kernel latency-bound)
+    constexpr int HIST_UNROLL = 8;
+    const int stride = gridDim.x * blockDim.x * HIST_UNROLL;
+    for (int base = (blockIdx.x * blockDim.x + (threadIdx.x & ~31)) * HIST_UNROLL; base < n; base += stride) {
+        KeyT keyv[HIST_UNROLL];
+#pragma unroll
+        for (int u = 0; u < HIST_UNROLL; u++) {
+            const int i = base + u * 32 + lane;
+            keyv[u] = i < n ? __ldg(keys + i) : (KeyT)0;
+        }
+#pragma unroll
+        for (int u = 0; u < HIST_UNROLL; u++) {
+            const int i = base + u * 32 + lane;
+            const bool valid = i < n;
+            const KeyT key = keyv[u];
+            const unsigned vmask = __ballot_sync(0xffffffffu, valid);
+            if (vmask == 0u) break;
+            for (int p = 0; p < passes; p++) {
+                const unsigned d = (unsigned)(key >> (begin_bit + 8 * p)) & 255u;
+                const unsigned d0 = __shfl_sync(0xffffffffu, d, __ffs(vmask) - 1);
+                // degenerate digits (tile high byte, float exponent) are warp-uniform almost always: one add
+                if (__all_sync(0xffffffffu, !valid || d == d0)) {
+                    if (lane == 0) atomicAdd(&s_hist[p * SORT_RADIX + d0], __popc(vmask));
+                } else if (valid) {
+                    atomicAdd(&s_hist[p * SORT_RADIX + d], 1u);
+                }
             }
         }
     }
@@ -232,8 +244,7 @@ int sort_pairs_device_t(const KeyT* keys_in, const uint32_t* vals_in, KeyT* keys
         LODGS_CUDA(cudaFuncSetAttribute(sort_onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem<KeyT>)));
         attr_set = true;
     }
-    // two CTAs per SM: every CTA ends with up to passes*256 global atomics, so more CTAs only add same-address contention
-    int hist_blocks = (int)min((size_t)148 * 2, ((size_t)n + 255) / 256);
+    int hist_blocks = (int)min((size_t)148 * 4, ((size_t)n + 2047) / 2048);
     sort_histogram_kernel<KeyT><<<hist_blocks, 256, 0, s>>>(keys_in, n, passes, begin_bit, w.hist);
     LODGS_LAUNCHED(hist_name);
     const KeyT* kin = keys_in;
