@@ -80,29 +80,39 @@ __device__ __forceinline__ void st_relaxed(unsigned long long* p, unsigned long 
     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-// Look back from tile `tile` (>0) for the exclusive prefix; called by one full warp. Returns the
-// exclusive prefix to all lanes.
+// Look back from tile `tile` (>0) for the exclusive prefix; called by one full warp. Returns the exclusive prefix to all
+// lanes. Every lane inspects LB_PER_LANE consecutive predecessors per step (1: a wider window was measured and only adds
+// polling traffic on the few L2 lines that hold the youngest states).
+constexpr int LB_PER_LANE = 1;
 __device__ __forceinline__ unsigned long long lookback_warp(const unsigned long long* state, int tile) {
     const unsigned lane = threadIdx.x & 31;
     unsigned long long exclusive = 0;
     int base = tile - 1;
     while (true) {
-        int idx = base - (int)lane;
-        unsigned long long s = pack_state(2, 0);  // virtual tile before 0: inclusive prefix 0
-        if (idx >= 0) {
-            do { s = ld_relaxed(state + idx); } while ((s >> 62) == 0);
+        // predecessor number p = lane*LB_PER_LANE + k of this window is tile base - p (p = 0 is the nearest)
+        unsigned long long local = 0;
+        bool found = false;
+#pragma unroll
+        for (int k = 0; k < LB_PER_LANE; k++) {
+            const int idx = base - ((int)lane * LB_PER_LANE + k);
+            unsigned long long s = pack_state(2, 0);  // virtual tile before 0: inclusive prefix 0
+            if (idx >= 0) {
+                do { s = ld_relaxed(state + idx); } while ((s >> 62) == 0);
+            }
+            if (!found) {
+                local += s & ((1ull << 62) - 1);
+                found = (s >> 62) == 2;
+            }
         }
-        unsigned flag = (unsigned)(s >> 62);
-        unsigned long long val = s & ((1ull << 62) - 1);
-        unsigned incl_mask = __ballot_sync(0xffffffffu, flag == 2);
-        // lanes strictly before (closer to us than) the first inclusive one contribute aggregates
-        int first = incl_mask ? (__ffs(incl_mask) - 1) : 32;
-        unsigned long long contrib = ((int)lane <= first) ? val : 0ull;
+        const unsigned incl_mask = __ballot_sync(0xffffffffu, found);
+        // lanes before the first one that met an inclusive prefix contribute all their aggregates, that lane its partial sum
+        const int first = incl_mask ? (__ffs(incl_mask) - 1) : 32;
+        unsigned long long contrib = ((int)lane <= first) ? local : 0ull;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, o);
         exclusive += contrib;
         if (incl_mask) break;
-        base -= 32;
+        base -= 32 * LB_PER_LANE;
     }
     return exclusive;
 }

@@ -67,51 +67,83 @@ struct CutHeader {
 
 constexpr int CUT_BLOCK = 512;
 
-__global__ void __launch_bounds__(CUT_BLOCK) cut_flat_kernel(const int32_t* __restrict__ nodes, const float* __restrict__ boxes,
-                                                            int N, float tau, const float* __restrict__ viewpoint,
-                                                            int32_t* __restrict__ render_indices,
-                                                            int32_t* __restrict__ parent_indices,
-                                                            int32_t* __restrict__ node_ids, int capacity, CutHeader* hdr,
-                                                            unsigned long long* tile_state) {
+// Flat rule, one pass. A tile is FLAT_TILE = 4096 consecutive nodes handled by 512 threads in 8 rows: thread t owns
+// nodes t, t+512, ... (box loads are fully coalesced 16-byte loads, the 28-byte records of a warp are 896 contiguous
+// bytes served from L1 after the first touch; output rows are coalesced). Counts are scanned in node order, the tile's
+// global offset comes from a decoupled look-back, entries are scattered in ascending node-id order.
+// Tile size matters more than anything else here: every tile publishes/polls look-back states that live on a few L2
+// lines, and with 512-node tiles that polling (not HBM) bounded the kernel at ~60 tiles/us whatever the staging scheme
+// (TMA-staged records, persistent prefetching CTAs and wider look-back windows were all measured, profiles/).
+constexpr int FLAT_THREADS = 512;
+constexpr int FLAT_ROWS = 8;
+constexpr int FLAT_TILE = FLAT_THREADS * FLAT_ROWS;
+constexpr int FLAT_PARTS = FLAT_ROWS * (FLAT_THREADS / 32);  // 64 (row, warp) partial sums per tile
+
+__global__ void __launch_bounds__(FLAT_THREADS, 2) cut_flat_kernel(const int32_t* __restrict__ nodes, const float* __restrict__ boxes,
+                                                                  int N, float tau, const float* __restrict__ viewpoint,
+                                                                  int32_t* __restrict__ render_indices,
+                                                                  int32_t* __restrict__ parent_indices,
+                                                                  int32_t* __restrict__ node_ids, int capacity, CutHeader* hdr,
+                                                                  unsigned long long* tile_state) {
     __shared__ int s_tile;
-    __shared__ int s_warp_sum[CUT_BLOCK / 32];
+    __shared__ int s_part[FLAT_PARTS];  // per (row, warp) totals -> exclusive offsets
     __shared__ unsigned long long s_prefix;
-    if (threadIdx.x == 0) s_tile = atomicAdd(&hdr->ticket, 1);
+    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_tile = atomicAdd(&hdr->ticket, 1);
     __syncthreads();
     const int tile = s_tile;
-    const int i = tile * CUT_BLOCK + threadIdx.x;
+    const int base = tile * FLAT_TILE;
+    const int cnt = min(FLAT_TILE, N - base);
     const float vx = __ldg(viewpoint), vy = __ldg(viewpoint + 1), vz = __ldg(viewpoint + 2);
 
-    int count = 0;
-    NodeRec n;
-    n.start = 0; n.parent = -1;
-    if (i < N) {
-        n = load_node(nodes, i);
-        const float4* b = reinterpret_cast<const float4*>(boxes) + (size_t)i * 2;
-        float size = node_size(__ldg(b), __ldg(b + 1), vx, vy, vz);
-        count = render_count(n, size, boxes, tau, vx, vy, vz);
-    }
-    // block-wide exclusive scan of count
-    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    int incl = count;
+    int count[FLAT_ROWS], start[FLAT_ROWS], pgauss[FLAT_ROWS], incl[FLAT_ROWS];
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        int t = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= (unsigned)o) incl += t;
+    for (int r = 0; r < FLAT_ROWS; r++) {
+        const int j = r * FLAT_THREADS + (int)tid;
+        count[r] = 0; start[r] = 0; pgauss[r] = -1;
+        if (j < cnt) {
+            const int i = base + j;
+            const float4* b = reinterpret_cast<const float4*>(boxes) + (size_t)i * 2;
+            const float4 bmin = __ldg(b), bmax = __ldg(b + 1);
+            const NodeRec n = load_node(nodes, i);
+            // the parent's Gaussian id is needed by every emitted entry: fetch it now, off the critical path
+            if (n.parent != -1) pgauss[r] = __ldg(nodes + (size_t)n.parent * 7 + 2);
+            const float size = node_size(bmin, bmax, vx, vy, vz);
+            count[r] = render_count(n, size, boxes, tau, vx, vy, vz);
+            start[r] = n.start;
+        }
+        int v = count[r];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int t = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= (unsigned)o) v += t;
+        }
+        incl[r] = v;
+        if (lane == 31) s_part[r * (FLAT_THREADS / 32) + warp] = v;
     }
-    if (lane == 31) s_warp_sum[warp] = incl;
     __syncthreads();
     if (warp == 0) {
-        int w = (lane < CUT_BLOCK / 32) ? s_warp_sum[lane] : 0;
-        int wi = w;
+        // FLAT_PARTS partial sums in node order: lane l scans entries [l*PPL, (l+1)*PPL)
+        constexpr int PPL = FLAT_PARTS / 32;
+        int w[PPL], wsum = 0;
+#pragma unroll
+        for (int k = 0; k < PPL; k++) {
+            w[k] = s_part[lane * PPL + k];
+            wsum += w[k];
+        }
+        int wi = wsum;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             int t = __shfl_up_sync(0xffffffffu, wi, o);
             if (lane >= (unsigned)o) wi += t;
         }
-        if (lane < CUT_BLOCK / 32) s_warp_sum[lane] = wi - w;  // exclusive warp offsets
-        int block_total = __shfl_sync(0xffffffffu, wi, CUT_BLOCK / 32 - 1);
-        // publish aggregate, look back, publish inclusive prefix
+        int run = wi - wsum;
+#pragma unroll
+        for (int k = 0; k < PPL; k++) {
+            s_part[lane * PPL + k] = run;
+            run += w[k];
+        }
+        const int block_total = __shfl_sync(0xffffffffu, wi, 31);
         unsigned long long excl = 0;
         if (tile == 0) {
             if (lane == 0) st_relaxed(tile_state, pack_state(2, (unsigned long long)block_total));
@@ -122,24 +154,26 @@ __global__ void __launch_bounds__(CUT_BLOCK) cut_flat_kernel(const int32_t* __re
         }
         if (lane == 0) {
             s_prefix = excl;
-            if ((long long)tile * CUT_BLOCK + CUT_BLOCK >= N) {  // last tile: total count
-                long long total = (long long)excl + block_total;
+            if ((long long)base + FLAT_TILE >= N) {  // last tile: total count
+                const long long total = (long long)excl + block_total;
                 hdr->count = (int)total;
                 if (total > capacity) hdr->overflow = 1;
             }
         }
     }
     __syncthreads();
-    if (count > 0) {
-        long long off = (long long)s_prefix + s_warp_sum[warp] + (incl - count);
-        int parentgaussian = -1;
-        if (n.parent != -1) parentgaussian = __ldg(nodes + (size_t)n.parent * 7 + 2);
-        for (int k = 0; k < count; k++) {
-            long long o = off + k;
-            if (o < capacity) {
-                render_indices[o] = n.start + k;
-                if (parent_indices) parent_indices[o] = parentgaussian;
-                if (node_ids) node_ids[o] = i;
+#pragma unroll
+    for (int r = 0; r < FLAT_ROWS; r++) {
+        if (count[r] > 0) {
+            const long long off = (long long)s_prefix + s_part[r * (FLAT_THREADS / 32) + warp] + (incl[r] - count[r]);
+            const int id = base + r * FLAT_THREADS + (int)tid;
+            for (int k = 0; k < count[r]; k++) {
+                const long long o = off + k;
+                if (o < capacity) {
+                    render_indices[o] = start[r] + k;
+                    if (parent_indices) parent_indices[o] = pgauss[r];
+                    if (node_ids) node_ids[o] = id;
+                }
             }
         }
     }
@@ -372,7 +406,7 @@ __global__ void cut_weights_kernel(const int32_t* __restrict__ nodes, const floa
 
 using namespace lodgs;
 
-static size_t cut_states(int N) { return (size_t)(N + CUT_BLOCK - 1) / CUT_BLOCK + 1; }
+static size_t cut_states(int N) { return (size_t)(N + CUT_BLOCK - 1) / CUT_BLOCK + 1; }  // CUT_BLOCK <= FLAT_TILE: enough for both scans
 
 extern "C" size_t lodgs_cut_workspace_bytes(int N) {
     if (N < 0) N = 0;
@@ -443,8 +477,8 @@ extern "C" int lodgs_expand_to_size(const int32_t* nodes, const float* boxes, in
     }
     if (mode == 0) {
         LODGS_CUDA(cudaMemsetAsync(ws, 0, align_up(sizeof(CutHeader), 128) + cut_states(N) * 8, s));
-        int tiles = (N + CUT_BLOCK - 1) / CUT_BLOCK;
-        cut_flat_kernel<<<tiles, CUT_BLOCK, 0, s>>>(nodes, boxes, N, target_size, viewpoint_dev, render_indices, parent_indices,
+        int tiles = (N + FLAT_TILE - 1) / FLAT_TILE;
+        cut_flat_kernel<<<tiles, FLAT_THREADS, 0, s>>>(nodes, boxes, N, target_size, viewpoint_dev, render_indices, parent_indices,
                                                    nodes_for_render_indices, capacity, c.hdr, c.states);
         LODGS_LAUNCHED("cut_flat_kernel");
     } else {

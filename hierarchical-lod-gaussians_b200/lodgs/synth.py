@@ -140,3 +140,46 @@ def build_hierarchy(points, radii, seed=0):
 def tau_to_threshold(tau_px, tanfovx, width):
     """render_hierarchy.py:56."""
     return (2.0 * (tau_px + 0.5)) * tanfovx / (0.5 * width)
+
+
+def build_hierarchy_torch(k, device, seed=0, extent=(200.0, 200.0, 10.0), radius_mean=0.1):
+    """Large synthetic hierarchy for the cut benchmarks, built with torch ops on `device` in
+    seconds: a perfect binary tree over L = 2^k leaves (N = 2L-1 nodes, one Gaussian per node, Gaussian id = node id).
+    Leaves are the points in Morton order (so siblings are spatial neighbours, like a kd-tree's), boxes are unions of the
+    children's boxes bottom-up (leaf box = point +- 3*radius, GH/PointbasedKdTreeGenerator.cpp:19-33), box.w = largest box
+    side for interior nodes and 0 for leaves (GH/ClusterMerger.cpp:165-168). Node ids are level order: the two children of
+    node i are 2i+1, 2i+2 (a contiguous block, as upstream populateRec produces). Returns nodes[N,7] i32, boxes[N,2,4] f32."""
+    import torch
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    L = 1 << k
+    N = 2 * L - 1
+    ext = torch.tensor(extent, dtype=torch.float32)
+    pts = ((torch.rand(L, 3, generator=g) * 2 - 1) * ext).to(device)
+    rad = torch.exp(torch.randn(L, generator=g) * 0.5 + float(np.log(radius_mean))).to(device)
+    # Morton order over a 2^10 grid per axis
+    q = ((pts / ext.to(device) * 0.5 + 0.5).clamp(0, 1 - 1e-7) * 1024).long()
+    code = torch.zeros(L, dtype=torch.int64, device=device)
+    for b in range(10):
+        for a in range(3):
+            code |= ((q[:, a] >> b) & 1) << (3 * b + a)
+    order = torch.argsort(code)
+    pts, rad = pts[order], rad[order]
+    boxes = torch.zeros(N, 2, 4, dtype=torch.float32, device=device)
+    lo, hi = pts - 3.0 * rad[:, None], pts + 3.0 * rad[:, None]
+    first = L - 1
+    boxes[first:, 0, :3], boxes[first:, 1, :3] = lo, hi
+    for d in range(k - 1, -1, -1):
+        n = 1 << d
+        lo = lo.view(n, 2, 3).min(1).values
+        hi = hi.view(n, 2, 3).max(1).values
+        s = n - 1
+        boxes[s:s + n, 0, :3], boxes[s:s + n, 1, :3] = lo, hi
+        w = (hi - lo).max(1).values
+        boxes[s:s + n, 0, 3], boxes[s:s + n, 1, 3] = w, w
+    ids = torch.arange(N, dtype=torch.int64, device=device)
+    depth = torch.floor(torch.log2((ids + 1).double())).long()
+    leaf = ids >= first
+    nodes = torch.stack([depth, torch.where(ids == 0, torch.full_like(ids, -1), (ids - 1) // 2), ids, leaf.long(), (~leaf).long(),
+                         torch.where(leaf, torch.full_like(ids, -1), 2 * ids + 1), torch.where(leaf, torch.zeros_like(ids),
+                                                                                              torch.full_like(ids, 2))], 1).int()
+    return nodes.contiguous(), boxes.contiguous()
