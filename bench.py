@@ -35,6 +35,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--P", type=int, default=P, help="number of Gaussians (default: the 1 M of config A)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cut", action="store_true", help="skip the LOD-cut ms/frame section")
     return ap.parse_args()
 
 

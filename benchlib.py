@@ -323,7 +323,22 @@ def run_ours(args, rank, world, dev):
                                      "ms_per_step": round(ms_e2e / args.steps, 4)},
              "gpu_launches": int(launches), "roofline": roof, "per_kernel": per_kernel, "workload_counters": counters,
              "cpu_baseline": _cpu_baseline(args.no_cpu_baseline)}
+    if not getattr(args, "no_cut", False) and world == 1:
+        extra["lod_cut"] = _lod_cut(dev, not args.no_cpu_baseline)
     return _line(args, world, value, ms / args.steps, clocks, extra)
+
+
+def _lod_cut(dev, with_cpu):
+    """Second half of BASELINE.json's metric: LOD-cut ms/frame (expand_to_size [+ get_interpolation_weights]) on a synthetic
+    4.19 M-node hierarchy, tau in {0,3,6,15} px, next to the reference CUDA cut and the CPU port (tools/bench_cut.py)."""
+    try:
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("bench_cut", os.path.join(ROOT, "tools", "bench_cut.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        return mod.run(k=21, frames=30, dev=dev, with_ref=True, with_cpu=with_cpu)
+    except Exception as e:  # noqa: BLE001
+        return {"unavailable": str(e)[:200]}
 
 
 def run_reference(args, rank, world, dev):

@@ -52,18 +52,22 @@ def run(k=21, frames=50, cpu_frames=2, dev=None, with_ref=True, with_cpu=True):
             for _ in range(3):
                 K = gh.expand_to_size(nodes, boxes, tau, vps[0], torch.zeros(3), ri, pi, ni, mode=mode)
             torch.cuda.synchronize()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            Ks = 0
-            for f in range(frames):
-                K = gh.expand_to_size(nodes, boxes, tau, vps[f], torch.zeros(3), ri, pi, ni, mode=mode)
-                gh.get_interpolation_weights(ni[:K], tau, nodes, boxes, torch.from_numpy(path[f]), torch.zeros(3), ts, kids)
-                Ks += K
-            e1.record()
-            torch.cuda.synchronize()
-            ms = e0.elapsed_time(e1) / frames
-            ent[name] = {"ms_per_frame": round(ms, 4), "mean_K": Ks // frames,
-                         "flat_equiv_GBps": round((60.0 * N + 12.0 * Ks / frames) / (ms * 1e-3) / 1e9, 1)}
+            def timed(with_weights):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                tot = 0
+                for f in range(frames):
+                    K = gh.expand_to_size(nodes, boxes, tau, vps[f], torch.zeros(3), ri, pi, ni, mode=mode)
+                    if with_weights:
+                        gh.get_interpolation_weights(ni[:K], tau, nodes, boxes, torch.from_numpy(path[f]), torch.zeros(3), ts, kids)
+                    tot += K
+                e1.record()
+                torch.cuda.synchronize()
+                return e0.elapsed_time(e1) / frames, tot
+            ms_cut, Ks = timed(False)
+            ms_all, _ = timed(True)
+            ent[name] = {"cut_ms_per_frame": round(ms_cut, 4), "cut_plus_weights_ms_per_frame": round(ms_all, 4), "mean_K": Ks // frames,
+                         "flat_equiv_GBps": round((60.0 * N + 12.0 * Ks / frames) / (ms_cut * 1e-3) / 1e9, 1)}
         if ref is not None:
             for _ in range(2):
                 ref.ref_expand_to_size(N, tau, nodes.data_ptr(), boxes.data_ptr(), vps[0].data_ptr(), 0.0, 0.0, 1.0, rri.data_ptr(),

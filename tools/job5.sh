@@ -4,7 +4,7 @@ timeout 1200 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&
 grep -E "^(FAILED|ERROR)|passed|failed|^E  " gpurun_out/pytest_gpu.log | tail -15 | cut -c1-300
 timeout 600 python tests/gpu_diag.py > gpurun_out/parity_diag.log 2>&1; echo "diag exit $?"
 grep -E "^==|FAIL|integer mismatches" gpurun_out/parity_diag.log
-timeout 600 python bench.py --steps 20 --warmup 5 --no-cpu-baseline > gpurun_out/bench_ours.json 2> gpurun_out/bench_ours.err; echo "bench exit $?"
+timeout 600 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-cut > gpurun_out/bench_ours.json 2> gpurun_out/bench_ours.err; echo "bench exit $?"
 python - <<'PY'
 import json
 for f in ('gpurun_out/bench_ours.json',):
