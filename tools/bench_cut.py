@@ -95,7 +95,7 @@ def run(k=21, frames=50, cpu_frames=2, dev=None, with_ref=True, with_cpu=True):
         for f in range(cpu_frames):
             orc.expand_to_size(nn, bb, synth.tau_to_threshold(3.0, 0.8, 1920), path[f])
         out["cpu_port_tau3"] = {"ms_per_frame": round((time.perf_counter() - t0) * 1e3 / cpu_frames, 2), "frames": cpu_frames,
-                                "cores": int(orc.lib().orc_num_threads()), "kind": "port (oracle/cut_oracle.c)"}
+                                "cores": 1, "kind": "port (oracle/cut_oracle.c, sequential scan+scatter)"}
     return out
 
 
