@@ -1,10 +1,9 @@
 // preprocess.cu — forward per-Gaussian stage: LOD parent interpolation, projection, EWA covariance -> conic,
 // SH -> RGB, tile rectangle, fused with the prefix sum of tile counts.
 //
-// Replaces preprocessCUDA<3> (HR/cuda_rasterizer/forward.cu:218-445) and the following
-// cub::DeviceScan::InclusiveSum (rasterizer_impl.cu:322). One kernel: each 256-Gaussian tile ends with a block
-// scan of tiles_touched and a decoupled look-back, so point_offsets and num_rendered are final when the kernel
-// retires and tiles_touched never makes a second trip through HBM. SH coefficients (192 B per Gaussian at
+// Replaces preprocessCUDA<3> (HR/cuda_rasterizer/forward.cu:218-445) and the total of the following
+// cub::DeviceScan::InclusiveSum (rasterizer_impl.cu:322): num_rendered is accumulated by one atomic per CTA, the
+// per-Gaussian offsets are produced later in DEPTH order (binning.cu), which is the order instances are emitted in. SH coefficients (192 B per Gaussian at
 // degree 3) and quaternions move as 16-byte vector loads.
 #include "gaussmath.cuh"
 #include "state.cuh"
@@ -198,29 +197,25 @@ __device__ __forceinline__ uint32_t preprocess_one(const PreParams& p, const Geo
 }
 
 __global__ void __launch_bounds__(PRE_BLOCK) preprocess_fwd_kernel(const PreParams p, const GeomState g) {
-    __shared__ int s_tile;
-    __shared__ unsigned s_warp_sum[PRE_BLOCK / 32];
-    __shared__ unsigned long long s_prefix;
     __shared__ float s_view[16], s_proj[16];
     __shared__ uint64_t s_bar;
     extern __shared__ __align__(128) float4 sh_stage[];  // [256][3M/4] when p.staged
     const int row4 = (p.M * 3) / 4;
+    const int tile = blockIdx.x;
     if (threadIdx.x == 0) {
-        s_tile = atomicAdd(&g.hdr->ticket, 1);
         if (p.staged) {
             // the tile's SH rows are one contiguous block: a single bulk copy (TMA) that lands while the projection math runs
             mbar_init(&s_bar, 1);
             mbar_fence_init();
-            const int cnt = min(PRE_BLOCK, p.P - s_tile * PRE_BLOCK);
+            const int cnt = min(PRE_BLOCK, p.P - tile * PRE_BLOCK);
             const unsigned bytes = (unsigned)cnt * (unsigned)row4 * 16u;
             mbar_expect_tx(&s_bar, bytes);
-            bulk_g2s(sh_stage, p.shs + (size_t)s_tile * PRE_BLOCK * p.M * 3, bytes, &s_bar);
+            bulk_g2s(sh_stage, p.shs + (size_t)tile * PRE_BLOCK * p.M * 3, bytes, &s_bar);
         }
     }
     if (threadIdx.x < 16) s_view[threadIdx.x] = __ldg(p.viewmatrix + threadIdx.x);
     else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = __ldg(p.projmatrix + threadIdx.x - 16);
     __syncthreads();
-    const int tile = s_tile;
     const int t_idx = tile * PRE_BLOCK + threadIdx.x;
     unsigned tiles = 0;
     if (t_idx < p.P) {
@@ -232,40 +227,14 @@ __global__ void __launch_bounds__(PRE_BLOCK) preprocess_fwd_kernel(const PrePara
         g.depth_keys[t_idx] = tiles ? __float_as_uint(g.depths[t_idx]) : 0xffffffffu;
     }
     if (p.staged && threadIdx.x == 0) mbar_wait(&s_bar, 0);  // the copy must have landed before the CTA may retire
-    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned incl = tiles;
+    // num_rendered = sum of the tile counts: one atomic per CTA. The per-Gaussian prefix sum of the reference
+    // (InclusiveSum, rasterizer_impl.cu:322) is not needed here — instances are emitted in depth order from a scan in
+    // THAT order (scan_sorted_kernel) — and a fused look-back scan chained all 3907 CTAs of this kernel for nothing.
+    const unsigned lane = threadIdx.x & 31;
+    unsigned sum = tiles;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        unsigned v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= (unsigned)o) incl += v;
-    }
-    if (lane == 31) s_warp_sum[warp] = incl;
-    __syncthreads();
-    if (warp == 0) {
-        unsigned w = (lane < PRE_BLOCK / 32) ? s_warp_sum[lane] : 0;
-        unsigned wi = w;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            unsigned v = __shfl_up_sync(0xffffffffu, wi, o);
-            if (lane >= (unsigned)o) wi += v;
-        }
-        if (lane < PRE_BLOCK / 32) s_warp_sum[lane] = wi - w;
-        unsigned block_total = __shfl_sync(0xffffffffu, wi, PRE_BLOCK / 32 - 1);
-        unsigned long long excl = 0;
-        if (tile == 0) {
-            if (lane == 0) st_relaxed(g.scan_state, pack_state(2, block_total));
-        } else {
-            if (lane == 0) st_relaxed(g.scan_state + tile, pack_state(1, block_total));
-            excl = lookback_warp(g.scan_state, tile);
-            if (lane == 0) st_relaxed(g.scan_state + tile, pack_state(2, excl + block_total));
-        }
-        if (lane == 0) {
-            s_prefix = excl;
-            if ((long long)tile * PRE_BLOCK + PRE_BLOCK >= p.P) g.hdr->num_rendered = (unsigned)(excl + block_total);
-        }
-    }
-    __syncthreads();
-    if (t_idx < p.P) g.point_offsets[t_idx] = (unsigned)s_prefix + s_warp_sum[warp] + incl;
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (lane == 0 && sum) atomicAdd(&g.hdr->num_rendered, sum);
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means, const float* __restrict__ view, uint8_t* present) {

@@ -36,7 +36,7 @@ struct GeomState {
     float* cov3D;                    // [P,6]
     uint8_t* clamped;                // [P] bit c set = channel c clamped to 0
     uint32_t* tiles_touched;         // [P]
-    uint32_t* point_offsets;         // [P] inclusive prefix sum of tiles_touched
+    uint32_t* point_offsets;         // [P] (unused since the depth-ordered emission; kept so that the layout indices stay put)
     int2* rects;                     // [P]
     // depth-ordered emission (raster_api.cu): Gaussians sorted by depth bits, then their tile counts scanned in that order
     uint32_t* depth_keys;            // [P] depth bits, 0xffffffff for culled Gaussians

@@ -165,7 +165,7 @@ int lodgs_mark_visible(int P, const float* means3D, const float* viewmatrix, con
 /* Parity-test accessors: byte offsets of the arrays inside the opaque buffers.
  * geom:   [0]=depths f32[P] [1]=means2D f32[P,2] [2]=conic_opacity f32[P,4] [3]=rgb f32[P,3]
  *         [4]=cov3D f32[P,6] [5]=clamped u8[P] (bit c = channel c clamped) [6]=tiles_touched u32[P]
- *         [7]=point_offsets u32[P] [8]=rects i32[P,2]
+ *         [7]=(unused) [8]=rects i32[P,2]
  * binning:[0]=tiles_unsorted u32[R] [1]=values_unsorted u32[R]  (instances emitted in (depth bits, index) order of their
  *         Gaussians, carrying only the tile id) [2]=keys_sorted u64[R] tile|depth [3]=point_list u32[R]
  *         [4]=splat records f32[R,12]

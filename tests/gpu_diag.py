@@ -59,7 +59,6 @@ def run(P, W, H, lod=False, seed=0):
     bad += cmp_int("radii", m["radii"], r["radii"])
     bad += cmp_int("rects", m["rects"][vis], r["rects"][vis])
     bad += cmp_int("tiles_touched", m["tiles_touched"], r["tiles_touched"])
-    bad += cmp_int("point_offsets", m["point_offsets"], r["point_offsets"])
     cmp_f("depths", m["depths"], r["depths"], vis)
     cmp_f("means2D", m["means2D"], r["means2D"], vis)
     cmp_f("conic_opacity", m["conic_opacity"], r["conic_opacity"], vis)

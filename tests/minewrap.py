@@ -43,7 +43,6 @@ def forward(sc, cam, bg, indices=None, parent_indices=None, ts=None, kids=None, 
     res["cov3D"] = _view(geom, o[4], P * 24, torch.float32, (P, 6))
     res["clamped_bits"] = _view(geom, o[5], P, torch.uint8, (P,))
     res["tiles_touched"] = _view(geom, o[6], P * 4, torch.int32, (P,))
-    res["point_offsets"] = _view(geom, o[7], P * 4, torch.int32, (P,))
     res["rects"] = _view(geom, o[8], P * 8, torch.int32, (P, 2))
     if R > 0:
         b = (C.c_size_t * 5)()

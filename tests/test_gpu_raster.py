@@ -17,7 +17,7 @@ pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 # the unsorted key list of duplicateWithKeys has no counterpart here (instances are emitted in depth order carrying only
 # their tile id); its sorted result — keys, point_list, ranges — is compared bit for bit
-INT_KEYS = ("radii", "tiles_touched", "point_offsets", "keys", "point_list", "ranges", "n_contrib", "seen")
+INT_KEYS = ("radii", "tiles_touched", "keys", "point_list", "ranges", "n_contrib", "seen")
 GRAD_KEYS = ("dL_dmean2D", "dL_dcolor", "dL_dopacity", "dL_dmean3D", "dL_dcov3D", "dL_dsh", "dL_dscale", "dL_drot")
 
 
@@ -116,8 +116,8 @@ def test_full_size_properties():
     cam, bg = cu(cam_np), torch.zeros(3, device="cuda")
     f = minewrap.forward(sc, cam, bg)
     R, P = f["R"], f["P"]
-    tt, po = f["tiles_touched"].long(), f["point_offsets"].long()
-    assert torch.equal(po, torch.cumsum(tt, 0)) and int(po[-1]) == R            # fused scan == prefix sum
+    tt = f["tiles_touched"].long()
+    assert int(tt.sum()) == R                                                    # num_rendered == total of the tile counts
     assert ((f["radii"] > 0) == (tt > 0)).all()
     ks, pl = f["keys"], f["point_list"].long()
     assert (ks[1:] >= ks[:-1]).all()                                             # sorted
