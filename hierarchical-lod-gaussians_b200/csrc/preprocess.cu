@@ -305,10 +305,14 @@ extern "C" int lodgs_forward_preprocess(int P, int D, int M, int W, int H, const
     // The count goes back to the host (the caller sizes the binning buffer from it, rasterizer_impl.cu:330-333) while the
     // GPU already orders the Gaussians by depth for the emission stage: the host waits on an event recorded right after
     // the 4-byte copy, not on the stream.
+    // (the copy lands in a pinned staging word: a copy to pageable memory would block the host until the kernel has run
+    // and the launches below would no longer be queued behind it)
     static thread_local cudaEvent_t ev = nullptr;
+    static thread_local int32_t* pinned = nullptr;
     if (num_rendered_host) {
         if (!ev) LODGS_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-        LODGS_CUDA(cudaMemcpyAsync(num_rendered_host, &g.hdr->num_rendered, sizeof(int), cudaMemcpyDeviceToHost, s));
+        if (!pinned) LODGS_CUDA(cudaHostAlloc((void**)&pinned, sizeof(int32_t), cudaHostAllocDefault));
+        LODGS_CUDA(cudaMemcpyAsync(pinned, &g.hdr->num_rendered, sizeof(int), cudaMemcpyDeviceToHost, s));
         LODGS_CUDA(cudaEventRecord(ev, s));
     }
     int rc = sort_pairs32_device(g.depth_keys, nullptr, g.depth_keys_sorted, g.order, g.sort_tmp_k, g.sort_tmp_v, P, 0, 32, g.sort_ws, s, "sort_depth_pass_kernel",
@@ -316,7 +320,10 @@ extern "C" int lodgs_forward_preprocess(int P, int D, int M, int W, int H, const
     if (rc) return rc;
     rc = launch_scan_sorted(P, g, s);
     if (rc) return rc;
-    if (num_rendered_host) LODGS_CUDA(cudaEventSynchronize(ev));
+    if (num_rendered_host) {
+        LODGS_CUDA(cudaEventSynchronize(ev));
+        *num_rendered_host = *pinned;
+    }
     return LODGS_OK;
 }
 

@@ -122,7 +122,8 @@ __global__ void __launch_bounds__(SORT_THREADS, sizeof(KeyT) == 4 ? 4 : 2) sort_
             key[k] = ~(KeyT)0;
         }
     }
-    // ---- rank inside the warp, item by item (index order => stable)
+    // ---- rank inside the warp, item by item (index order => stable). The 16 match-any instructions are independent
+    // and issued back to back; only the running per-digit counts of the warp are a serial chain (one LDS/STS per round).
     unsigned* wh = sm.warp_hist[warp];
 #pragma unroll
     for (int k = 0; k < SORT_ITEMS; k++) {
@@ -130,7 +131,14 @@ __global__ void __launch_bounds__(SORT_THREADS, sizeof(KeyT) == 4 ? 4 : 2) sort_
         const bool valid = e < tile_n;
         const unsigned d = (unsigned)(key[k] >> shift) & 255u;
         // invalid lanes match on a private value so that they never join a digit group
-        const unsigned mask = __match_any_sync(0xffffffffu, valid ? d : (256u + lane));
+        rank[k] = __match_any_sync(0xffffffffu, valid ? d : (256u + lane));
+    }
+#pragma unroll
+    for (int k = 0; k < SORT_ITEMS; k++) {
+        const int e = wbase + k * 32 + lane;
+        const bool valid = e < tile_n;
+        const unsigned d = (unsigned)(key[k] >> shift) & 255u;
+        const unsigned mask = rank[k];
         const int leader = __ffs(mask) - 1;
         unsigned old = 0;
         if ((int)lane == leader && valid) {
