@@ -177,12 +177,25 @@ __global__ void __launch_bounds__(SORT_THREADS, sizeof(KeyT) == 4 ? 4 : 2) sort_
             atomicExch(my, (2u << 30) | count);
         } else {
             atomicExch(my, (1u << 30) | count);
-            for (int t = tile - 1; t >= 0; t--) {
-                const volatile unsigned* prev = lookback + (size_t)t * SORT_RADIX + d;
-                unsigned s;
-                do { s = *prev; } while ((s >> 30) == 0);
-                excl += s & 0x3fffffffu;
-                if ((s >> 30) == 2u) break;
+            // LB independent loads per step: the chain of dependent L2 round trips, not HBM, bounds this kernel when every
+            // tile of a wave publishes its aggregate at the same moment (measured: ~sqrt(2*tiles) steps per wave)
+            constexpr int LB = 8;
+            bool done = false;
+            for (int t = tile - 1; t >= 0 && !done; t -= LB) {
+                unsigned sv[LB];
+#pragma unroll
+                for (int j = 0; j < LB; j++) {
+                    const int idx = t - j;
+                    sv[j] = idx >= 0 ? *((const volatile unsigned*)(lookback + (size_t)idx * SORT_RADIX + d)) : (2u << 30);
+                }
+#pragma unroll
+                for (int j = 0; j < LB; j++) {
+                    if (done) break;
+                    const int idx = t - j;
+                    while ((sv[j] >> 30) == 0) sv[j] = *((const volatile unsigned*)(lookback + (size_t)idx * SORT_RADIX + d));
+                    excl += sv[j] & 0x3fffffffu;
+                    done = (sv[j] >> 30) == 2u;
+                }
             }
             atomicExch(my, (2u << 30) | (excl + count));
         }
