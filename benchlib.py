@@ -222,7 +222,7 @@ def _work_model(arm, n_gauss):
     fa = (arm.bg, arm.ei, arm.ei, arm.ef, arm.ei, d["means3D"], arm.ef, d["opacities"], d["scales"], d["rotations"], 1.0, arm.ef,
           c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"], H, W, d["shs"], DEG, c["campos"], False, False, True)
     R, color, radii, geom, binning, imgb, invdepth, seen = arm._C.rasterize_gaussians(*fa)
-    lodgs.check(lodgs.lib.lodgs_blend_stats(W, H, R, 0, binning.data_ptr(), imgb.data_ptr(), cnt.data_ptr(), lodgs.current_stream()))
+    lodgs.check(lodgs.lib.lodgs_blend_stats(radii.numel(), W, H, R, 0, geom.data_ptr(), binning.data_ptr(), imgb.data_ptr(), cnt.data_ptr(), lodgs.current_stream()))
     torch.cuda.synchronize()
     n_test, n_alpha, n_blend = (int(x) for x in cnt.tolist())
     work = {
@@ -233,7 +233,7 @@ def _work_model(arm, n_gauss):
         "emit_balanced_kernel": ("hbm", 16.0 * n_gauss + 8.0 * R),
         "sort_tile_hist_kernel": ("hbm", 4.0 * R),
         "sort_tile_pass_kernel": ("hbm", 16.0 * R),            # per launch (one 8-bit digit of the tile id)
-        "build_records_kernel": ("hbm", (4.0 + 4.0 + 8.0 + 44.0 + 48.0) * R),
+        "tile_ranges_kernel": ("hbm", 4.0 * R),
         "blend_fwd_kernel": ("fp32", 11.0 * n_test + 2.0 * n_alpha + 14.0 * n_blend),
         "blend_bwd_kernel": ("fp32", 70.0 * n_blend),
         "preprocess_bwd_kernel": ("hbm", p_vis * (115.0 + 68.0 + 24.0 * M)),

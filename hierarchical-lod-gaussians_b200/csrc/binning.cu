@@ -155,24 +155,29 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_balanced_kernel(int P, unsi
     }
 }
 
-// Gather per-Gaussian blend inputs into sorted order: one 48-byte record per instance.
-__global__ void __launch_bounds__(256) build_records_kernel(int R, int P, const uint32_t* __restrict__ point_list,
-                                                           const uint32_t* __restrict__ tiles_sorted, uint64_t* __restrict__ keys,
-                                                           const float2* __restrict__ means2D,
-                                                           const float4* __restrict__ conic_opacity, const float* __restrict__ colors,
-                                                           const float* __restrict__ depths, const float* __restrict__ ts,
-                                                           const int32_t* __restrict__ kids, SplatRec* __restrict__ recs,
-                                                           uint2* __restrict__ ranges) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= R) return;
-    const uint32_t id = __ldg(point_list + i);
-    // identifyTileRanges (rasterizer_impl.cu:120-142) on the way: ranges were cleared before the launch
-    {
-        const uint32_t cur = __ldg(tiles_sorted + i);
+// identifyTileRanges (rasterizer_impl.cu:120-142) over the sorted tile ids; ranges were cleared before the launch.
+constexpr int RANGE_ITEMS = 4;
+__global__ void __launch_bounds__(256) tile_ranges_kernel(int R, const uint32_t* __restrict__ tiles_sorted, uint2* __restrict__ ranges) {
+    const int i0 = (blockIdx.x * blockDim.x + threadIdx.x) * RANGE_ITEMS;
+    if (i0 >= R) return;
+    uint32_t t[RANGE_ITEMS + 1];
+    t[0] = i0 ? __ldg(tiles_sorted + i0 - 1) : 0u;
+    if (i0 + RANGE_ITEMS <= R && (reinterpret_cast<uintptr_t>(tiles_sorted) & 15) == 0) {
+        const uint4 q = __ldg(reinterpret_cast<const uint4*>(tiles_sorted + i0));
+        t[1] = q.x; t[2] = q.y; t[3] = q.z; t[4] = q.w;
+    } else {
+#pragma unroll
+        for (int k = 0; k < RANGE_ITEMS; k++) t[k + 1] = i0 + k < R ? __ldg(tiles_sorted + i0 + k) : 0u;
+    }
+#pragma unroll
+    for (int k = 0; k < RANGE_ITEMS; k++) {
+        const int i = i0 + k;
+        if (i >= R) break;
+        const uint32_t cur = t[k + 1];
         if (i == 0) {
             ranges[cur].x = 0;
         } else {
-            const uint32_t prev = __ldg(tiles_sorted + i - 1);
+            const uint32_t prev = t[k];
             if (cur != prev) {
                 ranges[prev].y = i;
                 ranges[cur].x = i;
@@ -181,26 +186,23 @@ __global__ void __launch_bounds__(256) build_records_kernel(int R, int P, const 
             if (i == R - 1) ranges[cur].y = R;
         }
     }
-    const float2 xy = __ldg(means2D + id);
-    const float4 co = __ldg(conic_opacity + id);
-    float4 a = {xy.x, xy.y, co.x, co.y};
-    float4 b = {co.z, co.w, __ldg(colors + 3 * (size_t)id), __ldg(colors + 3 * (size_t)id + 1)};
-    const float depth = __ldg(depths + id);
-    keys[i] = ((uint64_t)__ldg(tiles_sorted + i) << 32) | (uint64_t)__float_as_uint(depth);  // the reference's sorted tile|depth key
-    float4 c = {__ldg(colors + 3 * (size_t)id + 2), __frcp_rn(depth), 1.0f, 1.0f};  // rcp.rn == the reference's 1/depth per pair
-    if (ts != nullptr && kids != nullptr) {
-        c.z = __ldg(ts + id);
-        c.w = 1.0f / (float)__ldg(kids + id);
-    } else {
-        // without LOD the t slot carries a conservative cut-off for the quadratic form: power < cut  =>  opacity * exp(power)
-        // < 1/255, so the blend kernels skip the exponential for such pairs (margin >> the 2-ulp error of expf)
-        const float lim = -logf(255.0f * co.w);
-        c.z = lim - 1e-4f * (1.0f + fabsf(lim));
-    }
-    float4* out = reinterpret_cast<float4*>(recs + i);
-    out[0] = a;
-    out[1] = b;
-    out[2] = c;
+}
+
+// LOD rendering: the last two slots of every blend record become the interpolation weight and 1/kids.
+__global__ void __launch_bounds__(256) lod_patch_kernel(int P, const float* __restrict__ ts, const int32_t* __restrict__ kids,
+                                                       SplatRec* __restrict__ recs) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    *reinterpret_cast<float2*>(&recs[i].t) = make_float2(__ldg(ts + i), 1.0f / (float)__ldg(kids + i));
+}
+
+// The reference's sorted 64-bit key list (tile << 32 | depth bits), rebuilt from the products of the tile sort. Parity tests only.
+__global__ void __launch_bounds__(256) sorted_keys_kernel(int R, const uint32_t* __restrict__ tiles_sorted,
+                                                         const uint32_t* __restrict__ point_list, const uint32_t* __restrict__ depth_keys,
+                                                         uint64_t* __restrict__ keys) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= R) return;
+    keys[i] = ((uint64_t)__ldg(tiles_sorted + i) << 32) | (uint64_t)__ldg(depth_keys + __ldg(point_list + i));
 }
 
 int launch_scan_sorted(int P, const GeomState& g, cudaStream_t s) {
@@ -215,12 +217,21 @@ int launch_emit_balanced(int P, int R, const GeomState& g, unsigned gx, uint32_t
     LODGS_LAUNCHED("emit_balanced_kernel");
     return LODGS_OK;
 }
-int launch_build_records(int R, int P, const BinningState& b, const GeomState& g, const float* colors, const float* ts,
-                         const int32_t* kids, uint2* ranges, size_t ntiles, cudaStream_t s) {
+int launch_tile_ranges(int R, const BinningState& b, uint2* ranges, size_t ntiles, cudaStream_t s) {
     LODGS_CUDA(cudaMemsetAsync(ranges, 0, ntiles * sizeof(uint2), s));
-    build_records_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, P, b.point_list, b.tiles_sorted, b.keys, g.means2D, g.conic_opacity, colors,
-                                                        g.depths, ts, kids, b.recs, ranges);
-    LODGS_LAUNCHED("build_records_kernel");
+    const int threads = (R + RANGE_ITEMS - 1) / RANGE_ITEMS;
+    tile_ranges_kernel<<<(threads + 255) / 256, 256, 0, s>>>(R, b.tiles_sorted, ranges);
+    LODGS_LAUNCHED("tile_ranges_kernel");
+    return LODGS_OK;
+}
+int launch_lod_patch(int P, const GeomState& g, const float* ts, const int32_t* kids, cudaStream_t s) {
+    lod_patch_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, ts, kids, g.recs);
+    LODGS_LAUNCHED("lod_patch_kernel");
+    return LODGS_OK;
+}
+int launch_sorted_keys(int R, const BinningState& b, const GeomState& g, uint64_t* keys, cudaStream_t s) {
+    sorted_keys_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, b.tiles_sorted, b.point_list, g.depth_keys, keys);
+    LODGS_LAUNCHED("sorted_keys_kernel");
     return LODGS_OK;
 }
 

@@ -5,9 +5,9 @@
 // across the 32 pixels of a warp with a value-splitting butterfly (12 shuffles instead of 50: every exchange
 // halves the number of values a lane still owns), the ten owning lanes add them to a per-batch shared-memory
 // accumulator, and after the batch one thread per Gaussian flushes non-zero totals with one global RED per value:
-// at most 10 atomics per (tile,Gaussian) instance instead of per pair. Records arrive through the same
-// bulk-copy ring as the forward, and the replay starts at the tile's last contributing splat instead of the
-// end of its range.
+// at most 10 atomics per (tile,Gaussian) instance instead of per pair. Records are gathered from the per-Gaussian
+// array through the same async-copy ring as the forward, and the replay starts at the tile's last contributing
+// splat instead of the end of its range.
 #include "state.cuh"
 
 namespace lodgs {
@@ -19,7 +19,6 @@ constexpr int NV = 10;  // dmean.x dmean.y dconic.xx dconic.xy dconic.yy dopacit
 struct BwdSmem {
     SplatRec recs[2][BWD_BATCH];
     float acc[2][BWD_BATCH * NV];
-    uint32_t ids[2][BWD_BATCH + 8];
     uint64_t bar[2];
     unsigned warp_max[BWD_THREADS / 32];
 };
@@ -176,8 +175,8 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
     const unsigned wmax = __reduce_max_sync(0xffffffffu, max(px[0].last_contributor, px[1].last_contributor));
     if (lane == 0) sm.warp_max[warp] = wmax;
     if (tid == 0) {
-        mbar_init(&sm.bar[0], 1);
-        mbar_init(&sm.bar[1], 1);
+        mbar_init(&sm.bar[0], BWD_THREADS);
+        mbar_init(&sm.bar[1], BWD_THREADS);
         mbar_fence_init();
     }
     for (int i = tid; i < 2 * BWD_BATCH * NV; i += BWD_THREADS) (&sm.acc[0][0])[i] = 0.f;
@@ -188,21 +187,31 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
     L = min(L, range.y - range.x);
     const int rounds = (int)((L + BWD_BATCH - 1) / BWD_BATCH);
 
-    // batch b covers sorted positions [lo_b, hi_b) with hi_b = L - b*BATCH, walked from hi_b-1 down to lo_b
-    auto issue = [&](int b) {
-        const int s = b & 1;
+    // batch b covers sorted positions [lo_b, hi_b) with hi_b = L - b*BATCH, walked from hi_b-1 down to lo_b; thread tid
+    // gathers the record of position lo_b + tid. The ids are fetched one batch ahead of the copies.
+    constexpr uint32_t NO_ID = 0xffffffffu;
+    auto load_id = [&](int b) -> uint32_t {
         const unsigned hi = L - (unsigned)b * BWD_BATCH;
         const unsigned lo = hi > BWD_BATCH ? hi - BWD_BATCH : 0u;
-        const unsigned cnt = hi - lo;
-        const unsigned start = range.x + lo;
-        const unsigned rec_bytes = cnt * (unsigned)sizeof(SplatRec);
-        const unsigned a0 = start & ~3u;
-        const unsigned id_bytes = (((start - a0) + cnt) * 4u + 15u) & ~15u;
-        mbar_expect_tx(&sm.bar[s], rec_bytes + id_bytes);
-        bulk_g2s(&sm.recs[s][0], recs + start, rec_bytes, &sm.bar[s]);
-        bulk_g2s(&sm.ids[s][0], point_list + a0, id_bytes, &sm.bar[s]);
+        return lo + tid < hi ? __ldg(point_list + range.x + lo + tid) : NO_ID;
     };
-    if (tid == 0 && rounds > 0) issue(0);
+    auto issue = [&](int b, uint32_t id) {
+        const int s = b & 1;
+        if (id != NO_ID) {
+            const float4* src = reinterpret_cast<const float4*>(recs + id);
+            float4* dst = reinterpret_cast<float4*>(&sm.recs[s][tid]);
+            cp_async16(dst, src);
+            cp_async16(dst + 1, src + 1);
+            cp_async16(dst + 2, src + 2);
+        }
+        cp_async_arrive(&sm.bar[s]);  // counts this thread in once its copies have landed
+    };
+    uint32_t id_cur = NO_ID, id_next = NO_ID;
+    if (rounds > 0) {
+        id_cur = load_id(0);
+        issue(0, id_cur);
+    }
+    if (rounds > 1) id_next = load_id(1);
 
     const float ddelx_dx = 0.5f * W;
     const float ddely_dy = 0.5f * H;
@@ -245,17 +254,18 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
     for (int b = 0; b < rounds; b++) {
         __syncthreads();  // all warps have left batch b-1: its accumulator is complete and its ring slot is free
         flush();
-        if (tid == 0 && b + 1 < rounds) issue(b + 1);
+        if (b + 1 < rounds) issue(b + 1, id_next);
+        const uint32_t id = id_cur;
+        id_cur = id_next;
+        if (b + 2 < rounds) id_next = load_id(b + 2);
         const int s = b & 1;
         mbar_wait(&sm.bar[s], (unsigned)(b >> 1) & 1u);
         const unsigned hi = L - (unsigned)b * BWD_BATCH;
         const unsigned lo = hi > BWD_BATCH ? hi - BWD_BATCH : 0u;
         const int cnt = (int)(hi - lo);
         {
-            const unsigned mis = (range.x + lo) & 3u;
             my_gid = -1;
             if ((int)tid < cnt) {
-                const uint32_t id = sm.ids[s][mis + tid];
                 my_gid = indices ? __ldg(indices + id) : (int)id;
                 const SplatRec& r = sm.recs[s][tid];  // read now: the ring slot is refilled before this batch is flushed
                 my_con = make_float4(r.conx, r.cony, r.conz, r.opac);
@@ -286,8 +296,8 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
     flush();
 }
 
-int launch_blend_bwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, int W, int H, const float* bg,
-                     const int32_t* indices, const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic,
+int launch_blend_bwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, const SplatRec* recs, int W, int H,
+                     const float* bg, const int32_t* indices, const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic,
                      float* dL_dopacity, float* dL_dcolor, float* dL_dinvdepth, cudaStream_t s) {
     dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1), block(BWD_THREADS, 1, 1);
     static bool attr_set = false;
@@ -299,7 +309,7 @@ int launch_blend_bwd(bool lod, bool depth, const ImageState& img, const BinningS
         attr_set = true;
     }
     const size_t smem = sizeof(BwdSmem);
-#define LODGS_BWD_ARGS img.ranges, bin.recs, bin.point_list, W, H, bg, indices, img.final_T, img.n_contrib, dL_dpix, dL_dinvdepth_pix, \
+#define LODGS_BWD_ARGS img.ranges, recs, bin.point_list, W, H, bg, indices, img.final_T, img.n_contrib, dL_dpix, dL_dinvdepth_pix, \
                        dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dinvdepth
     if (lod && depth) blend_bwd_kernel<true, true><<<grid, block, smem, s>>>(LODGS_BWD_ARGS);
     else if (lod) blend_bwd_kernel<true, false><<<grid, block, smem, s>>>(LODGS_BWD_ARGS);

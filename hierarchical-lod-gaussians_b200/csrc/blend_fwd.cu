@@ -1,11 +1,12 @@
 // blend_fwd.cu — per-tile front-to-back alpha blending with hierarchical-LOD alpha.
 //
-// Replaces renderCUDA<3> forward (HR/cuda_rasterizer/forward.cu:450-596). One CTA per 16x16 tile; the tile's
-// sorted splat records (48 B each, built after the sort) are streamed into a two-stage shared-memory ring by
-// 1-D bulk async copies (cp.async.bulk -> UBLKCP, completion on an mbarrier) issued by one thread, so the copy
-// of batch b+1 overlaps the blending of batch b and colours/depths never come from global memory inside the
-// pixel loop (the reference fetches them per blended pair). A warp leaves a batch as soon as all of its 32
-// pixels are saturated (ballot), the CTA leaves when all warps have.
+// Replaces renderCUDA<3> forward (HR/cuda_rasterizer/forward.cu:450-596). One CTA per 16x16 tile; the 48-byte
+// blend records of the tile's sorted Gaussians are gathered (through the sorted id list) straight from the
+// per-Gaussian array the preprocess kernel wrote — L2-resident, 48 MB per million Gaussians — into a two-stage
+// shared-memory ring by 16-byte async copies (cp.async -> LDGSTS, completion on an mbarrier), so the gather of
+// batch b+1 overlaps the blending of batch b, no per-instance record array is ever built, and colours/depths never
+// come from global memory inside the pixel loop (the reference fetches them per blended pair). A warp leaves a
+// batch as soon as all of its 64 pixels are saturated (ballot), the CTA leaves when all warps have.
 // The arithmetic keeps the reference's expression order (quadratic form, expf, __powf, blend FMAs) so that
 // n_contrib — an integer output decided by the alpha<1/255 and T<1e-4 tests — and the image are bit-identical.
 #include "state.cuh"
@@ -17,7 +18,6 @@ constexpr int BLEND_THREADS = 128;  // 16 x 8 threads, two vertically adjacent p
 
 struct BlendSmem {
     SplatRec recs[2][BLEND_BATCH];
-    uint32_t ids[2][BLEND_BATCH + 8];
     uint8_t flag[2][BLEND_BATCH];
     uint64_t bar[2];
 };
@@ -79,8 +79,8 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* _
     const int rounds = (total + BLEND_BATCH - 1) / BLEND_BATCH;
 
     if (tid == 0) {
-        mbar_init(&sm.bar[0], 1);
-        mbar_init(&sm.bar[1], 1);
+        mbar_init(&sm.bar[0], BLEND_THREADS);
+        mbar_init(&sm.bar[1], BLEND_THREADS);
         mbar_fence_init();
     }
     if (SEEN) {
@@ -88,19 +88,36 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* _
     }
     __syncthreads();
 
-    auto issue = [&](int b) {
-        const int s = b & 1;
+    constexpr uint32_t NO_ID = 0xffffffffu;
+    // every thread gathers the records of slots tid and tid + BLEND_THREADS of a batch; their ids are fetched one batch ahead
+    auto load_ids = [&](int b, uint32_t(&id)[2]) {
         const unsigned start = range.x + (unsigned)b * BLEND_BATCH;
-        const unsigned cnt = min((unsigned)BLEND_BATCH, range.y - start);
-        const unsigned rec_bytes = cnt * (unsigned)sizeof(SplatRec);
-        unsigned id_bytes = 0;
-        const unsigned a0 = start & ~3u;
-        if (SEEN) id_bytes = (((start - a0) + cnt) * 4u + 15u) & ~15u;
-        mbar_expect_tx(&sm.bar[s], rec_bytes + id_bytes);
-        bulk_g2s(&sm.recs[s][0], recs + start, rec_bytes, &sm.bar[s]);
-        if (SEEN) bulk_g2s(&sm.ids[s][0], point_list + a0, id_bytes, &sm.bar[s]);
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const unsigned pos = start + tid + h * BLEND_THREADS;
+            id[h] = pos < range.y ? __ldg(point_list + pos) : NO_ID;
+        }
     };
-    if (tid == 0 && rounds > 0) issue(0);
+    auto issue = [&](int b, const uint32_t(&id)[2]) {
+        const int s = b & 1;
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            if (id[h] != NO_ID) {
+                const float4* src = reinterpret_cast<const float4*>(recs + id[h]);
+                float4* dst = reinterpret_cast<float4*>(&sm.recs[s][tid + h * BLEND_THREADS]);
+                cp_async16(dst, src);
+                cp_async16(dst + 1, src + 1);
+                cp_async16(dst + 2, src + 2);
+            }
+        }
+        cp_async_arrive(&sm.bar[s]);  // counts this thread in once its copies have landed
+    };
+    uint32_t id_cur[2] = {NO_ID, NO_ID}, id_next[2] = {NO_ID, NO_ID};
+    if (rounds > 0) {
+        load_ids(0, id_cur);
+        issue(0, id_cur);
+    }
+    if (rounds > 1) load_ids(1, id_next);
 
     uint32_t my_id[2] = {0, 0};  // ids of the two splats this thread flushes `seen` for (previous batch)
     int pending = -1;            // batch whose seen flags still have to be flushed
@@ -127,20 +144,21 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* _
         pending = -1;
         const int s = b & 1;
         if (num_done == BLEND_THREADS) {
-            // batch b's bulk copy is still in flight: it must land before the CTA (and its smem) goes away
-            mbar_wait(&sm.bar[s], (unsigned)(b >> 1) & 1u);
+            // this thread's copies of batch b are still in flight: they must land before its CTA (and the smem) goes away
+            cp_async_wait_all();
             break;
         }
-        if (tid == 0 && b + 1 < rounds) issue(b + 1);
-        mbar_wait(&sm.bar[s], (unsigned)(b >> 1) & 1u);
-        const int cnt = min(BLEND_BATCH, toDo);
+        if (b + 1 < rounds) issue(b + 1, id_next);
         if (SEEN) {
-            const unsigned mis = (range.x + (unsigned)b * BLEND_BATCH) & 3u;
-#pragma unroll
-            for (int h = 0; h < 2; h++)
-                if ((int)(tid + h * BLEND_THREADS) < cnt) my_id[h] = sm.ids[s][mis + tid + h * BLEND_THREADS];
+            my_id[0] = id_cur[0];
+            my_id[1] = id_cur[1];
             pending = b;
         }
+        id_cur[0] = id_next[0];
+        id_cur[1] = id_next[1];
+        if (b + 2 < rounds) load_ids(b + 2, id_next);
+        mbar_wait(&sm.bar[s], (unsigned)(b >> 1) & 1u);
+        const int cnt = min(BLEND_BATCH, toDo);
         const float4* __restrict__ rp = reinterpret_cast<const float4*>(&sm.recs[s][0]);
         uint8_t* fl = &sm.flag[s][0];
         uint32_t contributor = (uint32_t)b * BLEND_BATCH;
@@ -204,22 +222,23 @@ static int launch_blend_seen(bool has_seen, dim3 grid, dim3 block, cudaStream_t 
     return launch_blend_one<LOD, DEPTH, false>(grid, s, ranges, recs, point_list, W, H, bg, final_T, n_contrib, out_color, out_invdepth, seen);
 }
 
-int launch_blend_fwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, int W, int H, const float* bg,
-                     float* out_color, float* out_invdepth, int32_t* seen, cudaStream_t s) {
+int launch_blend_fwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, const SplatRec* recs, int W, int H,
+                     const float* bg, float* out_color, float* out_invdepth, int32_t* seen, cudaStream_t s) {
     dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1), block(TILE_X, TILE_Y, 1);
     const bool hs = seen != nullptr;
-    if (lod && depth) return launch_blend_seen<true, true>(hs, grid, block, s, img.ranges, bin.recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
-    if (lod && !depth) return launch_blend_seen<true, false>(hs, grid, block, s, img.ranges, bin.recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
-    if (!lod && depth) return launch_blend_seen<false, true>(hs, grid, block, s, img.ranges, bin.recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
-    return launch_blend_seen<false, false>(hs, grid, block, s, img.ranges, bin.recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
+    if (lod && depth) return launch_blend_seen<true, true>(hs, grid, block, s, img.ranges, recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
+    if (lod && !depth) return launch_blend_seen<true, false>(hs, grid, block, s, img.ranges, recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
+    if (!lod && depth) return launch_blend_seen<false, true>(hs, grid, block, s, img.ranges, recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
+    return launch_blend_seen<false, false>(hs, grid, block, s, img.ranges, recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
 }
 
 // Work counters of the blend (bench.py roofline): replays the forward's per-pixel decisions and counts
 // N_test (pairs whose quadratic form is evaluated), N_alpha (pairs that reach the exponential) and N_blend
 // (pairs that are blended). Not on any product path.
 template <bool LOD>
-__global__ void __launch_bounds__(TILE_PIX) blend_stats_kernel(const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs, int W,
-                                                              int H, unsigned long long* __restrict__ counters) {
+__global__ void __launch_bounds__(TILE_PIX) blend_stats_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                                                              const SplatRec* __restrict__ grecs, int W, int H,
+                                                              unsigned long long* __restrict__ counters) {
     const unsigned horizontal_blocks = (W + TILE_X - 1) / TILE_X;
     const uint2 pix = {blockIdx.x * TILE_X + threadIdx.x, blockIdx.y * TILE_Y + threadIdx.y};
     const float2 pixf = {(float)pix.x, (float)pix.y};
@@ -229,8 +248,9 @@ __global__ void __launch_bounds__(TILE_PIX) blend_stats_kernel(const uint2* __re
     float T = 1.0f;
     if (inside) {
         for (unsigned i = range.x; i < range.y; i++) {
-            const float4 q0 = __ldg(reinterpret_cast<const float4*>(recs + i));
-            const float4 q1 = __ldg(reinterpret_cast<const float4*>(recs + i) + 1);
+            const float4* r4 = reinterpret_cast<const float4*>(grecs + __ldg(point_list + i));
+            const float4 q0 = __ldg(r4);
+            const float4 q1 = __ldg(r4 + 1);
             n_test++;
             const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
             const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
@@ -239,7 +259,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_stats_kernel(const uint2* __re
             const float my_alpha = min(0.99f, q1.y * expf(power));
             float alpha = my_alpha;
             if (LOD) {
-                const float4 q2 = __ldg(reinterpret_cast<const float4*>(recs + i) + 2);
+                const float4 q2 = __ldg(r4 + 2);
                 alpha = q2.z * my_alpha + (1.0f - q2.z) * (1.0f - __powf(1.0f - my_alpha, q2.w));
             }
             if (alpha < 1.0f / 255.0f) continue;
@@ -259,12 +279,12 @@ __global__ void __launch_bounds__(TILE_PIX) blend_stats_kernel(const uint2* __re
     }
 }
 
-int launch_blend_stats(bool lod, const ImageState& img, const BinningState& bin, int W, int H, unsigned long long* counters,
-                       cudaStream_t s) {
+int launch_blend_stats(bool lod, const ImageState& img, const BinningState& bin, const SplatRec* recs, int W, int H,
+                       unsigned long long* counters, cudaStream_t s) {
     dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1), block(TILE_X, TILE_Y, 1);
     LODGS_CUDA(cudaMemsetAsync(counters, 0, 3 * sizeof(unsigned long long), s));
-    if (lod) blend_stats_kernel<true><<<grid, block, 0, s>>>(img.ranges, bin.recs, W, H, counters);
-    else blend_stats_kernel<false><<<grid, block, 0, s>>>(img.ranges, bin.recs, W, H, counters);
+    if (lod) blend_stats_kernel<true><<<grid, block, 0, s>>>(img.ranges, bin.point_list, recs, W, H, counters);
+    else blend_stats_kernel<false><<<grid, block, 0, s>>>(img.ranges, bin.point_list, recs, W, H, counters);
     LODGS_LAUNCHED("blend_stats_kernel");
     return LODGS_OK;
 }

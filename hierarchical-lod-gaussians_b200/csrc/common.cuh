@@ -144,6 +144,15 @@ __device__ __forceinline__ void bulk_commit_wait_all() {
 }
 // make generic-proxy writes to shared memory visible to the async proxy (required before a bulk store reads them)
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+// ---- 16-byte async copies (LDGSTS) for gathers; completion is reported to an mbarrier: every participating thread
+// calls cp_async_arrive once per phase (the barrier is initialised with the number of participating threads).
+__device__ __forceinline__ void cp_async16(void* dst_smem, const void* src_gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(dst_smem)), "l"(src_gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_arrive(uint64_t* bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_addr(bar)) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
     unsigned ok;
     do {

@@ -89,7 +89,8 @@ __device__ __forceinline__ void load_sh(const PreParams& p, int idx, int pidx, b
 
 // Everything preprocessCUDA does for one Gaussian; returns tiles_touched (0 = culled).
 __device__ __forceinline__ uint32_t preprocess_one(const PreParams& p, const GeomState& g, int t_idx, const float* view,
-                                                   const float* proj, const float4* sh_row, uint64_t* bar, uint2& box) {
+                                                   const float* proj, const float4* sh_row, uint64_t* bar, uint2& box,
+                                                   unsigned& depth_bits) {
     const int r_idx = p.indices ? __ldg(p.indices + t_idx) : t_idx;
     p.radii[t_idx] = 0;
 
@@ -170,6 +171,7 @@ __device__ __forceinline__ uint32_t preprocess_one(const PreParams& p, const Geo
     if ((rmax.x - rmin.x) * (rmax.y - rmin.y) == 0) return 0;
     box = make_uint2(rmin.x | (rmin.y << 16), rmax.x | (rmax.y << 16));
 
+    float3 rgb;
     if (p.colors_precomp == nullptr) {
         // view direction from the UN-interpolated mean of r_idx (forward.cu:92: means[idx])
         float cx = __ldg(p.campos), cy = __ldg(p.campos + 1), cz = __ldg(p.campos + 2);
@@ -182,17 +184,25 @@ __device__ __forceinline__ uint32_t preprocess_one(const PreParams& p, const Geo
         result.x += 0.5f; result.y += 0.5f; result.z += 0.5f;
         uint8_t cl = (result.x < 0 ? 1 : 0) | (result.y < 0 ? 2 : 0) | (result.z < 0 ? 4 : 0);
         g.clamped[t_idx] = cl;
-        g.rgb[3 * (size_t)t_idx + 0] = max(result.x, 0.0f);
-        g.rgb[3 * (size_t)t_idx + 1] = max(result.y, 0.0f);
-        g.rgb[3 * (size_t)t_idx + 2] = max(result.z, 0.0f);
+        rgb = {max(result.x, 0.0f), max(result.y, 0.0f), max(result.z, 0.0f)};
+    } else {
+        rgb = {__ldg(p.colors_precomp + 3 * (size_t)t_idx), __ldg(p.colors_precomp + 3 * (size_t)t_idx + 1),
+               __ldg(p.colors_precomp + 3 * (size_t)t_idx + 2)};
     }
 
-    g.depths[t_idx] = p_view.z;
+    depth_bits = __float_as_uint(p_view.z);
     p.radii[t_idx] = (int)my_radius;
-    g.means2D[t_idx] = point_image;
     float opacity = __ldg(p.opacities + r_idx);
     if (has_parent) opacity = t * opacity + (1.0f - t) * __ldg(p.opacities + p_idx);
-    g.conic_opacity[t_idx] = {conic.x, conic.y, conic.z, FM(h_convolution_scaling, opacity)};
+    const float opac = FM(h_convolution_scaling, opacity);
+    // The blend record (48 B). Without LOD the t slot carries a conservative cut-off for the quadratic form: power < cut
+    // => opacity * exp(power) < 1/255, so the blend kernels skip the exponential for such pairs (margin >> the 2-ulp error
+    // of expf); with LOD, lod_patch_kernel overwrites the last two slots with t and 1/kids.
+    const float lim = -logf(255.0f * opac);
+    float4* out = reinterpret_cast<float4*>(g.recs + t_idx);
+    out[0] = {point_image.x, point_image.y, conic.x, conic.y};
+    out[1] = {conic.z, opac, rgb.x, rgb.y};
+    out[2] = {rgb.z, __frcp_rn(p_view.z), lim - 1e-4f * (1.0f + fabsf(lim)), 1.0f};  // rcp.rn == the reference's 1/depth per pair
     return (rmax.y - rmin.y) * (rmax.x - rmin.x);
 }
 
@@ -220,11 +230,12 @@ __global__ void __launch_bounds__(PRE_BLOCK) preprocess_fwd_kernel(const PrePara
     unsigned tiles = 0;
     if (t_idx < p.P) {
         uint2 box = make_uint2(0u, 0u);
-        tiles = preprocess_one(p, g, t_idx, s_view, s_proj, p.staged ? sh_stage + threadIdx.x * row4 : nullptr, &s_bar, box);
+        unsigned depth_bits = 0;
+        tiles = preprocess_one(p, g, t_idx, s_view, s_proj, p.staged ? sh_stage + threadIdx.x * row4 : nullptr, &s_bar, box, depth_bits);
         g.tiles_touched[t_idx] = tiles;
         g.tile_box[t_idx] = tiles ? box : make_uint2(0u, 0u);
         // sort key of the depth-ordered emission: culled Gaussians go to the end of the order and emit nothing
-        g.depth_keys[t_idx] = tiles ? __float_as_uint(g.depths[t_idx]) : 0xffffffffu;
+        g.depth_keys[t_idx] = tiles ? depth_bits : 0xffffffffu;
     }
     if (p.staged && threadIdx.x == 0) mbar_wait(&s_bar, 0);  // the copy must have landed before the CTA may retire
     // num_rendered = sum of the tile counts: one atomic per CTA. The per-Gaussian prefix sum of the reference

@@ -7,12 +7,13 @@ int launch_emit_balanced(int P, int R, const GeomState& g, unsigned gx, uint32_t
 int sort_pairs32_device(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* keys_out, uint32_t* vals_out, uint32_t* keys_tmp,
                         uint32_t* vals_tmp, int n, int begin_bit, int end_bit, void* ws, cudaStream_t s, const char* pass_name,
                         const char* hist_name);
-int launch_build_records(int R, int P, const BinningState& b, const GeomState& g, const float* colors, const float* ts,
-                         const int32_t* kids, uint2* ranges, size_t ntiles, cudaStream_t s);
+int launch_tile_ranges(int R, const BinningState& b, uint2* ranges, size_t ntiles, cudaStream_t s);
+int launch_lod_patch(int P, const GeomState& g, const float* ts, const int32_t* kids, cudaStream_t s);
+int launch_sorted_keys(int R, const BinningState& b, const GeomState& g, uint64_t* keys, cudaStream_t s);
 int sort_pairs_device(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, uint64_t* keys_tmp,
                       uint32_t* vals_tmp, int n, int end_bit, void* ws, cudaStream_t s);
-int launch_blend_fwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, int W, int H, const float* bg,
-                     float* out_color, float* out_invdepth, int32_t* seen, cudaStream_t s);
+int launch_blend_fwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, const SplatRec* recs, int W, int H,
+                     const float* bg, float* out_color, float* out_invdepth, int32_t* seen, cudaStream_t s);
 
 // Same as getHigherMsb (rasterizer_impl.cu:35-50): number of bits needed for the tile id.
 static uint32_t higher_msb(uint32_t n) {
@@ -74,8 +75,10 @@ extern "C" int lodgs_forward_render(int P, int W, int H, int R, const float* bac
     prof_stage_begin(s);
     ImageState img = image_from_chunk(image_buffer, W, H);
     const unsigned gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+    (void)colors_precomp;  // already folded into the blend records by stage 1
     BinningFull bf;
     bf.b = binning_from_chunk(nullptr, 0);
+    const SplatRec* recs = nullptr;
     if (R > 0) {
         if (!geom_buffer || !binning_buffer || !radii || P == 0) { set_error("lodgs_forward_render: null pointer argument"); return LODGS_E_ARG; }
         if (binning_bytes < lodgs_binning_bytes(R) - 128) { set_error("lodgs_forward_render: binning buffer too small"); return LODGS_E_WORKSPACE; }
@@ -89,9 +92,13 @@ extern "C" int lodgs_forward_render(int P, int W, int H, int R, const float* bac
         rc = sort_pairs32_device(bf.b.tiles_unsorted, bf.b.vals_unsorted, bf.b.tiles_sorted, bf.b.point_list, bf.keys_tmp, bf.vals_tmp, R, 0,
                                  bit, bf.b.sort_ws, s, "sort_tile_pass_kernel", "sort_tile_hist_kernel");
         if (rc) return rc;
-        const float* colors = colors_precomp ? colors_precomp : g.rgb;
-        rc = launch_build_records(R, P, bf.b, g, colors, ts, kids, img.ranges, (size_t)gx * gy, s);
+        rc = launch_tile_ranges(R, bf.b, img.ranges, (size_t)gx * gy, s);
         if (rc) return rc;
+        if (ts != nullptr && kids != nullptr) {
+            rc = launch_lod_patch(P, g, ts, kids, s);
+            if (rc) return rc;
+        }
+        recs = g.recs;
     } else {
         // The reference returns before rendering when nothing is visible (rasterizer_impl.cu:332-333), leaving the
         // zero-filled image; the blend below runs with empty ranges and writes the background instead. Keep the
@@ -99,14 +106,14 @@ extern "C" int lodgs_forward_render(int P, int W, int H, int R, const float* bac
         return LODGS_OK;
     }
     const bool lod = ts != nullptr && kids != nullptr;
-    return launch_blend_fwd(lod, out_invdepth != nullptr, img, bf.b, W, H, background, out_color, out_invdepth, seen, s);
+    return launch_blend_fwd(lod, out_invdepth != nullptr, img, bf.b, recs, W, H, background, out_color, out_invdepth, seen, s);
 }
 
 // ------------------------------------------------------------------------------------------------ backward
 namespace lodgs {
 struct PreBwdParams;
-int launch_blend_bwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, int W, int H, const float* bg,
-                     const int32_t* indices, const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic,
+int launch_blend_bwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, const SplatRec* recs, int W, int H,
+                     const float* bg, const int32_t* indices, const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic,
                      float* dL_dopacity, float* dL_dcolor, float* dL_dinvdepth, cudaStream_t s);
 int run_preprocess_bwd(int P, int D, int M, const int32_t* indices, const int32_t* parent_indices, const float* ts, const float* means3D,
                        const int32_t* radii, const float* shs, const uint8_t* clamped, const float* opacities, const float* scales,
@@ -145,7 +152,7 @@ extern "C" int lodgs_backward(int P, int fullP, int D, int M, int R, int W, int 
         if (!binning_buffer) { set_error("lodgs_backward: null binning buffer"); return LODGS_E_ARG; }
         BinningState bin = binning_from_chunk(binning_buffer, R);
         const bool lod = ts != nullptr && kids != nullptr;
-        int rc = launch_blend_bwd(lod, dL_dinvdepth_pix != nullptr, img, bin, W, H, background, indices, dL_dpix, dL_dinvdepth_pix,
+        int rc = launch_blend_bwd(lod, dL_dinvdepth_pix != nullptr, img, bin, g.recs, W, H, background, indices, dL_dpix, dL_dinvdepth_pix,
                                   dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dinvdepth, s);
         if (rc) return rc;
     }
@@ -159,14 +166,24 @@ extern "C" int lodgs_backward(int P, int fullP, int D, int M, int R, int W, int 
 }
 
 namespace lodgs {
-int launch_blend_stats(bool lod, const ImageState& img, const BinningState& bin, int W, int H, unsigned long long* counters,
-                       cudaStream_t s);
+int launch_blend_stats(bool lod, const ImageState& img, const BinningState& bin, const SplatRec* recs, int W, int H,
+                       unsigned long long* counters, cudaStream_t s);
 }
-extern "C" int lodgs_blend_stats(int W, int H, int R, int lod, void* binning_buffer, void* image_buffer, uint64_t* counters3_dev,
-                                 void* stream) {
-    if (W <= 0 || H <= 0 || R <= 0 || !binning_buffer || !image_buffer || !counters3_dev) { set_error("lodgs_blend_stats: bad argument"); return LODGS_E_ARG; }
+extern "C" int lodgs_blend_stats(int P, int W, int H, int R, int lod, void* geom_buffer, void* binning_buffer, void* image_buffer,
+                                 uint64_t* counters3_dev, void* stream) {
+    if (P <= 0 || W <= 0 || H <= 0 || R <= 0 || !geom_buffer || !binning_buffer || !image_buffer || !counters3_dev) {
+        set_error("lodgs_blend_stats: bad argument");
+        return LODGS_E_ARG;
+    }
     cudaStream_t s = (cudaStream_t)stream;
     prof_stage_begin(s);
-    return launch_blend_stats(lod != 0, image_from_chunk(image_buffer, W, H), binning_from_chunk(binning_buffer, R), W, H,
-                              (unsigned long long*)counters3_dev, s);
+    return launch_blend_stats(lod != 0, image_from_chunk(image_buffer, W, H), binning_from_chunk(binning_buffer, R),
+                              geom_from_chunk(geom_buffer, P).recs, W, H, (unsigned long long*)counters3_dev, s);
+}
+
+extern "C" int lodgs_sorted_keys(int P, int R, void* geom_buffer, void* binning_buffer, uint64_t* keys_out, void* stream) {
+    if (P <= 0 || R <= 0 || !geom_buffer || !binning_buffer || !keys_out) { set_error("lodgs_sorted_keys: bad argument"); return LODGS_E_ARG; }
+    cudaStream_t s = (cudaStream_t)stream;
+    prof_stage_begin(s);
+    return launch_sorted_keys(R, binning_from_chunk(binning_buffer, R), geom_from_chunk(geom_buffer, P), keys_out, s);
 }

@@ -1,7 +1,7 @@
 // state.cuh — layout of the three opaque scratch buffers (geometry / binning / image state).
 // Plays the role of GeometryState/BinningState/ImageState::fromChunk (HR/cuda_rasterizer/rasterizer_impl.cu:159-199)
 // but with its own SoA layout: clamp flags packed to one byte, rects kept inside, the scan's look-back
-// states and the sorted per-instance splat records added, no CUB temp.
+// states and one 48-byte blend record per Gaussian added, no CUB temp.
 #pragma once
 #include "common.cuh"
 
@@ -19,6 +19,15 @@ static inline size_t sort_ws_bytes(size_t n) {
            align_up((size_t)SORT_MAX_PASSES * sort_tiles(n) * SORT_RADIX * 4, 128);
 }
 
+// Blend inputs of one Gaussian, written by the preprocess kernel and gathered into shared memory by the blend kernels
+// through the tile's sorted id list (three 16-byte async copies per record).
+struct __align__(16) SplatRec {
+    float x, y, conx, cony;      // projected mean, conic xx, xy
+    float conz, opac, r, g;      // conic yy, opacity (AA-compensated), colour
+    float b, invdepth, t, invkids;  // colour, 1/view depth (rcp.rn), LOD weight (alpha cut-off without LOD), 1/kids
+};
+static_assert(sizeof(SplatRec) == 48, "SplatRec must be 48 bytes");
+
 struct GeomHeader {
     unsigned num_rendered;  // total (Gaussian,tile) instances, written by the last preprocess tile
     int ticket;             // dynamic tile dispenser for the fused scan
@@ -29,14 +38,10 @@ struct GeomHeader {
 struct GeomState {
     GeomHeader* hdr;
     unsigned long long* scan_state;  // [ceil(P/PRE_BLOCK)]
-    float* depths;                   // [P]
-    float2* means2D;                 // [P]
-    float4* conic_opacity;           // [P]
-    float* rgb;                      // [P,3]
+    SplatRec* recs;                  // [P] blend inputs of every visible Gaussian (gathered by the blend kernels)
     float* cov3D;                    // [P,6]
     uint8_t* clamped;                // [P] bit c set = channel c clamped to 0
     uint32_t* tiles_touched;         // [P]
-    uint32_t* point_offsets;         // [P] (unused since the depth-ordered emission; kept so that the layout indices stay put)
     int2* rects;                     // [P]
     // depth-ordered emission (raster_api.cu): Gaussians sorted by depth bits, then their tile counts scanned in that order
     uint32_t* depth_keys;            // [P] depth bits, 0xffffffff for culled Gaussians
@@ -69,16 +74,12 @@ static inline GeomState geom_from_chunk(void* chunk, size_t P) {
     g.scan_state = carve_arr<unsigned long long>(b, off, (P + PRE_BLOCK - 1) / PRE_BLOCK + 1);
     g.scan2_state = carve_arr<unsigned long long>(b, off, (P + PRE_BLOCK - 1) / PRE_BLOCK + 1);
     g.zero_bytes = off;
-    g.depths = carve_arr<float>(b, off, P);            g.offsets[0] = (char*)g.depths - b;
-    g.means2D = carve_arr<float2>(b, off, P);          g.offsets[1] = (char*)g.means2D - b;
-    g.conic_opacity = carve_arr<float4>(b, off, P);    g.offsets[2] = (char*)g.conic_opacity - b;
-    g.rgb = carve_arr<float>(b, off, P * 3);           g.offsets[3] = (char*)g.rgb - b;
+    g.depth_keys = carve_arr<uint32_t>(b, off, P);     g.offsets[0] = (char*)g.depth_keys - b;
+    g.recs = carve_arr<SplatRec>(b, off, P);           g.offsets[1] = g.offsets[2] = g.offsets[3] = (char*)g.recs - b;
     g.cov3D = carve_arr<float>(b, off, P * 6);         g.offsets[4] = (char*)g.cov3D - b;
     g.clamped = carve_arr<uint8_t>(b, off, P);         g.offsets[5] = (char*)g.clamped - b;
     g.tiles_touched = carve_arr<uint32_t>(b, off, P);  g.offsets[6] = (char*)g.tiles_touched - b;
-    g.point_offsets = carve_arr<uint32_t>(b, off, P);  g.offsets[7] = (char*)g.point_offsets - b;
-    g.rects = carve_arr<int2>(b, off, P);              g.offsets[8] = (char*)g.rects - b;
-    g.depth_keys = carve_arr<uint32_t>(b, off, P);
+    g.rects = carve_arr<int2>(b, off, P);              g.offsets[7] = g.offsets[8] = (char*)g.rects - b;
     g.depth_keys_sorted = carve_arr<uint32_t>(b, off, P);
     g.order = carve_arr<uint32_t>(b, off, P);
     g.sort_tmp_k = carve_arr<uint32_t>(b, off, P);
@@ -91,14 +92,6 @@ static inline GeomState geom_from_chunk(void* chunk, size_t P) {
     g.bytes = align_up(off, 128);
     return g;
 }
-
-// Sorted per-instance splat record staged into shared memory by 1-D bulk copies in the blend kernels.
-struct __align__(16) SplatRec {
-    float x, y, conx, cony;      // projected mean, conic xx, xy
-    float conz, opac, r, g;      // conic yy, opacity (AA-compensated), colour
-    float b, invdepth, t, invkids;  // colour, 1/view depth (rcp.rn), LOD weight, 1/kids
-};
-static_assert(sizeof(SplatRec) == 48, "SplatRec must be 48 bytes");
 
 struct SortWs {
     unsigned* hist;                  // [SORT_MAX_PASSES][256] global digit histograms -> exclusive bases
@@ -123,9 +116,7 @@ struct BinningState {
     uint32_t* tiles_unsorted;  // [R] tile id of every instance, emitted in (depth, index) order of the Gaussians
     uint32_t* vals_unsorted;   // [R] list position of the instance's Gaussian, same order
     uint32_t* tiles_sorted;    // [R] tile ids after the stable sort by tile
-    uint64_t* keys;            // [R] sorted tile|depth keys (identical to the reference's sorted key list)
-    uint32_t* point_list;      // [R] sorted
-    SplatRec* recs;            // [R] sorted splat records
+    uint32_t* point_list;      // [R] list positions of the Gaussians, sorted by (tile, depth bits, index)
     void* sort_ws;
     size_t offsets[5];
     size_t bytes;
@@ -136,10 +127,8 @@ static inline BinningState binning_from_chunk(void* chunk, size_t R) {
     size_t off = 0;
     s.tiles_unsorted = carve_arr<uint32_t>(b, off, R); s.offsets[0] = (char*)s.tiles_unsorted - b;
     s.vals_unsorted = carve_arr<uint32_t>(b, off, R);  s.offsets[1] = (char*)s.vals_unsorted - b;
-    s.tiles_sorted = carve_arr<uint32_t>(b, off, R);
-    s.keys = carve_arr<uint64_t>(b, off, R);           s.offsets[2] = (char*)s.keys - b;
-    s.point_list = carve_arr<uint32_t>(b, off, R + 8); s.offsets[3] = (char*)s.point_list - b;
-    s.recs = carve_arr<SplatRec>(b, off, R);           s.offsets[4] = (char*)s.recs - b;
+    s.tiles_sorted = carve_arr<uint32_t>(b, off, R);   s.offsets[2] = (char*)s.tiles_sorted - b;
+    s.point_list = carve_arr<uint32_t>(b, off, R + 8); s.offsets[3] = s.offsets[4] = (char*)s.point_list - b;
     off = align_up(off, 128);
     s.sort_ws = b + off;
     off += sort_from_chunk(nullptr, R).bytes;

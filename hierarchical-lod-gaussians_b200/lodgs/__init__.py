@@ -64,7 +64,8 @@ _SIGS = {
     "lodgs_geom_layout": (_i, [_i, _p]),
     "lodgs_binning_layout": (_i, [_i, _p]),
     "lodgs_image_layout": (_i, [_i, _i, _p]),
-    "lodgs_blend_stats": (_i, [_i, _i, _i, _i, _p, _p, _p, _p]),
+    "lodgs_blend_stats": (_i, [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p]),
+    "lodgs_sorted_keys": (_i, [_i, _i, _p, _p, _p, _p]),
     "lodgs_sort_workspace_bytes": (_sz, [_i]),
     "lodgs_sort_pairs": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _p, _sz, _p]),
     "lodgs_backward_overwrites_dsh": (_i, [_i, _i, _i, _p, _p]),

@@ -108,10 +108,12 @@ size_t lodgs_geom_bytes(int P);
 size_t lodgs_image_bytes(int W, int H);
 size_t lodgs_binning_bytes(int R);
 
-/* Stage 1: preprocessCUDA (HR forward.cu:218-445) fused with the tile-count prefix sum
- * (rasterizer_impl.cu:322). Writes radii[P], the geometry state, and the number of
- * (Gaussian,tile) instances R. If num_rendered_host is non-NULL, R is copied back and the stream
- * synchronised (rasterizer_impl.cu:330-331). */
+/* Stage 1: preprocessCUDA (HR forward.cu:218-445). Writes radii[P], the geometry state (one 48-byte blend record,
+ * cov3D, clamp bits, tile box and depth bits per Gaussian) and the number of (Gaussian,tile) instances R; then orders the
+ * Gaussians by depth bits (onesweep radix sort over P u32 keys) and scans their tile counts in that order, which
+ * replaces the index-order InclusiveSum of rasterizer_impl.cu:322. If num_rendered_host is non-NULL, R is copied back
+ * through a pinned staging word and the call waits for it (rasterizer_impl.cu:330-331). colors_precomp, when given, is
+ * folded into the blend records here. */
 int lodgs_forward_preprocess(int P, int D, int M, int W, int H,
                              const int32_t* indices, const int32_t* parent_indices, const float* ts,
                              const float* means3D, const float* shs, const float* colors_precomp,
@@ -125,8 +127,9 @@ int lodgs_forward_preprocess(int P, int D, int M, int W, int H,
  * tile|depth keys (:358-363) + identifyTileRanges (:120-142) + renderCUDA (forward.cu:450-596). Stage 1 has already
  * ordered the Gaussians by depth bits (onesweep radix sort over P u32 keys); stage 2 emits the (tile, Gaussian) instances
  * in that order, sorts them stably by tile id alone (2 onesweep passes at 1080p instead of 6 over 64-bit keys), which
- * yields exactly the reference's sorted list, then builds keys / tile ranges / sorted splat records and blends.
- * R is the value stage 1 reported.
+ * yields exactly the reference's sorted list, then finds the tile ranges and blends; the blend kernels gather the
+ * per-Gaussian records through the sorted id list, so no per-instance record or key array is written.
+ * R is the value stage 1 reported; ts/kids non-NULL select the hierarchical-LOD alpha.
  * out_color [3,H,W]; out_invdepth [H,W] or NULL; seen [P] i32 or NULL (must be zero-filled by the caller,
  * as the reference's torch::full does). */
 int lodgs_forward_render(int P, int W, int H, int R, const float* background,
@@ -163,12 +166,13 @@ int lodgs_mark_visible(int P, const float* means3D, const float* viewmatrix, con
                        uint8_t* present, void* stream);
 
 /* Parity-test accessors: byte offsets of the arrays inside the opaque buffers.
- * geom:   [0]=depths f32[P] [1]=means2D f32[P,2] [2]=conic_opacity f32[P,4] [3]=rgb f32[P,3]
+ * geom:   [0]=depth bits u32[P] (view-space depth as f32 bits; 0xffffffff for culled Gaussians)
+ *         [1]=[2]=[3]=blend records f32[P,12], rows of visible Gaussians only:
+ *             mean2D.x mean2D.y conic.xx conic.xy | conic.yy opacity r g | b 1/depth t-or-cut 1/kids
  *         [4]=cov3D f32[P,6] [5]=clamped u8[P] (bit c = channel c clamped) [6]=tiles_touched u32[P]
- *         [7]=(unused) [8]=rects i32[P,2]
+ *         [7]=[8]=rects i32[P,2]
  * binning:[0]=tiles_unsorted u32[R] [1]=values_unsorted u32[R]  (instances emitted in (depth bits, index) order of their
- *         Gaussians, carrying only the tile id) [2]=keys_sorted u64[R] tile|depth [3]=point_list u32[R]
- *         [4]=splat records f32[R,12]
+ *         Gaussians, carrying only the tile id) [2]=tiles_sorted u32[R] [3]=[4]=point_list u32[R]
  * image:  [0]=final_T f32[W*H] [1]=n_contrib u32[W*H] [2]=ranges u32[tiles,2] */
 int lodgs_geom_layout(int P, size_t* offsets9);
 int lodgs_binning_layout(int R, size_t* offsets5);
@@ -177,8 +181,13 @@ int lodgs_image_layout(int W, int H, size_t* offsets3);
 /* Work counters of the blend for roofline reports (bench.py): after a forward, counts over all pixels the pairs
  * whose quadratic form is evaluated (N_test), that reach the exponential (N_alpha) and that are blended (N_blend)
  * into counters3_dev[0..2] (device u64). Not used by any product path. */
-int lodgs_blend_stats(int W, int H, int R, int lod, void* binning_buffer, void* image_buffer, uint64_t* counters3_dev,
-                      void* stream);
+int lodgs_blend_stats(int P, int W, int H, int R, int lod, void* geom_buffer, void* binning_buffer, void* image_buffer,
+                      uint64_t* counters3_dev, void* stream);
+
+/* Parity-test accessor: the reference's sorted 64-bit key list (tile << 32 | depth bits, rasterizer_impl.cu:358-363),
+ * rebuilt after a forward from the sorted tile ids, the sorted id list and the depth bits into keys_out u64[R].
+ * The product path never materialises these keys. */
+int lodgs_sorted_keys(int P, int R, void* geom_buffer, void* binning_buffer, uint64_t* keys_out, void* stream);
 
 /* Stand-alone stable LSD radix sort of (u64 key, u32 value) pairs on bits [0,end_bit) — the onesweep
  * kernel used inside lodgs_forward_render, exported for the CUB cross-check tests.

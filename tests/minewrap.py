@@ -36,10 +36,14 @@ def forward(sc, cam, bg, indices=None, parent_indices=None, ts=None, kids=None, 
            "geom": geom, "binning": binning, "img": img}
     o = (C.c_size_t * 9)()
     lodgs.lib.lodgs_geom_layout(P, o)
-    res["depths"] = _view(geom, o[0], P * 4, torch.float32, (P,))
-    res["means2D"] = _view(geom, o[1], P * 8, torch.float32, (P, 2))
-    res["conic_opacity"] = _view(geom, o[2], P * 16, torch.float32, (P, 4))
-    res["rgb"] = _view(geom, o[3], P * 12, torch.float32, (P, 3))
+    # per-Gaussian blend records (include/lodgs.h): rows of culled Gaussians are never written -> masked to zero here
+    vis = (radii > 0)
+    recs = torch.where(vis[:, None], _view(geom, o[1], P * 48, torch.float32, (P, 12)), torch.zeros((), device=geom.device))
+    res["recs"] = recs
+    res["depths"] = torch.where(vis, _view(geom, o[0], P * 4, torch.float32, (P,)), torch.zeros((), device=geom.device))
+    res["means2D"] = recs[:, 0:2].contiguous()
+    res["conic_opacity"] = recs[:, 2:6].contiguous()
+    res["rgb"] = recs[:, 6:9].contiguous()
     res["cov3D"] = _view(geom, o[4], P * 24, torch.float32, (P, 6))
     res["clamped_bits"] = _view(geom, o[5], P, torch.uint8, (P,))
     res["tiles_touched"] = _view(geom, o[6], P * 4, torch.int32, (P,))
@@ -49,9 +53,12 @@ def forward(sc, cam, bg, indices=None, parent_indices=None, ts=None, kids=None, 
         lodgs.lib.lodgs_binning_layout(R, b)
         res["tiles_unsorted"] = _view(binning, b[0], R * 4, torch.int32, (R,))   # depth-ordered emission
         res["vals_unsorted"] = _view(binning, b[1], R * 4, torch.int32, (R,))
-        res["keys"] = _view(binning, b[2], R * 8, torch.int64, (R,))
+        res["tiles_sorted"] = _view(binning, b[2], R * 4, torch.int32, (R,))
         res["point_list"] = _view(binning, b[3], R * 4, torch.int32, (R,))
-        res["recs"] = _view(binning, b[4], R * 48, torch.float32, (R, 12))
+        keys = torch.empty(R, dtype=torch.int64, device=geom.device)
+        lodgs.check(lodgs.lib.lodgs_sorted_keys(P, R, geom.data_ptr(), binning.data_ptr(), keys.data_ptr(), lodgs.current_stream()))
+        torch.cuda.synchronize()
+        res["keys"] = keys
         im = (C.c_size_t * 3)()
         lodgs.lib.lodgs_image_layout(W, H, im)
         ntiles = ((W + 15) // 16) * ((H + 15) // 16)

@@ -28,7 +28,8 @@ def _worker(rank, world, port, q):
     nbytes = parallel.allreduce_gradients(grads)
     lo, hi = parallel.shard_range(11, rank, world)
     t = parallel.gather_timings(torch.arange(lo, hi, dtype=torch.float64))
-    q.put((rank, [None if x is None else x.clone() for x in grads], nbytes, [x.tolist() for x in t]))
+    # numpy arrays travel by value; torch tensors would be passed as shared-memory handles that die with this process
+    q.put((rank, [None if x is None else x.numpy().copy() for x in grads], nbytes, [x.tolist() for x in t]))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -50,7 +51,7 @@ def test_gradient_allreduce_two_ranks():
         exp.append([torch.randn(50, 3, generator=g), torch.randn(50, 16, 3, generator=g), torch.randn(50, 1, generator=g)])
     sums = [exp[0][i] + exp[1][i] for i in range(3)]
     for rank, grads, nbytes, timings in res:
-        got = [x for x in grads if x is not None]
+        got = [torch.from_numpy(x) for x in grads if x is not None]
         assert nbytes == 4 * (150 + 2400 + 50)
         for a, b in zip(got, sums):
             assert torch.allclose(a, b, atol=0, rtol=0)
