@@ -42,6 +42,7 @@ struct PreBwdParams {
     float* dL_dscale;
     float* dL_drot;
     int sh_vec4;
+    int write_all;  // no index list and no parents: every row [0,P) of dL_dmean3D / dL_dcov3D / dL_dscale / dL_drot is stored (no RMW)
 };
 
 __device__ __forceinline__ float sq(float x) { return x * x; }
@@ -73,6 +74,18 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
     __syncthreads();
     const int t_idx = tile_base + threadIdx.x;
     const bool active = t_idx < p.P && (__ldg(p.radii + t_idx) > 0);
+    if (p.write_all && !active && t_idx < p.P) {
+        // culled Gaussians get their zero gradients here, so the caller need not zero-fill these four tensors
+        float* m = p.dL_dmean3D + 3 * (size_t)t_idx;
+        m[0] = m[1] = m[2] = 0.f;
+        float2* c = reinterpret_cast<float2*>(p.dL_dcov3D + 6 * (size_t)t_idx);
+        c[0] = c[1] = c[2] = make_float2(0.f, 0.f);
+        if (p.scales) {
+            float* sc = p.dL_dscale + 3 * (size_t)t_idx;
+            sc[0] = sc[1] = sc[2] = 0.f;
+            reinterpret_cast<float4*>(p.dL_drot)[t_idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
     if (STAGED) {
         if (!active) {
             // culled rows still travel with the block store: they carry the zeros the caller's zero-fill put there
@@ -354,9 +367,15 @@ __device__ __forceinline__ void preprocess_bwd_one(const PreBwdParams& p, int t_
         atomicAdd(p.dL_dmean3D + 3 * (size_t)parent_id + 2, (1.0f - tt) * dmean.z);
     } else {
         p.dL_dopacity[idx] = dL_dopacity_out;
-        atomicAdd(p.dL_dmean3D + 3 * (size_t)idx + 0, dmean.x);
-        atomicAdd(p.dL_dmean3D + 3 * (size_t)idx + 1, dmean.y);
-        atomicAdd(p.dL_dmean3D + 3 * (size_t)idx + 2, dmean.z);
+        if (p.write_all) {
+            p.dL_dmean3D[3 * (size_t)idx + 0] = dmean.x;
+            p.dL_dmean3D[3 * (size_t)idx + 1] = dmean.y;
+            p.dL_dmean3D[3 * (size_t)idx + 2] = dmean.z;
+        } else {
+            atomicAdd(p.dL_dmean3D + 3 * (size_t)idx + 0, dmean.x);
+            atomicAdd(p.dL_dmean3D + 3 * (size_t)idx + 1, dmean.y);
+            atomicAdd(p.dL_dmean3D + 3 * (size_t)idx + 2, dmean.z);
+        }
     }
 }
 
@@ -394,6 +413,7 @@ int run_preprocess_bwd(int P, int D, int M, const int32_t* indices, const int32_
     p.focal_x = focal_x; p.focal_y = focal_y; p.tan_fovx = tan_fovx; p.tan_fovy = tan_fovy; p.dL_dmean2D = dL_dmean2D; p.dL_dconic = dL_dconic;
     p.dL_dinvdepth = dL_dinvdepth; p.dL_dcolor = dL_dcolor; p.dL_dopacity = dL_dopacity; p.dL_dmean3D = dL_dmean3D; p.dL_dcov3D = dL_dcov3D;
     p.dL_dsh = dL_dsh; p.dL_dscale = dL_dscale; p.dL_drot = dL_drot;
+    p.write_all = lodgs_backward_overwrites_geometry(indices != nullptr, parent_indices != nullptr);
     p.sh_vec4 = (shs && ((uintptr_t)shs & 15) == 0 && (M * 3) % 4 == 0) ? 1 : 0;
     if (parent_indices && !ts) { set_error("lodgs_backward: parent_indices without ts"); return LODGS_E_ARG; }
     return launch_preprocess_bwd(p, s);
@@ -402,6 +422,10 @@ int run_preprocess_bwd(int P, int D, int M, const int32_t* indices, const int32_
 
 // 1 when lodgs_backward takes the staged path of preprocess_bwd_kernel, which writes EVERY row of dL_dsh[0..P) (zeros for
 // culled Gaussians): the caller may then skip the zero-fill of that tensor (192 B per Gaussian at M = 16).
+// 1 when lodgs_backward stores every row [0,P) of dL_dmean3D and dL_dcov3D, and of dL_dscale / dL_drot when scales are given
+// (zeros for culled Gaussians): without an index list no other row exists and without parents nothing is scattered.
+extern "C" int lodgs_backward_overwrites_geometry(int has_indices, int has_parents) { return (!has_indices && !has_parents) ? 1 : 0; }
+
 extern "C" int lodgs_backward_overwrites_dsh(int M, int has_indices, int has_parents, const float* shs, const float* dL_dsh) {
     return (shs && dL_dsh && !has_indices && !has_parents && M > 0 && M <= 16 && (M * 12) % 16 == 0 && ((uintptr_t)shs & 15) == 0 &&
             ((uintptr_t)dL_dsh & 15) == 0) ? 1 : 0;

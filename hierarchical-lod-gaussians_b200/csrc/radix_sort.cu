@@ -4,7 +4,7 @@
 // digits over bits [0,end_bit): one histogram pass over the keys builds all digit histograms at once, then one
 // kernel per digit does rank -> decoupled look-back -> scatter, reading and writing every pair exactly once
 // per pass. Stability (and therefore bit-identical output to CUB) comes from ranking keys in index order:
-// warp-striped tiles, per-warp match-any ranking, warps and tiles chained in order.
+// warp-striped tiles, per-warp ballot ranking, warps and tiles chained in order.
 //
 // The kernels are templated on the key type: u64 keys serve the exported lodgs_sort_pairs (the reference's tile|depth
 // sort, kept for the CUB cross-check), u32 keys serve the two sorts of the forward pass (Gaussians by depth bits, then
@@ -122,32 +122,49 @@ __global__ void __launch_bounds__(SORT_THREADS, sizeof(KeyT) == 4 ? 4 : 2) sort_
             key[k] = ~(KeyT)0;
         }
     }
-    // ---- rank inside the warp, item by item (index order => stable). The 16 match-any instructions are independent
-    // and issued back to back; only the running per-digit counts of the warp are a serial chain (one LDS/STS per round).
+    // ---- rank inside the warp, item by item (index order => stable). Per group of RANK_GROUP items: the peer masks
+    // are computed first; then the leader lane of every digit group bumps the warp's
+    // running per-digit count with ONE shared-memory atomic per item whose return value is not consumed until all
+    // atomics of the group are in flight (same-warp shared atomics execute in issue order; __syncwarp orders them
+    // formally) — a chain of SORT_ITEMS / RANK_GROUP round trips instead of SORT_ITEMS LDS -> STS -> SHFL ones.
     unsigned* wh = sm.warp_hist[warp];
+    constexpr int RANK_GROUP = 8;
+    const unsigned lt_mask = (1u << lane) - 1u;
 #pragma unroll
-    for (int k = 0; k < SORT_ITEMS; k++) {
-        const int e = wbase + k * 32 + lane;
-        const bool valid = e < tile_n;
-        const unsigned d = (unsigned)(key[k] >> shift) & 255u;
-        // invalid lanes match on a private value so that they never join a digit group
-        rank[k] = __match_any_sync(0xffffffffu, valid ? d : (256u + lane));
-    }
+    for (int g = 0; g < SORT_ITEMS; g += RANK_GROUP) {
+        unsigned old[RANK_GROUP];
 #pragma unroll
-    for (int k = 0; k < SORT_ITEMS; k++) {
-        const int e = wbase + k * 32 + lane;
-        const bool valid = e < tile_n;
-        const unsigned d = (unsigned)(key[k] >> shift) & 255u;
-        const unsigned mask = rank[k];
-        const int leader = __ffs(mask) - 1;
-        unsigned old = 0;
-        if ((int)lane == leader && valid) {
-            old = wh[d];
-            wh[d] = old + __popc(mask);
+        for (int k = g; k < g + RANK_GROUP; k++) {
+            const int e = wbase + k * 32 + lane;
+            const bool valid = e < tile_n;
+            const unsigned d = (unsigned)(key[k] >> shift) & 255u;
+            // peers = lanes holding the same digit, from 8 ballots (one per digit bit). MATCH.ANY does the same in one
+            // instruction but its cost grows with the number of distinct values in the warp (measured: ~half of the
+            // kernel's stall samples sat behind it on high-entropy digits); 8 VOTE + 8 LOP3 issue at full rate.
+            unsigned peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+            for (int b = 0; b < 8; b++) {
+                const bool bit = (d >> b) & 1u;
+                const unsigned bal = __ballot_sync(0xffffffffu, bit);
+                peers &= bit ? bal : ~bal;
+            }
+            rank[k] = valid ? peers : (1u << lane);  // invalid lanes form private groups and never touch the counters
         }
-        old = __shfl_sync(0xffffffffu, old, leader);
-        rank[k] = old + __popc(mask & ((1u << lane) - 1u));
-        __syncwarp();
+#pragma unroll
+        for (int k = g; k < g + RANK_GROUP; k++) {
+            const int e = wbase + k * 32 + lane;
+            const bool valid = e < tile_n;
+            const unsigned d = (unsigned)(key[k] >> shift) & 255u;
+            const unsigned mask = rank[k];
+            old[k - g] = 0;
+            if ((mask & lt_mask) == 0u && valid) old[k - g] = atomicAdd(&wh[d], (unsigned)__popc(mask));  // lowest lane of the group
+            __syncwarp();
+        }
+#pragma unroll
+        for (int k = g; k < g + RANK_GROUP; k++) {
+            const unsigned mask = rank[k];
+            rank[k] = __shfl_sync(0xffffffffu, old[k - g], __ffs(mask) - 1) + __popc(mask & lt_mask);
+        }
     }
     __syncthreads();
 

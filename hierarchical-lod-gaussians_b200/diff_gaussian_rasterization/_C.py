@@ -85,16 +85,37 @@ def rasterize_gaussians_backward(background, indices, parent_indices, ts, kids, 
     P = fullP if indices.numel() == 0 else indices.size(0)
     H, W = dL_dout_color.size(1), dL_dout_color.size(2)
     M = sh.size(1) if sh.numel() != 0 else 0
+    has_depth = dL_dout_invdepth is not None and dL_dout_invdepth.numel() != 0
+    # The five tensors the blend accumulates into with atomics are carved from ONE zero-filled allocation (one fill
+    # kernel instead of five); the reference allocates each with torch::zeros (rasterize_points.cu:178-187).
+    acc = torch.zeros((fullP * (3 + NUM_CHANNELS + 4 + 1 + (1 if has_depth else 0)),), dtype=torch.float32, device=dev)
+    o = 0
+
+    def carve(*shape):
+        nonlocal o
+        n = 1
+        for d in shape:
+            n *= d
+        v = acc[o:o + n].view(*shape)
+        o += n
+        return v
+
+    dL_dconic = carve(fullP, 2, 2)  # first: keeps the 16-byte rows aligned
+    dL_dmeans2D, dL_dcolors, dL_dopacity = carve(fullP, 3), carve(fullP, NUM_CHANNELS), carve(fullP, 1)
+    dL_dinvdepths = carve(fullP, 1) if has_depth else torch.zeros((0, 1), dtype=torch.float32, device=dev)
+    # Tensors the library stores every row of need no zero-fill.
+    own_geom = P != 0 and bool(lib.lodgs_backward_overwrites_geometry(int(indices.numel() != 0), int(parent_indices.numel() != 0)))
+    alloc = (lambda *shape: torch.empty(shape, dtype=torch.float32, device=dev)) if own_geom else \
+        (lambda *shape: torch.zeros(shape, dtype=torch.float32, device=dev))
     z = lambda *shape: torch.zeros(shape, dtype=torch.float32, device=dev)  # noqa: E731
-    dL_dmeans3D, dL_dmeans2D, dL_dcolors = z(fullP, 3), z(fullP, 3), z(fullP, NUM_CHANNELS)
-    dL_dconic, dL_dopacity, dL_dcov3D = z(fullP, 2, 2), z(fullP, 1), z(fullP, 6)
-    dL_dscales, dL_drotations = z(fullP, 3), z(fullP, 4)
+    dL_dmeans3D, dL_dcov3D = alloc(fullP, 3), alloc(fullP, 6)
+    has_scales = scales.numel() != 0
+    dL_dscales = alloc(fullP, 3) if has_scales else z(fullP, 3)
+    dL_drotations = alloc(fullP, 4) if has_scales else z(fullP, 4)
     dL_dsh = torch.empty((fullP, M, 3), dtype=torch.float32, device=dev)
     if not (P != 0 and sh.numel() and sh.device == dev and sh.is_contiguous() and
             lib.lodgs_backward_overwrites_dsh(M, int(indices.numel() != 0), int(parent_indices.numel() != 0), ptr(sh), ptr(dL_dsh))):
         dL_dsh.zero_()
-    has_depth = dL_dout_invdepth is not None and dL_dout_invdepth.numel() != 0
-    dL_dinvdepths = z(fullP, 1) if has_depth else z(0, 1)
     if P != 0:
         t = [_f(x.to(dev)) if x.numel() and x.device != dev else _f(x) for x in
              (background, indices, parent_indices, ts, kids, means3D, colors, opacities, scales, rotations, cov3D_precomp,

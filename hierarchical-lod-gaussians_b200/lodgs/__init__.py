@@ -69,6 +69,7 @@ _SIGS = {
     "lodgs_sort_workspace_bytes": (_sz, [_i]),
     "lodgs_sort_pairs": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _p, _sz, _p]),
     "lodgs_backward_overwrites_dsh": (_i, [_i, _i, _i, _p, _p]),
+    "lodgs_backward_overwrites_geometry": (_i, [_i, _i]),
     "lodgs_adam_step": (_i, [_p, _p, _p, _p, _p, _i64, _p, _i64, _i, _d, _d, _d, _d, _i64, _i, _p]),
 }
 

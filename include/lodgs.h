@@ -161,6 +161,12 @@ int lodgs_backward(int P, int fullP, int D, int M, int R, int W, int H, const fl
  * allocates (rasterize_points.cu:183). */
 int lodgs_backward_overwrites_dsh(int M, int has_indices, int has_parents, const float* shs, const float* dL_dsh);
 
+/* 1 when lodgs_backward stores every row [0,P) of dL_dmean3D and dL_dcov3D — and of dL_dscale / dL_drot when scales are
+ * given — itself, zeros for culled Gaussians (no index list, no parents): the caller may then pass these four tensors
+ * uninitialised instead of zero-filled (rasterize_points.cu:178-187). The tensors the blend accumulates into with
+ * atomics (dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dinvdepth) must always be zero-filled. */
+int lodgs_backward_overwrites_geometry(int has_indices, int has_parents);
+
 /* checkFrustum (HR rasterizer_impl.cu:54-66,145-157): present[i] = (view-space z > 0.2). present is u8[P]. */
 int lodgs_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                        uint8_t* present, void* stream);
