@@ -74,12 +74,13 @@ __device__ __forceinline__ float warp_reduce10(const float (&v)[NV], unsigned la
 
 // One (pixel, splat) pair of the replay (backward.cu:600-716); adds this pixel's ten partial gradients to v.
 template <bool LOD, bool DEPTH>
-__device__ __forceinline__ bool bwd_pair(BwdPix& p, const float4 q0, const float4 q1, const float4 q2, float (&v)[NV]) {
-    const float dx = __fsub_rn(q0.x, p.px), dy = __fsub_rn(q0.y, p.py);
-    const float quad = __fmaf_rn(dx, __fmul_rn(dx, q0.z), __fmul_rn(dy, __fmul_rn(dy, q1.x)));
-    const float power = __fsub_rn(__fmul_rn(quad, -0.5f), __fmul_rn(dy, __fmul_rn(dx, q0.w)));
+__device__ __forceinline__ bool bwd_pair(BwdPix& p, const float dx, const float dxa, const float dxb, const float4 q0, const float4 q1,
+                                         const float4 q2, float (&v)[NV]) {
+    const float dy = __fsub_rn(q0.y, p.py);
+    const float quad = __fmaf_rn(dx, dxa, __fmul_rn(dy, __fmul_rn(dy, q1.x)));
+    const float power = __fsub_rn(__fmul_rn(quad, -0.5f), __fmul_rn(dy, dxb));
     if (power > 0.0f) return false;
-    if (!LOD && power < q2.z) return false;  // certainly below the 1/255 cut (see build_records_kernel)
+    if (!LOD && power < q2.z) return false;  // certainly below the 1/255 cut (see preprocess_one)
     // ex2.approx instead of the forward's full-range expf (8 fewer instructions per pair): alpha moves by ~1e-7 relative, so a
     // pair can change sides of the 1/255 cut only when it sits within that distance of it — its contribution is then 0.4 % of
     // one pixel, far inside the 1e-3 relative-L2 budget of the gradients
@@ -284,8 +285,10 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
             for (int k = 0; k < NV; k++) v[k] = 0.f;
             const float4 q0 = rp[0], q1 = rp[1], q2 = rp[2];
             bool contrib = false;
-            if (act0) contrib |= bwd_pair<LOD, DEPTH>(px[0], q0, q1, q2, v);
-            if (act1) contrib |= bwd_pair<LOD, DEPTH>(px[1], q0, q1, q2, v);
+            // the thread's two pixels share the column: dx and its two products are computed once
+            const float dx = __fsub_rn(q0.x, px[0].px), dxa = __fmul_rn(dx, q0.z), dxb = __fmul_rn(dx, q0.w);
+            if (act0) contrib |= bwd_pair<LOD, DEPTH>(px[0], dx, dxa, dxb, q0, q1, q2, v);
+            if (act1) contrib |= bwd_pair<LOD, DEPTH>(px[1], dx, dxa, dxb, q0, q1, q2, v);
             if (!__any_sync(0xffffffffu, contrib)) continue;
             int slot;
             const float total = warp_reduce10(v, lane, slot);

@@ -29,14 +29,15 @@ struct PixState {
 
 // One (pixel, splat) pair; rounding pinned to the reference build's PTX for renderCUDA (forward.cu:529-585):
 // power = (dx*(dx*con.x) + dy*(dy*con.z)) * -0.5 - dy*(dx*con.y), C += T * (alpha * c).
+// dx, dxa = dx*con.x and dxb = dx*con.y are shared by the thread's two pixels (same column) and come from the caller.
 template <bool LOD, bool DEPTH, bool SEEN>
-__device__ __forceinline__ void blend_pair(PixState& p, unsigned& done, const float4 q0, const float4 q1, const float4 q2, uint32_t contributor,
-                                           uint8_t* flagp) {
-    const float dx = __fsub_rn(q0.x, p.px), dy = __fsub_rn(q0.y, p.py);
-    const float quad = __fmaf_rn(dx, __fmul_rn(dx, q0.z), __fmul_rn(dy, __fmul_rn(dy, q1.x)));
-    const float power = __fsub_rn(__fmul_rn(quad, -0.5f), __fmul_rn(dy, __fmul_rn(dx, q0.w)));
+__device__ __forceinline__ void blend_pair(PixState& p, unsigned& done, const float dx, const float dxa, const float dxb, const float4 q0,
+                                           const float4 q1, const float4 q2, uint32_t contributor, uint8_t* flagp) {
+    const float dy = __fsub_rn(q0.y, p.py);
+    const float quad = __fmaf_rn(dx, dxa, __fmul_rn(dy, __fmul_rn(dy, q1.x)));
+    const float power = __fsub_rn(__fmul_rn(quad, -0.5f), __fmul_rn(dy, dxb));
     if (power > 0.0f) return;
-    if (!LOD && power < q2.z) return;  // alpha is certainly below 1/255 (cut-off precomputed per splat, see build_records_kernel)
+    if (!LOD && power < q2.z) return;  // alpha is certainly below 1/255 (cut-off precomputed per splat, see preprocess_one)
     float alpha = fminf(0.99f, __fmul_rn(q1.y, expf(power)));
     if (LOD) {
         const float kidsqrt_alpha = __fsub_rn(1.0f, __powf(__fsub_rn(1.0f, alpha), q2.w));
@@ -169,8 +170,9 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* _
             const float4 q0 = rp[0];  // x y conx cony
             const float4 q1 = rp[1];  // conz opac r g
             const float4 q2 = rp[2];  // b 1/depth t 1/kids
-            if (!done0) blend_pair<LOD, DEPTH, SEEN>(p0, done0, q0, q1, q2, contributor, fl);
-            if (!done1) blend_pair<LOD, DEPTH, SEEN>(p1, done1, q0, q1, q2, contributor, fl);
+            const float dx = __fsub_rn(q0.x, p0.px), dxa = __fmul_rn(dx, q0.z), dxb = __fmul_rn(dx, q0.w);
+            if (!done0) blend_pair<LOD, DEPTH, SEEN>(p0, done0, dx, dxa, dxb, q0, q1, q2, contributor, fl);
+            if (!done1) blend_pair<LOD, DEPTH, SEEN>(p1, done1, dx, dxa, dxb, q0, q1, q2, contributor, fl);
         }
     }
     if (SEEN) {
