@@ -55,7 +55,7 @@ __device__ __forceinline__ void preprocess_bwd_one(const PreBwdParams& p, int t_
 // array, so they arrive in shared memory by ONE bulk copy (TMA) issued before the covariance math, and the dL_dsh rows
 // leave the same buffer by ONE bulk store — instead of 12+12 strided 16-byte accesses per thread (192-byte stride).
 template <bool STAGED>
-__global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams p) {
+__global__ void __launch_bounds__(256, 3) preprocess_bwd_kernel(const PreBwdParams p) {
     extern __shared__ __align__(128) float4 sh_stage[];  // [256][3M/4] when STAGED
     __shared__ float s_view[16], s_proj[16];
     __shared__ uint64_t s_bar;
