@@ -75,7 +75,7 @@ __device__ __forceinline__ float warp_reduce10(const float (&v)[NV], unsigned la
 // One (pixel, splat) pair of the replay (backward.cu:600-716); adds this pixel's ten partial gradients to v.
 template <bool LOD, bool DEPTH>
 __device__ __forceinline__ bool bwd_pair(BwdPix& p, const float dx, const float dxa, const float dxb, const float4 q0, const float4 q1,
-                                         const float4 q2, float (&v)[NV]) {
+                                         const float4 q2, const float null_thr, float (&v)[NV]) {
     const float dy = __fsub_rn(q0.y, p.py);
     const float quad = __fmaf_rn(dx, dxa, __fmul_rn(dy, __fmul_rn(dy, q1.x)));
     const float power = __fsub_rn(__fmul_rn(quad, -0.5f), __fmul_rn(dy, dxb));
@@ -86,7 +86,7 @@ __device__ __forceinline__ bool bwd_pair(BwdPix& p, const float dx, const float 
     // one pixel, far inside the 1e-3 relative-L2 budget of the gradients
     const float G = __expf(power);
     const float test_alpha = __fmul_rn(q1.y, G);
-    const bool nullalpha = test_alpha > 0.99f;
+    const bool nullalpha = test_alpha > null_thr;  // 0.99 (backward.cu:620,687); +inf with the alt-rasterizer's convention
     const float my_alpha = fminf(0.99f, test_alpha);
     float alpha = my_alpha, t = 1.f, frac = 1.f;
     if (LOD) {
@@ -136,7 +136,8 @@ __device__ __forceinline__ bool bwd_pair(BwdPix& p, const float dx, const float 
 template <bool LOD, bool DEPTH>
 __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
                                                                const uint32_t* __restrict__ point_list, int W, int H,
-                                                               const float* __restrict__ bg_color, const int32_t* __restrict__ indices,
+                                                               const float* __restrict__ bg_color, const float bg_mult,
+                                                               const float null_thr, const int32_t* __restrict__ indices,
                                                                const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
                                                                const float* __restrict__ dL_dpixels, const float* __restrict__ dL_invdepths,
                                                                float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic2D,
@@ -169,7 +170,7 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
         p.g1 = inside ? dL_dpixels[1 * HW + pix_id] : 0.f;
         p.g2 = inside ? dL_dpixels[2 * HW + pix_id] : 0.f;
         p.gd = (DEPTH && inside) ? dL_invdepths[pix_id] : 0.f;
-        p.bg_dot = bg0 * p.g0 + bg1 * p.g1 + bg2 * p.g2;
+        p.bg_dot = bg_mult * (bg0 * p.g0 + bg1 * p.g1 + bg2 * p.g2);
     }
 
     // the replay only has to cover splats up to the tile's deepest contributor
@@ -287,8 +288,8 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
             bool contrib = false;
             // the thread's two pixels share the column: dx and its two products are computed once
             const float dx = __fsub_rn(q0.x, px[0].px), dxa = __fmul_rn(dx, q0.z), dxb = __fmul_rn(dx, q0.w);
-            if (act0) contrib |= bwd_pair<LOD, DEPTH>(px[0], dx, dxa, dxb, q0, q1, q2, v);
-            if (act1) contrib |= bwd_pair<LOD, DEPTH>(px[1], dx, dxa, dxb, q0, q1, q2, v);
+            if (act0) contrib |= bwd_pair<LOD, DEPTH>(px[0], dx, dxa, dxb, q0, q1, q2, null_thr, v);
+            if (act1) contrib |= bwd_pair<LOD, DEPTH>(px[1], dx, dxa, dxb, q0, q1, q2, null_thr, v);
             if (!__any_sync(0xffffffffu, contrib)) continue;
             int slot;
             const float total = warp_reduce10(v, lane, slot);
@@ -300,7 +301,7 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
 }
 
 int launch_blend_bwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, const SplatRec* recs, int W, int H,
-                     const float* bg, const int32_t* indices, const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic,
+                     const float* bg, float bg_mult, float null_thr, const int32_t* indices, const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic,
                      float* dL_dopacity, float* dL_dcolor, float* dL_dinvdepth, cudaStream_t s) {
     dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1), block(BWD_THREADS, 1, 1);
     static bool attr_set = false;
@@ -312,7 +313,7 @@ int launch_blend_bwd(bool lod, bool depth, const ImageState& img, const BinningS
         attr_set = true;
     }
     const size_t smem = sizeof(BwdSmem);
-#define LODGS_BWD_ARGS img.ranges, recs, bin.point_list, W, H, bg, indices, img.final_T, img.n_contrib, dL_dpix, dL_dinvdepth_pix, \
+#define LODGS_BWD_ARGS img.ranges, recs, bin.point_list, W, H, bg, bg_mult, null_thr, indices, img.final_T, img.n_contrib, dL_dpix, dL_dinvdepth_pix, \
                        dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dinvdepth
     if (lod && depth) blend_bwd_kernel<true, true><<<grid, block, smem, s>>>(LODGS_BWD_ARGS);
     else if (lod) blend_bwd_kernel<true, false><<<grid, block, smem, s>>>(LODGS_BWD_ARGS);

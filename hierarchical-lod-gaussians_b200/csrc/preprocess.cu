@@ -38,6 +38,7 @@ struct PreParams {
     unsigned grid_x, grid_y;
     int sh_vec4;  // 1 when shs is 16-byte aligned and 3*M is a multiple of 4
     int staged;   // 1 when the SH rows of a tile are staged through shared memory by one bulk copy
+    unsigned flags;  // LODGS_RASTER_* (include/lodgs.h): alt-rasterizer conventions
 };
 
 // Load the (D+1)^2 RGB coefficient triples of Gaussian `idx`, lerped with parent `pidx` by t when has_parent
@@ -152,7 +153,9 @@ __device__ __forceinline__ uint32_t preprocess_one(const PreParams& p, const Geo
     cov.x = FA(cov.x, h_var);
     cov.z = FA(cov.z, h_var);
     const float det_cov_plus_h_cov = FF(cov.x, cov.z, -cov01sq);
-    const float h_convolution_scaling = __fsqrt_rn(fmaxf(__fdiv_rn(det_cov, det_cov_plus_h_cov), 0.000025f));
+    // AR/cuda_rasterizer/forward.cu:226-229: the alt-rasterizer applies the opacity compensation only with antialiasing=True
+    const float h_convolution_scaling =
+        (p.flags & LODGS_RASTER_NO_ANTIALIAS) ? 1.0f : __fsqrt_rn(fmaxf(__fdiv_rn(det_cov, det_cov_plus_h_cov), 0.000025f));
     const float det = det_cov_plus_h_cov;
     if (det == 0.0f) return 0;
     const float det_inv = __frcp_rn(det);
@@ -167,7 +170,9 @@ __device__ __forceinline__ uint32_t preprocess_one(const PreParams& p, const Geo
     uint2 rmin, rmax;
     const int2 my_rect = {(int)ceilf(FM(__fsqrt_rn(cov.x), 3.f)), (int)ceilf(FM(__fsqrt_rn(cov.z), 3.f))};
     g.rects[t_idx] = my_rect;
-    tile_rect(point_image, my_rect, rmin, rmax, p.grid_x, p.grid_y);
+    // AR/cuda_rasterizer/forward.cu:249 bounds the splat by the square of its largest 3-sigma radius instead of the per-axis rectangle
+    const int2 ext = (p.flags & LODGS_RASTER_SQUARE_RECT) ? make_int2((int)my_radius, (int)my_radius) : my_rect;
+    tile_rect(point_image, ext, rmin, rmax, p.grid_x, p.grid_y);
     if ((rmax.x - rmin.x) * (rmax.y - rmin.y) == 0) return 0;
     box = make_uint2(rmin.x | (rmin.y << 16), rmax.x | (rmax.y << 16));
 
@@ -274,6 +279,17 @@ extern "C" int lodgs_forward_preprocess(int P, int D, int M, int W, int H, const
                                         const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
                                         const float* campos, float tan_fovx, float tan_fovy, int32_t* radii, void* geom_buffer,
                                         size_t geom_bytes, int32_t* num_rendered_host, void* stream) {
+    return lodgs_forward_preprocess_ex(P, D, M, W, H, indices, parent_indices, ts, means3D, shs, colors_precomp, opacities, scales,
+                                       scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, radii,
+                                       geom_buffer, geom_bytes, num_rendered_host, 0u, stream);
+}
+
+extern "C" int lodgs_forward_preprocess_ex(int P, int D, int M, int W, int H, const int32_t* indices, const int32_t* parent_indices,
+                                           const float* ts, const float* means3D, const float* shs, const float* colors_precomp,
+                                           const float* opacities, const float* scales, float scale_modifier, const float* rotations,
+                                           const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                                           const float* campos, float tan_fovx, float tan_fovy, int32_t* radii, void* geom_buffer,
+                                           size_t geom_bytes, int32_t* num_rendered_host, unsigned flags, void* stream) {
     if (P < 0 || W <= 0 || H <= 0 || D < 0 || D > 3) { set_error("lodgs_forward_preprocess: bad size argument"); return LODGS_E_ARG; }
     if (P == 0) { if (num_rendered_host) *num_rendered_host = 0; return LODGS_OK; }
     if (!means3D || !opacities || !viewmatrix || !projmatrix || !campos || !radii || !geom_buffer) {
@@ -297,6 +313,7 @@ extern "C" int lodgs_forward_preprocess(int P, int D, int M, int W, int H, const
     p.focal_y = H / (2.0f * tan_fovy);
     p.focal_x = W / (2.0f * tan_fovx);
     p.radii = radii;
+    p.flags = flags;
     p.grid_x = (W + TILE_X - 1) / TILE_X; p.grid_y = (H + TILE_Y - 1) / TILE_Y;
     p.sh_vec4 = (shs && ((uintptr_t)shs & 15) == 0 && (M * 3) % 4 == 0) ? 1 : 0;
     if (rotations && ((uintptr_t)rotations & 15) != 0) { set_error("lodgs_forward_preprocess: rotations must be 16-byte aligned"); return LODGS_E_ARG; }

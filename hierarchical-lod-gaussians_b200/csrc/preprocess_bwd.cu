@@ -42,6 +42,7 @@ struct PreBwdParams {
     float* dL_dscale;
     float* dL_drot;
     int sh_vec4;
+    unsigned flags;  // LODGS_RASTER_*
     int write_all;  // no index list and no parents: every row [0,P) of dL_dmean3D / dL_dcov3D / dL_dscale / dL_drot is stored (no RMW)
 };
 
@@ -137,11 +138,14 @@ __device__ __forceinline__ void preprocess_bwd_one(const PreBwdParams& p, int t_
     c_xx += h_var;
     c_yy += h_var;
     const float det_cov_plus_h_cov = c_xx * c_yy - c_xy * c_xy;
-    const float h_convolution_scaling = sqrtf(max(0.000025f, det_cov / det_cov_plus_h_cov));
+    // without antialiasing (AR/cuda_rasterizer/backward.cu:210-229) opacity is not compensated: scaling 1, no gradient through it
+    const bool aa = !(p.flags & LODGS_RASTER_NO_ANTIALIAS);
+    const float h_convolution_scaling = aa ? sqrtf(max(0.000025f, det_cov / det_cov_plus_h_cov)) : 1.0f;
     const float dL_dopacity_v = p.dL_dopacity[idx];
     const float d_h_convolution_scaling = dL_dopacity_v * __ldg(p.opacities + idx);
     float dL_dopacity_out = dL_dopacity_v * h_convolution_scaling;
-    const float d_inside_root = (det_cov / det_cov_plus_h_cov) <= 0.000025f ? 0.f : d_h_convolution_scaling / (2 * h_convolution_scaling);
+    const float d_inside_root =
+        (!aa || (det_cov / det_cov_plus_h_cov) <= 0.000025f) ? 0.f : d_h_convolution_scaling / (2 * h_convolution_scaling);
 
     float dL_dc_xx, dL_dc_xy, dL_dc_yy;
     {
@@ -405,8 +409,9 @@ int run_preprocess_bwd(int P, int D, int M, const int32_t* indices, const int32_
                        const float* projmatrix, const float* campos, float focal_x, float focal_y, float tan_fovx, float tan_fovy,
                        const float* dL_dmean2D, const float* dL_dconic, const float* dL_dinvdepth, const float* dL_dcolor,
                        float* dL_dopacity, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
-                       cudaStream_t s) {
+                       unsigned flags, cudaStream_t s) {
     PreBwdParams p;
+    p.flags = flags;
     p.P = P; p.D = D; p.M = M; p.indices = indices; p.parent_indices = parent_indices; p.ts = ts; p.means3D = means3D; p.radii = radii;
     p.shs = shs; p.clamped = clamped; p.opacities = opacities; p.scales = scales; p.rotations = rotations; p.scale_modifier = scale_modifier;
     p.cov3Ds = cov3Ds; p.cov3D_by_global = cov3D_by_global; p.viewmatrix = viewmatrix; p.projmatrix = projmatrix; p.campos = campos;

@@ -113,7 +113,7 @@ extern "C" int lodgs_forward_render(int P, int W, int H, int R, const float* bac
 namespace lodgs {
 struct PreBwdParams;
 int launch_blend_bwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, const SplatRec* recs, int W, int H,
-                     const float* bg, const int32_t* indices, const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic,
+                     const float* bg, float bg_mult, float null_thr, const int32_t* indices, const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic,
                      float* dL_dopacity, float* dL_dcolor, float* dL_dinvdepth, cudaStream_t s);
 int run_preprocess_bwd(int P, int D, int M, const int32_t* indices, const int32_t* parent_indices, const float* ts, const float* means3D,
                        const int32_t* radii, const float* shs, const uint8_t* clamped, const float* opacities, const float* scales,
@@ -121,7 +121,7 @@ int run_preprocess_bwd(int P, int D, int M, const int32_t* indices, const int32_
                        const float* projmatrix, const float* campos, float focal_x, float focal_y, float tan_fovx, float tan_fovy,
                        const float* dL_dmean2D, const float* dL_dconic, const float* dL_dinvdepth, const float* dL_dcolor,
                        float* dL_dopacity, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
-                       cudaStream_t s);
+                       unsigned flags, cudaStream_t s);
 }  // namespace lodgs
 
 extern "C" int lodgs_backward(int P, int fullP, int D, int M, int R, int W, int H, const float* background, const int32_t* indices,
@@ -133,6 +133,21 @@ extern "C" int lodgs_backward(int P, int fullP, int D, int M, int R, int W, int 
                               const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
                               float* dL_dinvdepth, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
                               void* stream) {
+    return lodgs_backward_ex(P, fullP, D, M, R, W, H, background, indices, parent_indices, ts, kids, means3D, shs, colors_precomp, opacities,
+                             scales, scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, radii,
+                             geom_buffer, binning_buffer, image_buffer, dL_dpix, dL_dinvdepth_pix, dL_dmean2D, dL_dconic, dL_dopacity,
+                             dL_dcolor, dL_dinvdepth, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, 0u, stream);
+}
+
+extern "C" int lodgs_backward_ex(int P, int fullP, int D, int M, int R, int W, int H, const float* background, const int32_t* indices,
+                                 const int32_t* parent_indices, const float* ts, const int32_t* kids, const float* means3D,
+                                 const float* shs, const float* colors_precomp, const float* opacities, const float* scales,
+                                 float scale_modifier, const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                                 const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy, const int32_t* radii,
+                                 void* geom_buffer, void* binning_buffer, void* image_buffer, const float* dL_dpix,
+                                 const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                                 float* dL_dinvdepth, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                                 unsigned flags, void* stream) {
     (void)colors_precomp;
     if (P < 0 || fullP < 0 || W <= 0 || H <= 0 || R < 0 || D < 0 || D > 3) { set_error("lodgs_backward: bad size argument"); return LODGS_E_ARG; }
     if (P == 0) return LODGS_OK;
@@ -152,7 +167,9 @@ extern "C" int lodgs_backward(int P, int fullP, int D, int M, int R, int W, int 
         if (!binning_buffer) { set_error("lodgs_backward: null binning buffer"); return LODGS_E_ARG; }
         BinningState bin = binning_from_chunk(binning_buffer, R);
         const bool lod = ts != nullptr && kids != nullptr;
-        int rc = launch_blend_bwd(lod, dL_dinvdepth_pix != nullptr, img, bin, g.recs, W, H, background, indices, dL_dpix, dL_dinvdepth_pix,
+        int rc = launch_blend_bwd(lod, dL_dinvdepth_pix != nullptr, img, bin, g.recs, W, H, background,
+                                  (flags & LODGS_RASTER_BACKGROUND_TWICE) ? 2.0f : 1.0f,
+                                  (flags & LODGS_RASTER_CLAMPED_ALPHA_GRAD) ? __builtin_huge_valf() : 0.99f, indices, dL_dpix, dL_dinvdepth_pix,
                                   dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dinvdepth, s);
         if (rc) return rc;
     }
@@ -162,7 +179,7 @@ extern "C" int lodgs_backward(int P, int fullP, int D, int M, int R, int W, int 
     return run_preprocess_bwd(P, D, M, indices, parent_indices, ts, means3D, radii, shs, g.clamped, opacities, scales, rotations,
                               scale_modifier, cov3Ds, cov3D_precomp ? 1 : 0, viewmatrix, projmatrix, campos, focal_x, focal_y, tan_fovx,
                               tan_fovy, dL_dmean2D, dL_dconic, dL_dinvdepth, dL_dcolor, dL_dopacity, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale,
-                              dL_drot, s);
+                              dL_drot, flags, s);
 }
 
 namespace lodgs {

@@ -27,6 +27,15 @@ def _f(t):
 def rasterize_gaussians(background, indices, parent_indices, ts, kids, means3D, colors, opacity, scales, rotations,
                         scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height,
                         image_width, sh, degree, campos, prefiltered, debug, do_depth):
+    return forward_impl(background, indices, parent_indices, ts, kids, means3D, colors, opacity, scales, rotations, scale_modifier,
+                        cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                        prefiltered, debug, do_depth, 0)
+
+
+def forward_impl(background, indices, parent_indices, ts, kids, means3D, colors, opacity, scales, rotations, scale_modifier,
+                 cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                 prefiltered, debug, do_depth, _flags):
+    """Shared by this module (_flags = 0) and alt_gaussian_rasterization._C (LODGS_RASTER_* flags)."""
     if means3D.dim() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     dev = means3D.device
@@ -55,11 +64,11 @@ def rasterize_gaussians(background, indices, parent_indices, ts, kids, means3D, 
         geom = _byte_buffer(lib.lodgs_geom_bytes(P), dev)
         img = _byte_buffer(lib.lodgs_image_bytes(W, H), dev)
         n = C.c_int32(0)
-        check(lib.lodgs_forward_preprocess(P, int(degree), M, W, H, ptr(indices), ptr(parent_indices), ptr(ts), ptr(means3D),
-                                           ptr(sh), ptr(colors), ptr(opacity), ptr(scales), float(scale_modifier),
-                                           ptr(rotations), ptr(cov3D_precomp), ptr(viewmatrix), ptr(projmatrix), ptr(campos),
-                                           float(tan_fovx), float(tan_fovy), ptr(radii), geom.data_ptr(), geom.numel(),
-                                           C.addressof(n), stream))
+        check(lib.lodgs_forward_preprocess_ex(P, int(degree), M, W, H, ptr(indices), ptr(parent_indices), ptr(ts), ptr(means3D),
+                                              ptr(sh), ptr(colors), ptr(opacity), ptr(scales), float(scale_modifier),
+                                              ptr(rotations), ptr(cov3D_precomp), ptr(viewmatrix), ptr(projmatrix), ptr(campos),
+                                              float(tan_fovx), float(tan_fovy), ptr(radii), geom.data_ptr(), geom.numel(),
+                                              C.addressof(n), int(_flags), stream))
         rendered = int(n.value)
         if rendered > 0:
             binning = _byte_buffer(lib.lodgs_binning_bytes(rendered), dev)
@@ -80,6 +89,14 @@ def rasterize_gaussians_backward(background, indices, parent_indices, ts, kids, 
                                  rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
                                  dL_dout_color, dL_dout_invdepth, sh, degree, campos, geomBuffer, R, binningBuffer,
                                  imageBuffer, debug):
+    return backward_impl(background, indices, parent_indices, ts, kids, means3D, radii, colors, opacities, scales, rotations,
+                         scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_invdepth, sh,
+                         degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug, 0)
+
+
+def backward_impl(background, indices, parent_indices, ts, kids, means3D, radii, colors, opacities, scales, rotations, scale_modifier,
+                  cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_invdepth, sh, degree, campos,
+                  geomBuffer, R, binningBuffer, imageBuffer, debug, _flags):
     dev = means3D.device
     fullP = means3D.size(0)
     P = fullP if indices.numel() == 0 else indices.size(0)
@@ -125,14 +142,14 @@ def rasterize_gaussians_backward(background, indices, parent_indices, ts, kids, 
         dL_dout_color = dL_dout_color.contiguous()
         if has_depth:
             dL_dout_invdepth = dL_dout_invdepth.contiguous()
-        check(lib.lodgs_backward(P, fullP, int(degree), M, int(R), W, H, ptr(background), ptr(indices), ptr(parent_indices),
+        check(lib.lodgs_backward_ex(P, fullP, int(degree), M, int(R), W, H, ptr(background), ptr(indices), ptr(parent_indices),
                                  ptr(ts), ptr(kids), ptr(means3D), ptr(sh), ptr(colors), ptr(opacities), ptr(scales),
                                  float(scale_modifier), ptr(rotations), ptr(cov3D_precomp), ptr(viewmatrix), ptr(projmatrix),
                                  ptr(campos), float(tan_fovx), float(tan_fovy), ptr(radii), ptr(geomBuffer), ptr(binningBuffer),
                                  ptr(imageBuffer), ptr(dL_dout_color), ptr(dL_dout_invdepth) if has_depth else None,
                                  ptr(dL_dmeans2D), ptr(dL_dconic), ptr(dL_dopacity), ptr(dL_dcolors),
                                  ptr(dL_dinvdepths) if has_depth else None, ptr(dL_dmeans3D), ptr(dL_dcov3D), ptr(dL_dsh),
-                                 ptr(dL_dscales), ptr(dL_drotations), current_stream()))
+                                 ptr(dL_dscales), ptr(dL_drotations), int(_flags), current_stream()))
         if debug:
             torch.cuda.synchronize()
     return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations
@@ -145,3 +162,18 @@ def mark_visible(means3D, viewmatrix, projmatrix):
         check(lib.lodgs_mark_visible(P, ptr(means3D.contiguous()), ptr(viewmatrix.contiguous()), ptr(projmatrix.contiguous()),
                                      present.data_ptr(), current_stream()))
     return present
+
+
+def compute_relocation(opacity_old, scale_old, N, binoms, n_max):
+    """HR/rasterize_points.cu ComputeRelocationCUDA: returns (final_opacity [P], final_scale [3P]) like the reference."""
+    P = opacity_old.size(0)
+    dev = opacity_old.device
+    if dev.type != "cuda":
+        raise RuntimeError("lodgs compute_relocation needs CUDA tensors (there is no CPU path)")
+    final_opacity = torch.zeros((P,), dtype=torch.float32, device=dev)
+    final_scale = torch.zeros((3 * P,), dtype=torch.float32, device=dev)
+    if P != 0:
+        check(lib.lodgs_compute_relocation(P, ptr(opacity_old.contiguous().float()), ptr(scale_old.contiguous().float()),
+                                           ptr(N.to(dev).int().contiguous()), ptr(binoms.to(dev).contiguous().float()), int(n_max),
+                                           ptr(final_opacity), ptr(final_scale), current_stream()))
+    return final_opacity, final_scale

@@ -13,6 +13,7 @@ LIB_PATH = os.path.join(_PKG, "lib", "liblodgs.so")
 HEADER_PATH = os.path.join(os.path.dirname(_PKG), "include", "lodgs.h")
 
 OK, E_ARG, E_WORKSPACE, E_CUDA, E_IO = 0, -1, -2, -3, -4
+RASTER_SQUARE_RECT, RASTER_NO_ANTIALIAS, RASTER_BACKGROUND_TWICE, RASTER_CLAMPED_ALPHA_GRAD = 1, 2, 4, 8  # LODGS_RASTER_* of include/lodgs.h
 
 
 class LodgsError(RuntimeError):
@@ -57,10 +58,15 @@ _SIGS = {
     "lodgs_binning_bytes": (_sz, [_i]),
     "lodgs_forward_preprocess": (_i, [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _f, _f, _p,
                                       _p, _sz, _p, _p]),
+    "lodgs_forward_preprocess_ex": (_i, [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _f, _f, _p,
+                                         _p, _sz, _p, C.c_uint, _p]),
     "lodgs_forward_render": (_i, [_i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _sz, _p, _sz, _p, _p, _p, _p]),
     "lodgs_backward": (_i, [_i, _i, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _f, _f, _p,
                             _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "lodgs_backward_ex": (_i, [_i, _i, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _f, _f, _p,
+                               _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, C.c_uint, _p]),
     "lodgs_mark_visible": (_i, [_i, _p, _p, _p, _p, _p]),
+    "lodgs_compute_relocation": (_i, [_i, _p, _p, _p, _p, _i, _p, _p, _p]),
     "lodgs_geom_layout": (_i, [_i, _p]),
     "lodgs_binning_layout": (_i, [_i, _p]),
     "lodgs_image_layout": (_i, [_i, _i, _p]),

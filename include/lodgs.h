@@ -123,6 +123,31 @@ int lodgs_forward_preprocess(int P, int D, int M, int W, int H,
                              float tan_fovx, float tan_fovy, int32_t* radii,
                              void* geom_buffer, size_t geom_bytes, int32_t* num_rendered_host, void* stream);
 
+/* Same as lodgs_forward_preprocess with the conventions of the reference's second rasterizer
+ * (submodules/alt-rasterizer, AR) selected by `flags`:
+ *   LODGS_RASTER_SQUARE_RECT   tile rectangle from the square of the largest 3-sigma radius (AR/cuda_rasterizer/forward.cu:249,
+ *                              auxiliary.h:45-55) instead of the per-axis rectangle (HR forward.cu:400-404)
+ *   LODGS_RASTER_NO_ANTIALIAS  no opacity compensation (AR forward.cu:226-229 with antialiasing=false); pass the same flag to
+ *                              lodgs_backward_ex.
+ * and, for lodgs_backward_ex only, two quirks of AR's per-Gaussian backward that a drop-in has to reproduce:
+ *   LODGS_RASTER_BACKGROUND_TWICE    the background term of dL/dalpha is counted twice: AR backward.cu:576 starts the running
+ *                                    colour from minus the RENDERED pixel colour, which already contains T_final*bg
+ *                                    (forward.cu:422, rasterizer_impl.cu:495), and :617 subtracts T_final/(1-alpha)*bg.dL again
+ *   LODGS_RASTER_CLAMPED_ALPHA_GRAD  pairs whose opacity*G exceeds 0.99 keep their alpha gradient (AR backward.cu:596 has no
+ *                                    counterpart of HR backward.cu:620,687 `nullalpha`). */
+#define LODGS_RASTER_SQUARE_RECT 1u
+#define LODGS_RASTER_NO_ANTIALIAS 2u
+#define LODGS_RASTER_BACKGROUND_TWICE 4u
+#define LODGS_RASTER_CLAMPED_ALPHA_GRAD 8u
+int lodgs_forward_preprocess_ex(int P, int D, int M, int W, int H,
+                                const int32_t* indices, const int32_t* parent_indices, const float* ts,
+                                const float* means3D, const float* shs, const float* colors_precomp,
+                                const float* opacities, const float* scales, float scale_modifier,
+                                const float* rotations, const float* cov3D_precomp,
+                                const float* viewmatrix, const float* projmatrix, const float* campos,
+                                float tan_fovx, float tan_fovy, int32_t* radii,
+                                void* geom_buffer, size_t geom_bytes, int32_t* num_rendered_host, unsigned flags, void* stream);
+
 /* Stage 2: replaces duplicateWithKeys (rasterizer_impl.cu:70-115) + cub::DeviceRadixSort::SortPairs on the 64-bit
  * tile|depth keys (:358-363) + identifyTileRanges (:120-142) + renderCUDA (forward.cu:450-596). Stage 1 has already
  * ordered the Gaussians by depth bits (onesweep radix sort over P u32 keys); stage 2 emits the (tile, Gaussian) instances
@@ -156,6 +181,19 @@ int lodgs_backward(int P, int fullP, int D, int M, int R, int W, int H, const fl
                    float* dL_dinvdepth, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
                    float* dL_dscale, float* dL_drot, void* stream);
 
+/* lodgs_backward with the LODGS_RASTER_* flags the forward was run with (AR/cuda_rasterizer/rasterizer_impl.cu:537-621). */
+int lodgs_backward_ex(int P, int fullP, int D, int M, int R, int W, int H, const float* background,
+                      const int32_t* indices, const int32_t* parent_indices, const float* ts, const int32_t* kids,
+                      const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
+                      const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                      const float* viewmatrix, const float* projmatrix, const float* campos,
+                      float tan_fovx, float tan_fovy, const int32_t* radii,
+                      void* geom_buffer, void* binning_buffer, void* image_buffer,
+                      const float* dL_dpix, const float* dL_dinvdepth_pix,
+                      float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                      float* dL_dinvdepth, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
+                      float* dL_dscale, float* dL_drot, unsigned flags, void* stream);
+
 /* 1 when lodgs_backward will write every row of dL_dsh[0..P) itself (no index list, SH rows a multiple of 16 bytes, 16-byte
  * aligned pointers): the caller may then pass an uninitialised dL_dsh instead of the zero-filled one the reference
  * allocates (rasterize_points.cu:183). */
@@ -166,6 +204,11 @@ int lodgs_backward_overwrites_dsh(int M, int has_indices, int has_parents, const
  * uninitialised instead of zero-filled (rasterize_points.cu:178-187). The tensors the blend accumulates into with
  * atomics (dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dinvdepth) must always be zero-filled. */
 int lodgs_backward_overwrites_geometry(int has_indices, int has_parents);
+
+/* MCMC relocation, replaces UTILS::ComputeRelocation (HR/cuda_rasterizer/utils.cu:6-51, bound as _C.compute_relocation):
+ * opacity_new[P], scale_new[P,3] of Gaussians split into N[i] copies; binoms is the [n_max,n_max] binomial table. */
+int lodgs_compute_relocation(int P, const float* opacity_old, const float* scale_old, const int32_t* N, const float* binoms,
+                             int n_max, float* opacity_new, float* scale_new, void* stream);
 
 /* checkFrustum (HR rasterizer_impl.cu:54-66,145-157): present[i] = (view-space z > 0.2). present is u8[P]. */
 int lodgs_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,

@@ -120,6 +120,21 @@ def test_plugin_surface_matches_reference_names():
     assert list(inspect.signature(d._C.rasterize_gaussians).parameters)[:5] == ["background", "indices", "parent_indices", "ts", "kids"]
     assert len(inspect.signature(d._C.rasterize_gaussians).parameters) == 24
     assert len(inspect.signature(d._C.rasterize_gaussians_backward).parameters) == 27
+    assert list(inspect.signature(d.compute_relocation).parameters) == ["opacity_old", "scale_old", "N", "binoms", "n_max"]
+    # the second plugin (AR/alt_gaussian_rasterization/__init__.py, AR/rasterize_points.cu): 13-field settings, dc + shs, 21 / 27 args
+    import alt_gaussian_rasterization as a
+    assert a.GaussianRasterizationSettings._fields == (
+        "image_height", "image_width", "tanfovx", "tanfovy", "bg", "scale_modifier", "viewmatrix", "projmatrix", "sh_degree", "campos",
+        "prefiltered", "debug", "antialiasing")
+    assert list(inspect.signature(a.GaussianRasterizer.forward).parameters) == [
+        "self", "means3D", "means2D", "opacities", "dc", "shs", "colors_precomp", "scales", "rotations", "cov3D_precomp"]
+    assert len(inspect.signature(a._C.rasterize_gaussians).parameters) == 21
+    assert len(inspect.signature(a._C.rasterize_gaussians_backward).parameters) == 27
+    assert list(inspect.signature(a._C.adamUpdate).parameters) == ["param", "param_grad", "exp_avg", "exp_avg_sq", "visible", "lr", "b1", "b2",
+                                                                   "eps", "N", "M"]
+    assert list(inspect.signature(a.SparseGaussianAdam.step).parameters) == ["self", "visibility", "N"]
+    from lodgs.optim import Adam
+    assert list(inspect.signature(Adam.step).parameters)[:2] == ["self", "relevant"]
     r = d.GaussianRasterizer(None)
     with pytest.raises(Exception, match="excatly one of either SHs"):
         r.forward(None, None, None)
