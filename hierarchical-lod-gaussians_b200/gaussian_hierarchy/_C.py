@@ -68,6 +68,39 @@ def get_interpolation_weights(indices, size, nodes, boxes, viewpoint, viewdir, t
                                               ptr(num_kids), current_stream()))
 
 
+def expand_to_size_dynamic(nodes, positions, scales, size, viewpoint, viewdir, render_indices, parent_indices,
+                           nodes_for_render_indices):
+    """GH/torch/torch_interface.cpp:171-194 (ExpandToSizeDynamic): cut on the dynamic hierarchy format, nodes [N,6] i32
+    {depth, parent, child_count, first_child, next_sibling, max_side_length}, positions/scales [N,3]. `viewpoint` is read on
+    the device, `viewdir` on the host, as in the reference. -> K; a cut entry is the node id."""
+    if nodes.device.type != "cuda":
+        raise RuntimeError("expand_to_size_dynamic needs CUDA tensors (there is no CPU path)")
+    dev = nodes.device
+    nodes, positions, scales = nodes.contiguous(), positions.contiguous(), scales.contiguous()
+    N = nodes.size(0)
+    vp = viewpoint.to(device=dev, dtype=torch.float32).contiguous()
+    z = viewdir.detach().to("cpu", torch.float32)
+    ws = _workspace(N, dev)
+    capacity = min(render_indices.numel(), parent_indices.numel() if parent_indices.numel() else 1 << 62,
+                   nodes_for_render_indices.numel() if nodes_for_render_indices.numel() else 1 << 62)
+    count = C.c_int32(0)
+    check(lib.lodgs_expand_to_size_dynamic(ptr(nodes), ptr(positions), ptr(scales), N, float(size), ptr(vp), float(z[0]), float(z[1]),
+                                           float(z[2]), ptr(render_indices), ptr(parent_indices), ptr(nodes_for_render_indices),
+                                           int(capacity), ws.data_ptr(), ws.numel(), C.addressof(count), current_stream()))
+    return int(count.value)
+
+
+def get_interpolation_weights_dynamic(indices, size, nodes, positions, scales, viewpoint, viewdir, ts, num_kids):
+    """GH/torch/torch_interface.cpp:222-244 (GetTsIndexedDynamic); `viewpoint` is read on the host."""
+    K = indices.size(0)
+    if K == 0:
+        return
+    v = viewpoint.detach().to("cpu", torch.float32)
+    check(lib.lodgs_get_interpolation_weights_dynamic(ptr(indices.contiguous()), K, float(size), ptr(nodes.contiguous()),
+                                                      ptr(positions.contiguous()), ptr(scales.contiguous()), float(v[0]), float(v[1]),
+                                                      float(v[2]), ptr(ts), ptr(num_kids), current_stream()))
+
+
 def load_hierarchy(filename):
     """-> (pos[P,3], shs[P,16,3], alpha[P,1], scales[P,3], rot[P,4], nodes[N,7] i32, boxes[N,2,4]) CPU tensors."""
     P, N = C.c_int32(0), C.c_int32(0)

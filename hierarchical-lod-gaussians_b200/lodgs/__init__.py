@@ -50,6 +50,8 @@ _SIGS = {
     "lodgs_expand_to_size": (_i, [_p, _p, _i, _f, _p, _p, _p, _p, _i, _p, _sz, _i, _p, _p]),
     "lodgs_cut_prepare": (_i, [_p, _p, _i, _p, _sz, _p, _p]),
     "lodgs_get_interpolation_weights": (_i, [_p, _i, _f, _p, _p, _f, _f, _f, _p, _p, _p]),
+    "lodgs_expand_to_size_dynamic": (_i, [_p, _p, _p, _i, _f, _p, _f, _f, _f, _p, _p, _p, _i, _p, _sz, _p, _p]),
+    "lodgs_get_interpolation_weights_dynamic": (_i, [_p, _i, _f, _p, _p, _p, _f, _f, _f, _p, _p, _p]),
     "lodgs_hier_probe": (_i, [C.c_char_p, _p, _p]),
     "lodgs_hier_load": (_i, [C.c_char_p, _p, _p, _p, _p, _p, _p, _p]),
     "lodgs_hier_write": (_i, [C.c_char_p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _i]),

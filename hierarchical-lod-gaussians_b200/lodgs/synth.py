@@ -183,3 +183,38 @@ def build_hierarchy_torch(k, device, seed=0, extent=(200.0, 200.0, 10.0), radius
                          torch.where(leaf, torch.full_like(ids, -1), 2 * ids + 1), torch.where(leaf, torch.zeros_like(ids),
                                                                                               torch.full_like(ids, 2))], 1).int()
     return nodes.contiguous(), boxes.contiguous()
+
+
+def to_dynamic_hierarchy(nodes, boxes, gauss_pos, gauss_rad, seed=0, skybox=0):
+    """Re-express a static hierarchy (build_hierarchy) in the DYNAMIC format of this fork (GH/types.h:60-79 `HierarchyNode`):
+    nodes[N,6] i32 {depth, parent, child_count, first_child, next_sibling, max_side_length}, positions[N,3], scales[N,3]
+    (one Gaussian per node: position = the node's Gaussian, anisotropic scales around its radius). `skybox` extra nodes with
+    depth -1 are appended (they are never selected by the cut, GH/runtime_switching.cu:556-560)."""
+    rng = np.random.default_rng(seed)
+    N = nodes.shape[0]
+    dyn = np.zeros((N + skybox, 6), np.int32)
+    dyn[:N, 0] = nodes[:, 0]
+    dyn[:N, 1] = nodes[:, 1]
+    dyn[:N, 2] = nodes[:, 6]
+    dyn[:N, 3] = np.where(nodes[:, 6] > 0, nodes[:, 5], -1)
+    nxt = np.full(N, -1, np.int32)
+    for i in range(N):
+        c0, cc = nodes[i, 5], nodes[i, 6]
+        for k in range(cc - 1):
+            nxt[c0 + k] = c0 + k + 1
+    dyn[:N, 4] = nxt
+    side = (boxes[:, 1, :3] - boxes[:, 0, :3]).max(1)
+    dyn[:N, 5] = np.minimum(side, 2 ** 30).astype(np.int32)
+    pos = np.zeros((N + skybox, 3), np.float32)
+    sca = np.zeros((N + skybox, 3), np.float32)
+    gid = nodes[:, 2]
+    pos[:N] = gauss_pos[gid]
+    sca[:N] = gauss_rad[gid, None] * rng.uniform(0.4, 1.0, (N, 3)).astype(np.float32)
+    if skybox:
+        dyn[N:, 0] = -1
+        dyn[N:, 1] = -1
+        dyn[N:, 3] = -1
+        dyn[N:, 4] = -1
+        pos[N:] = rng.uniform(-500, 500, (skybox, 3)).astype(np.float32)
+        sca[N:] = 50.0
+    return dyn, pos, sca

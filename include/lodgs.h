@@ -75,6 +75,23 @@ int lodgs_get_interpolation_weights(const int32_t* node_indices, int K, float ta
                                     const int32_t* nodes, const float* boxes, float vx, float vy, float vz,
                                     float* ts, int32_t* num_siblings, void* stream);
 
+/* Cut and weights on the DYNAMIC hierarchy format (the one this fork's creator writes and create_from_hier loads):
+ * replaces Switching::expandToSizeDynamic (GH/runtime_switching.cu:748-782, kernels :533-582, :95-108; bound as
+ * expand_to_size_dynamic, GH/torch/torch_interface.cpp:171-194) and Switching::getTsIndexedDynamic (:637-684; bound as
+ * get_interpolation_weights_dynamic, torch_interface.cpp:222-244). nodes = HierarchyNode[N] (6 x i32: depth, parent,
+ * child_count, first_child, next_sibling, max_side_length; GH/types.h:60-79), positions f32[N,3], scales f32[N,3].
+ * A node is on the cut when it lies inside the view cone (cos between viewpoint-position and zdir < -0.5), has depth >= 0 and is
+ * either a leaf with max(scale)/distance >= target_size or the first node below target_size on its path. Entries are node ids
+ * in ascending order; parent_indices[k] is written only for entries with a parent (the reference leaves the caller's value
+ * for roots). Workspace and count conventions as lodgs_expand_to_size. */
+int lodgs_expand_to_size_dynamic(const int32_t* nodes, const float* positions, const float* scales, int N,
+                                 float target_size, const float* viewpoint_dev, float zdir_x, float zdir_y, float zdir_z,
+                                 int32_t* render_indices, int32_t* parent_indices, int32_t* nodes_for_render_indices,
+                                 int capacity, void* ws, size_t ws_bytes, int32_t* count_host, void* stream);
+int lodgs_get_interpolation_weights_dynamic(const int32_t* node_indices, int K, float target_size, const int32_t* nodes,
+                                            const float* positions, const float* scales, float vx, float vy, float vz,
+                                            float* ts, int32_t* num_siblings, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Hierarchy file I/O (host only). Replaces HierarchyLoader::load (GH/hierarchy_loader.cpp:26-128)
  * behind gaussian_hierarchy._C.load_hierarchy (torch_interface.cpp:9-40), and HierarchyWriter::write

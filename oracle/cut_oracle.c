@@ -81,3 +81,74 @@ void orc_get_interpolation_weights(const int32_t* indices, int K, float tau, con
         kids[idx] = (n[1] == -1) ? 1 : nodes[(long)n[1] * 7 + 6];
     }
 }
+
+/* ---- dynamic hierarchy format (HierarchyNode = 6 x i32: depth parent child_count first_child next_sibling max_side_length,
+ * GH/types.h:60-79): markNodesForSizeDynamic + InclusiveSum + putRenderIndicesDynamic (GH/runtime_switching.cu:533-582, :95-108),
+ * is_in_frustum (:165-186), computeSizeGPUDynamic / pointgaussiandistCUDA (:146-163, :222-232), computeTsIndexedDynamic (:637-684).
+ * Distance with the association of the reference SASS, which differs between its two kernels: the mark kernel compiles to
+ * fma(dz,dz, fma(dy,dy, dx*dx)), the weights kernel to fma(dz,dz, fma(dx,dx, dy*dy)); dot product x*zx -> fma(y,zy,.) -> fma(z,zz,.). */
+static float dyn_norm_assoc(const float* pos, const float* v, float* d, int y_first) {
+    d[0] = v[0] - pos[0];
+    d[1] = v[1] - pos[1];
+    d[2] = v[2] - pos[2];
+    if (y_first) return sqrtf(fmaf(d[2], d[2], fmaf(d[0], d[0], d[1] * d[1])));
+    return sqrtf(fmaf(d[2], d[2], fmaf(d[1], d[1], d[0] * d[0])));
+}
+static float dyn_norm(const float* pos, const float* v, float* d) { return dyn_norm_assoc(pos, v, d, 0); }
+static float dyn_size(const float* scale, float norm) {
+    if (norm < 0.0f) return 0.0f;
+    return fmaxf(scale[0], fmaxf(scale[1], scale[2])) / norm;
+}
+
+int orc_expand_to_size_dynamic(const int32_t* nodes, const float* positions, const float* scales, int N, float tau, const float* viewpoint,
+                               const float* zdir, int32_t* render_indices, int32_t* parent_indices, int32_t* node_ids) {
+    int off = 0;
+    for (int i = 0; i < N; i++) {
+        const int32_t* n = nodes + (long)i * 6;
+        float d[3];
+        float norm = dyn_norm(positions + (long)i * 3, viewpoint, d);
+        float c = fmaf(d[2] / norm, zdir[2], fmaf(d[1] / norm, zdir[1], (d[0] / norm) * zdir[0]));
+        if (!(c < -0.5f)) continue;
+        if (n[0] < 0) continue;
+        float size = dyn_size(scales + (long)i * 3, norm);
+        int count = 0;
+        if (size >= tau && n[2] == 0) {
+            count = 1;
+        } else if (n[1] >= 0) {
+            float pd[3];
+            float pnorm = dyn_norm(positions + (long)n[1] * 3, viewpoint, pd);
+            float psize = dyn_size(scales + (long)n[1] * 3, pnorm);
+            if (psize >= tau && size < tau) count = 1;
+        }
+        if (count) {
+            render_indices[off] = i;
+            if (node_ids) node_ids[off] = i;
+            if (parent_indices && n[1] != -1) parent_indices[off] = n[1];
+            off++;
+        }
+    }
+    return off;
+}
+
+void orc_get_interpolation_weights_dynamic(const int32_t* indices, int K, float tau, const int32_t* nodes, const float* positions,
+                                           const float* scales, const float* viewpoint, float* ts, int32_t* kids) {
+    for (int idx = 0; idx < K; idx++) {
+        int node_id = indices[idx];
+        const int32_t* n = nodes + (long)node_id * 6;
+        float t = 1.0f, d[3];
+        if (n[1] >= 0) {
+            float parentsize = dyn_size(scales + (long)n[1] * 3, dyn_norm_assoc(positions + (long)n[1] * 3, viewpoint, d, 1));
+            if (!(parentsize > 2.0f * tau)) {
+                float size = dyn_size(scales + (long)node_id * 3, dyn_norm_assoc(positions + (long)node_id * 3, viewpoint, d, 1));
+                float start = fmaxf(0.5f * parentsize, size);
+                float diff = parentsize - start;
+                if (!(diff <= 0)) {
+                    float tdiff = fmaxf(0.0f, tau - start);
+                    t = fmaxf(1.0f - (tdiff / diff), 0.0f);
+                }
+            }
+        }
+        ts[idx] = t;
+        kids[idx] = n[1] < 0 ? 1 : nodes[(long)n[1] * 6 + 2];
+    }
+}

@@ -39,6 +39,9 @@ def lib():
         _lib.orc_expand_to_size.restype = C.c_int
         _lib.orc_expand_to_size.argtypes = [_ip, _fp, C.c_int, C.c_float, _fp, _ip, _ip, _ip]
         _lib.orc_get_interpolation_weights.argtypes = [_ip, C.c_int, C.c_float, _ip, _fp, _fp, _fp, _ip]
+        _lib.orc_expand_to_size_dynamic.restype = C.c_int
+        _lib.orc_expand_to_size_dynamic.argtypes = [_ip, _fp, _fp, C.c_int, C.c_float, _fp, _fp, _ip, _ip, _ip]
+        _lib.orc_get_interpolation_weights_dynamic.argtypes = [_ip, C.c_int, C.c_float, _ip, _fp, _fp, _fp, _fp, _ip]
         _lib.orc_forward.restype = C.c_int
         _lib.orc_forward.argtypes = [C.POINTER(Scene), C.POINTER(State)]
         _lib.orc_backward.argtypes = [C.POINTER(Scene), C.POINTER(State)] + [_fp] * 12
@@ -74,6 +77,26 @@ def get_interpolation_weights(node_ids, tau, nodes, boxes, viewpoint):
     K = idx.shape[0]
     ts, kids = np.zeros(K, np.float32), np.zeros(K, np.int32)
     lib().orc_get_interpolation_weights(_i(idx), K, float(tau), _i(nodes), _f(boxes), _f(vp), _f(ts), _i(kids))
+    return ts, kids
+
+
+def expand_to_size_dynamic(nodes, positions, scales, tau, viewpoint, zdir, parent_fill=-7):
+    """-> (render_indices[K], parent_indices[K] (entries of roots keep parent_fill, as the reference leaves them), node_ids[K])"""
+    nodes, pos, sca = _c(nodes, np.int32), _c(positions, np.float32), _c(scales, np.float32)
+    vp, zd = _c(viewpoint, np.float32), _c(zdir, np.float32)
+    N = nodes.shape[0]
+    ri, ni = np.zeros(N, np.int32), np.zeros(N, np.int32)
+    pi = np.full(N, parent_fill, np.int32)
+    K = lib().orc_expand_to_size_dynamic(_i(nodes), _f(pos), _f(sca), N, float(tau), _f(vp), _f(zd), _i(ri), _i(pi), _i(ni))
+    return ri[:K].copy(), pi[:K].copy(), ni[:K].copy()
+
+
+def get_interpolation_weights_dynamic(node_ids, tau, nodes, positions, scales, viewpoint):
+    idx, nodes, pos, sca, vp = (_c(node_ids, np.int32), _c(nodes, np.int32), _c(positions, np.float32), _c(scales, np.float32),
+                                _c(viewpoint, np.float32))
+    K = idx.shape[0]
+    ts, kids = np.zeros(K, np.float32), np.zeros(K, np.int32)
+    lib().orc_get_interpolation_weights_dynamic(_i(idx), K, float(tau), _i(nodes), _f(pos), _f(sca), _f(vp), _f(ts), _i(kids))
     return ts, kids
 
 

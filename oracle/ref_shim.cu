@@ -92,6 +92,17 @@ REF_API void ref_get_ts_indexed(int K, int* indices, float target_size, int* nod
     Switching::getTsIndexed(K, indices, target_size, nodes, boxes, vx, vy, vz, zx, zy, zz, ts, kids, stream);
 }
 
+REF_API int ref_expand_to_size_dynamic(int N, float target_size, int* nodes, float* positions, float* scales, float* viewpoint_dev, float zx,
+                                       float zy, float zz, int* render_indices, int* parent_indices, int* nodes_for_render_indices) {
+    return Switching::expandToSizeDynamic(N, target_size, nodes, positions, scales, viewpoint_dev, zx, zy, zz, render_indices, nullptr,
+                                          parent_indices, nodes_for_render_indices);
+}
+
+REF_API void ref_get_ts_indexed_dynamic(int K, int* indices, float target_size, int* nodes, float* positions, float* scales, float vx,
+                                        float vy, float vz, float zx, float zy, float zz, float* ts, int* kids, void* stream) {
+    Switching::getTsIndexedDynamic(K, indices, target_size, nodes, positions, scales, vx, vy, vz, zx, zy, zz, ts, kids, stream);
+}
+
 REF_API int ref_copy_d2d(void* dst, const void* src, size_t nbytes) {
     cudaError_t e = cudaMemcpy(dst, src, nbytes, cudaMemcpyDeviceToDevice);
     if (e == cudaSuccess) e = cudaDeviceSynchronize();

@@ -35,6 +35,10 @@ def lib():
         _lib.ref_expand_to_size.argtypes = [_i, _f, _p, _p, _p, _f, _f, _f, _p, _p, _p]
         _lib.ref_get_ts_indexed.restype = None
         _lib.ref_get_ts_indexed.argtypes = [_i, _p, _f, _p, _p, _f, _f, _f, _f, _f, _f, _p, _p, _p]
+        _lib.ref_expand_to_size_dynamic.restype = _i
+        _lib.ref_expand_to_size_dynamic.argtypes = [_i, _f, _p, _p, _p, _p, _f, _f, _f, _p, _p, _p]
+        _lib.ref_get_ts_indexed_dynamic.restype = None
+        _lib.ref_get_ts_indexed_dynamic.argtypes = [_i, _p, _f, _p, _p, _p, _f, _f, _f, _f, _f, _f, _p, _p, _p]
     return _lib
 
 

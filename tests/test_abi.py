@@ -133,6 +133,11 @@ def test_plugin_surface_matches_reference_names():
     assert list(inspect.signature(a._C.adamUpdate).parameters) == ["param", "param_grad", "exp_avg", "exp_avg_sq", "visible", "lr", "b1", "b2",
                                                                    "eps", "N", "M"]
     assert list(inspect.signature(a.SparseGaussianAdam.step).parameters) == ["self", "visibility", "N"]
+    import gaussian_hierarchy._C as ghc
+    assert list(inspect.signature(ghc.expand_to_size_dynamic).parameters) == [
+        "nodes", "positions", "scales", "size", "viewpoint", "viewdir", "render_indices", "parent_indices", "nodes_for_render_indices"]
+    assert list(inspect.signature(ghc.get_interpolation_weights_dynamic).parameters) == [
+        "indices", "size", "nodes", "positions", "scales", "viewpoint", "viewdir", "ts", "num_kids"]
     from lodgs.optim import Adam
     assert list(inspect.signature(Adam.step).parameters)[:2] == ["self", "relevant"]
     r = d.GaussianRasterizer(None)
