@@ -39,3 +39,19 @@ def make_cut_case(L=2000, seed=0):
     nodes, boxes, gpos, grad = synth.build_hierarchy(pts, rad)
     views = [np.array(v, np.float32) for v in ([0.0, 0.0, -30.0], [10.0, -5.0, 1.0], [80.0, 80.0, 20.0], [0.5, 0.25, 0.1])]
     return nodes, boxes, views
+
+
+DYN_VIEWS = [([0.0, 0.0, -60.0], [0.0, 0.0, 1.0]), ([30.0, -20.0, 25.0], [-0.6, 0.4, -0.69]), ([5.0, 5.0, 1.0], [1.0, 0.0, 0.0]),
+             ([-80.0, 10.0, -5.0], [0.99, -0.1, 0.05])]
+DYN_TAUS = (0.0, 0.002, 0.01, 0.05, 0.5)
+
+
+def make_dynamic_cut_case(L=2000, seed=21, skybox=4):
+    """Dynamic-format hierarchy (nodes[N,6], positions, scales) + (viewpoint, zdir) pairs for the dynamic cut tests."""
+    rng = np.random.default_rng(seed)
+    pts = (rng.uniform(-1, 1, (L, 3)) * np.array([40.0, 40.0, 4.0])).astype(np.float32)
+    rad = np.exp(rng.normal(np.log(0.05), 0.5, L)).astype(np.float32)
+    nodes, boxes, gpos, grad = synth.build_hierarchy(pts, rad)
+    dyn, pos, sca = synth.to_dynamic_hierarchy(nodes, boxes, gpos, grad, seed=seed, skybox=skybox)
+    views = [(np.array(v, np.float32), (np.array(z, np.float32) / np.linalg.norm(z)).astype(np.float32)) for v, z in DYN_VIEWS]
+    return dyn, pos, sca, views

@@ -55,3 +55,26 @@ for vi, v in enumerate(views):
         res[key + "_ts"], res[key + "_kids"] = ts[:K].cpu().numpy(), kids[:K].cpu().numpy()
         print(key, "K", K)
 np.savez_compressed(os.path.join(OUT, "cut.npz"), **res)
+
+# ---- dynamic-format cut (expandToSizeDynamic / getTsIndexedDynamic)
+dyn, pos, sca, dviews = cases.make_dynamic_cut_case()
+d_t, p_t, s_t = torch.from_numpy(dyn).cuda(), torch.from_numpy(pos).cuda(), torch.from_numpy(sca).cuda()
+N = dyn.shape[0]
+res = {}
+for vi, (v, z) in enumerate(dviews):
+    for ti, tau in enumerate(cases.DYN_TAUS):
+        ri, pi, ni = (torch.full((N,), -7, dtype=torch.int32, device="cuda") for _ in range(3))
+        vp = torch.from_numpy(v).cuda()
+        torch.cuda.synchronize()
+        K = L.ref_expand_to_size_dynamic(N, float(tau), d_t.data_ptr(), p_t.data_ptr(), s_t.data_ptr(), vp.data_ptr(), float(z[0]), float(z[1]),
+                                         float(z[2]), ri.data_ptr(), pi.data_ptr(), ni.data_ptr())
+        ts, kids = torch.zeros(max(K, 1), device="cuda"), torch.zeros(max(K, 1), dtype=torch.int32, device="cuda")
+        if K:
+            L.ref_get_ts_indexed_dynamic(K, ni.data_ptr(), float(tau), d_t.data_ptr(), p_t.data_ptr(), s_t.data_ptr(), float(v[0]), float(v[1]),
+                                         float(v[2]), float(z[0]), float(z[1]), float(z[2]), ts.data_ptr(), kids.data_ptr(), None)
+        torch.cuda.synchronize()
+        key = "v%d_t%d" % (vi, ti)
+        res[key + "_ri"], res[key + "_pi"], res[key + "_ni"] = ri[:K].cpu().numpy(), pi[:K].cpu().numpy(), ni[:K].cpu().numpy()
+        res[key + "_ts"], res[key + "_kids"] = ts[:K].cpu().numpy(), kids[:K].cpu().numpy()
+        print("dyn", key, "K", K)
+np.savez_compressed(os.path.join(OUT, "cut_dynamic.npz"), **res)

@@ -37,6 +37,25 @@ def test_cut_oracle_matches_reference_bit_exact():
     assert n > 10000
 
 
+def test_dynamic_cut_oracle_matches_reference_bit_exact():
+    """expand_to_size_dynamic / get_interpolation_weights_dynamic restatement vs the reference kernels' outputs (cut_dynamic.npz)."""
+    g = np.load(os.path.join(GOLD, "cut_dynamic.npz"))
+    dyn, pos, sca, views = cases.make_dynamic_cut_case()
+    n = 0
+    for vi, (v, z) in enumerate(views):
+        for ti, tau in enumerate(cases.DYN_TAUS):
+            ri, pi, ni = orc.expand_to_size_dynamic(dyn, pos, sca, np.float32(tau), v, z, parent_fill=-7)
+            key = "v%d_t%d" % (vi, ti)
+            assert np.array_equal(ri, g[key + "_ri"]), key
+            assert np.array_equal(pi, g[key + "_pi"]), key
+            assert np.array_equal(ni, g[key + "_ni"]), key
+            ts, kids = orc.get_interpolation_weights_dynamic(ni, np.float32(tau), dyn, pos, sca, v)
+            assert np.array_equal(kids, g[key + "_kids"]), key
+            assert np.array_equal(ts.view(np.uint32), g[key + "_ts"].view(np.uint32)), key
+            n += len(ri)
+    assert n > 3000
+
+
 @pytest.mark.parametrize("name", list(cases.CASES))
 def test_raster_oracle_matches_reference(name):
     g = np.load(os.path.join(GOLD, "raster_%s.npz" % name))
