@@ -100,6 +100,34 @@ class OursArm:
     def step_resident(self):
         self.fwd_bwd(self.d, self.target)
 
+    # ---- training iteration (first half of "train iters/s"): fwd + bwd + sparse Adam on the visible Gaussians, the
+    # update rule of scene/OurAdam.py Adam.step(relevant) with relevant = (radii > 0).nonzero() (train_single.py:171-176)
+    GRAD_OF = {"means3D": 3, "shs": 5, "opacities": 2, "scales": 6, "rotations": 7}   # index into the backward's 8-tuple
+    # the training learning rates x 1e-3: the cost of an Adam step does not depend on them, and the scene (hence the work of
+    # the timed forward/backward) stays what it is over the timed iterations
+    LR = {"means3D": 1.6e-7, "shs": 2.5e-6, "opacities": 5e-5, "scales": 5e-6, "rotations": 1e-6}
+
+    def train_init(self):
+        self.tp = {k: self.d[k].clone() for k in PARAM_KEYS}
+        self.tm = {k: torch.zeros_like(v) for k, v in self.tp.items()}
+        self.tv = {k: torch.zeros_like(v) for k, v in self.tp.items()}
+        self.tstep = 0
+
+    def adam(self, relevant, grads):
+        import lodgs
+        self.tstep += 1
+        for k in PARAM_KEYS:
+            p, g = self.tp[k], grads[self.GRAD_OF[k]].contiguous()
+            rows = p.size(0)
+            lodgs.check(lodgs.lib.lodgs_adam_step(p.data_ptr(), g.data_ptr(), self.tm[k].data_ptr(), self.tv[k].data_ptr(), relevant.data_ptr(),
+                                                  relevant.numel(), None, rows, p.numel() // rows, self.LR[k], 0.9, 0.999, 1e-15, self.tstep,
+                                                  1, lodgs.current_stream()))
+
+    def step_train(self):
+        color, grads = self.fwd_bwd(self.tp, self.target)
+        relevant = (self.last[2] > 0).nonzero().reshape(-1)
+        self.adam(relevant, grads)
+
     def step_e2e(self):
         """One end-to-end step: inputs leave pinned host memory, results land in pinned host memory. Three streams
         (H2D, compute, D2H) and two buffer slots let step i's copies overlap its neighbours' kernels; every step still
@@ -198,6 +226,9 @@ class RefArm(OursArm):
         self.last = (R, color, radii, None, grads)
         return color, grads
 
+    def adam(self, relevant, grads):
+        _eager_index_adam(self, relevant, grads)
+
 
 # ------------------------------------------------------------------------------------------------ roofline
 def _peaks():
@@ -239,6 +270,27 @@ def _work_model(arm, n_gauss):
         "preprocess_bwd_kernel": ("hbm", p_vis * (115.0 + 68.0 + 24.0 * M)),
     }
     return work, {"num_rendered": R, "p_visible": p_vis, "n_test": n_test, "n_alpha": n_alpha, "n_blend": n_blend}
+
+
+def _eager_index_adam(arm, relevant, grads):
+    """The reference's optimizer step as it runs there: scene/OurAdam.py:251-354 `_single_tensor_adam` — gather the listed rows of
+    param / grad / moments, eager elementwise Adam with host-side bias correction, scatter the rows back."""
+    import math
+    arm.tstep += 1
+    b1, b2, eps = 0.9, 0.999, 1e-15
+    for k in PARAM_KEYS:
+        grad = grads[arm.GRAD_OF[k]][relevant]
+        exp_avg = arm.tm[k][relevant]
+        exp_avg_sq = arm.tv[k][relevant]
+        param = arm.tp[k][relevant]
+        exp_avg.mul_(b1).add_(grad, alpha=1 - b1)
+        exp_avg_sq.mul_(b2).addcmul_(grad, grad.conj(), value=1 - b2)
+        step_size = arm.LR[k] / (1 - b1 ** arm.tstep)
+        denom = (exp_avg_sq.sqrt() / math.sqrt(1 - b2 ** arm.tstep)).add_(eps)
+        param.addcdiv_(exp_avg, denom, value=-step_size)
+        arm.tm[k][relevant] = exp_avg
+        arm.tv[k][relevant] = exp_avg_sq
+        arm.tp[k][relevant] = param
 
 
 def _roofline(prof, steps, work, sm_count):
@@ -293,6 +345,15 @@ def _line(args, world, value, ms_per_step, clocks, extra):
     return line
 
 
+def _train_section(arm, args, world, dev, what):
+    """fwd + bwd + sparse Adam per iteration, one view per iteration (configs/vanilla.json training step without the image loss
+    terms outside the plugin); single GPU."""
+    arm.train_init()
+    ms = _timed(arm.step_train, args.steps, 3, world, dev)
+    return {"iters_per_s": round(args.steps / (ms * 1e-3), 2), "ms_per_iter": round(ms / args.steps, 4), "optimizer": what,
+            "updated_floats_per_gaussian": 59}
+
+
 def run_ours(args, rank, world, dev):
     import lodgs
     sc, cam, target = make_inputs(rank, args.P)
@@ -323,6 +384,8 @@ def run_ours(args, rank, world, dev):
                                      "ms_per_step": round(ms_e2e / args.steps, 4)},
              "gpu_launches": int(launches), "roofline": roof, "per_kernel": per_kernel, "workload_counters": counters,
              "cpu_baseline": _cpu_baseline(args.no_cpu_baseline)}
+    if world == 1:
+        extra["train"] = _train_section(arm, args, world, dev, "lodgs_adam_step on the rows with radii > 0 (one fused kernel per tensor)")
     if not getattr(args, "no_cut", False) and world == 1:
         extra["lod_cut"] = _lod_cut(dev, not args.no_cpu_baseline)
     return _line(args, world, value, ms / args.steps, clocks, extra)
@@ -363,4 +426,7 @@ def run_reference(args, rank, world, dev):
              "cpu_baseline": {"value": round(e2e, 2), "unit": "Mpix/s", "cores": 0, "kind": "reference",
                               "sample": "full workload; the reference has no CPU implementation of this path, so this arm runs its "
                                         "unmodified CUDA kernels (oracle/_ref, sm_100a rebuild) on the same B200"}}
+    if world == 1:
+        extra["train"] = _train_section(arm, args, world, dev, "eager torch restatement of scene/OurAdam.py _single_tensor_adam "
+                                                               "(row gather, elementwise ops, row scatter) on the rows with radii > 0")
     return _line(args, world, value, ms / args.steps, clocks, extra)
