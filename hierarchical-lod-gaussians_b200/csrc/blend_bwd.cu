@@ -29,12 +29,6 @@ __device__ __forceinline__ float rcp_approx(float x) {
     return r;
 }
 
-// Per-pixel replay state of the back-to-front pass.
-struct BwdPix {
-    float px, py, T, T_final, last_alpha, lc0, lc1, lc2, ar0, ar1, ar2, last_invd, ar_invd, g0, g1, g2, gd, bg_dot;
-    unsigned last_contributor;
-};
-
 // Sum v[0..9] over the warp. On return lanes with even lane id and a valid slot hold the total of value
 // `slot` (returned, -1 otherwise) in the return value `out`.
 __device__ __forceinline__ float warp_reduce10(const float (&v)[NV], unsigned lane, int& slot) {
@@ -72,64 +66,129 @@ __device__ __forceinline__ float warp_reduce10(const float (&v)[NV], unsigned la
     return t[0];
 }
 
-// One (pixel, splat) pair of the replay (backward.cu:600-716); adds this pixel's ten partial gradients to v.
+// ---- packed FP32 (sm_100 FFMA2 / FMUL2 / FADD2): the thread's two pixels ride in the halves of one 64-bit register pair, so
+// the arithmetic of a (splat, pixel pair) costs one issue slot instead of two (the kernel is issue-bound, not FP-pipe-bound).
+// Splat constants enter as broadcast operands (mov.b64 {x,x} folds into the instruction). ptxas contracts mul+add pairs of
+// packed operations even with .rn; harmless here (gradients are held to 1e-3, not bit-exact), which is why the FORWARD
+// kernel, whose rounding is pinned, keeps scalar instructions.
+typedef unsigned long long f2;
+__device__ __forceinline__ f2 pk(float lo, float hi) {
+    f2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ f2 bc(float x) { return pk(x, x); }
+__device__ __forceinline__ float lo(f2 v) {
+    float a, b;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+    return a;
+}
+__device__ __forceinline__ float hi(f2 v) {
+    float a, b;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+    return b;
+}
+__device__ __forceinline__ float hsum(f2 v) { return lo(v) + hi(v); }
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) {
+    f2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) {
+    f2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f2 add2(f2 a, f2 b) {
+    f2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+
+// Replay state of the thread's two pixels (lo = upper pixel, hi = the one below it).
+struct BwdPix2 {
+    f2 npy, T, T_final, last_alpha, ar0, ar1, ar2, ar_invd, g0, g1, g2, gd, nbg_dot;
+    float px, lc0, lc1, lc2, last_invd;  // the colour / inverse depth of the previously processed splat is the same for both pixels
+    unsigned last0, last1;
+};
+
+// One splat against both pixels (backward.cu:600-716). A pixel the splat does not contribute to (behind its last contributor,
+// power > 0, below the cut-off or alpha < 1/255) takes part as a ZERO-ALPHA splat: T / (1 - 0) = T, the running colour
+// recurrence ar' = last_alpha*lc + (1-last_alpha)*ar passes through it unchanged (the next splat sees last_alpha = 0), and
+// its k is forced to 0 — so no per-pixel branches and no per-pixel copies of the previous colour are needed.
 template <bool LOD, bool DEPTH>
-__device__ __forceinline__ bool bwd_pair(BwdPix& p, const float dx, const float dxa, const float dxb, const float4 q0, const float4 q1,
-                                         const float4 q2, const float null_thr, float (&v)[NV]) {
-    const float dy = __fsub_rn(q0.y, p.py);
-    const float quad = __fmaf_rn(dx, dxa, __fmul_rn(dy, __fmul_rn(dy, q1.x)));
-    const float power = __fsub_rn(__fmul_rn(quad, -0.5f), __fmul_rn(dy, dxb));
-    if (power > 0.0f) return false;
-    if (!LOD && power < q2.z) return false;  // certainly below the 1/255 cut (see preprocess_one)
-    // ex2.approx instead of the forward's full-range expf (8 fewer instructions per pair): alpha moves by ~1e-7 relative, so a
-    // pair can change sides of the 1/255 cut only when it sits within that distance of it — its contribution is then 0.4 % of
-    // one pixel, far inside the 1e-3 relative-L2 budget of the gradients
-    const float G = __expf(power);
-    const float test_alpha = __fmul_rn(q1.y, G);
-    const bool nullalpha = test_alpha > null_thr;  // 0.99 (backward.cu:620,687); +inf with the alt-rasterizer's convention
-    const float my_alpha = fminf(0.99f, test_alpha);
-    float alpha = my_alpha, t = 1.f, frac = 1.f;
+__device__ __forceinline__ bool bwd_pair2(BwdPix2& p, const unsigned pos, const float4 q0, const float4 q1, const float4 q2,
+                                          const float null_thr, float (&v)[NV]) {
+    const float dx = q0.x - p.px;
+    const f2 dy = add2(bc(q0.y), p.npy);
+    const f2 quad = fma2(dy, mul2(dy, bc(q1.x)), bc(dx * (dx * q0.z)));
+    const f2 power = fma2(dy, bc(-(dx * q0.w)), mul2(quad, bc(-0.5f)));
+    const float pw0 = lo(power), pw1 = hi(power);
+    bool ok0 = pos < p.last0 && !(pw0 > 0.0f), ok1 = pos < p.last1 && !(pw1 > 0.0f);
+    if (!LOD) {  // certainly below the 1/255 cut (cut-off stored by the preprocess kernel)
+        ok0 = ok0 && !(pw0 < q2.z);
+        ok1 = ok1 && !(pw1 < q2.z);
+    }
+    if (!ok0 && !ok1) return false;
+    // ex2.approx instead of the forward's full-range expf: alpha moves by ~1e-7 relative, far inside the gradient budget
+    const float G0 = __expf(pw0), G1 = __expf(pw1);
+    const f2 G = pk(G0, G1);
+    const f2 ta = mul2(bc(q1.y), G);
+    const float ta0 = lo(ta), ta1 = hi(ta);
+    const float ma0 = fminf(0.99f, ta0), ma1 = fminf(0.99f, ta1);
+    float a0 = ma0, a1 = ma1, t = 1.f, frac = 1.f;
     if (LOD) {
         t = q2.z;
         frac = q2.w;
-        const float kidsqrt_alpha = __fsub_rn(1.0f, __powf(__fsub_rn(1.0f, my_alpha), frac));
-        alpha = __fmaf_rn(my_alpha, t, __fmul_rn(__fsub_rn(1.0f, t), kidsqrt_alpha));
+        a0 = fmaf(ma0, t, (1.0f - t) * (1.0f - __powf(1.0f - ma0, frac)));
+        a1 = fmaf(ma1, t, (1.0f - t) * (1.0f - __powf(1.0f - ma1, frac)));
     }
-    if (alpha < 1.0f / 255.0f) return false;
-    const float rcp1ma = rcp_approx(1.f - alpha);  // 1-alpha in [0.01,1]: one MUFU instead of two IEEE divides per pair
-    p.T *= rcp1ma;
-    const float weight = alpha * p.T;
-    const float oml = 1.f - p.last_alpha;
-    p.ar0 = p.last_alpha * p.lc0 + oml * p.ar0;
-    p.ar1 = p.last_alpha * p.lc1 + oml * p.ar1;
-    p.ar2 = p.last_alpha * p.lc2 + oml * p.ar2;
+    ok0 = ok0 && !(a0 < 1.0f / 255.0f);
+    ok1 = ok1 && !(a1 < 1.0f / 255.0f);
+    if (!ok0 && !ok1) return false;
+    const f2 alpha = pk(ok0 ? a0 : 0.f, ok1 ? a1 : 0.f);
+    const f2 oma = fma2(alpha, bc(-1.0f), bc(1.0f));
+    const f2 rcp1ma = pk(rcp_approx(lo(oma)), rcp_approx(hi(oma)));  // 1-alpha in [0.01,1]; rcp.approx(1) == 1 exactly
+    p.T = mul2(p.T, rcp1ma);
+    const f2 weight = mul2(alpha, p.T);
+    const f2 oml = fma2(p.last_alpha, bc(-1.0f), bc(1.0f));
+    p.ar0 = fma2(p.last_alpha, bc(p.lc0), mul2(oml, p.ar0));
+    p.ar1 = fma2(p.last_alpha, bc(p.lc1), mul2(oml, p.ar1));
+    p.ar2 = fma2(p.last_alpha, bc(p.lc2), mul2(oml, p.ar2));
     p.lc0 = q1.z; p.lc1 = q1.w; p.lc2 = q2.x;
-    float dL_dalpha = (q1.z - p.ar0) * p.g0 + (q1.w - p.ar1) * p.g1 + (q2.x - p.ar2) * p.g2;
-    v[6] += weight * p.g0;
-    v[7] += weight * p.g1;
-    v[8] += weight * p.g2;
+    f2 dL_dalpha = mul2(fma2(p.ar0, bc(-1.0f), bc(q1.z)), p.g0);
+    dL_dalpha = fma2(fma2(p.ar1, bc(-1.0f), bc(q1.w)), p.g1, dL_dalpha);
+    dL_dalpha = fma2(fma2(p.ar2, bc(-1.0f), bc(q2.x)), p.g2, dL_dalpha);
+    v[6] += hsum(mul2(weight, p.g0));
+    v[7] += hsum(mul2(weight, p.g1));
+    v[8] += hsum(mul2(weight, p.g2));
     if (DEPTH) {
-        p.ar_invd = p.last_alpha * p.last_invd + oml * p.ar_invd;
+        p.ar_invd = fma2(p.last_alpha, bc(p.last_invd), mul2(oml, p.ar_invd));
         p.last_invd = q2.y;
-        dL_dalpha += (q2.y - p.ar_invd) * p.gd;
-        v[9] += weight * p.gd;
+        dL_dalpha = fma2(fma2(p.ar_invd, bc(-1.0f), bc(q2.y)), p.gd, dL_dalpha);
+        v[9] += hsum(mul2(weight, p.gd));
     }
-    dL_dalpha *= p.T;
     p.last_alpha = alpha;
-    dL_dalpha -= p.T_final * rcp1ma * p.bg_dot;
-    dL_dalpha = nullalpha ? 0.f : dL_dalpha;
+    dL_dalpha = fma2(mul2(p.T_final, rcp1ma), p.nbg_dot, mul2(dL_dalpha, p.T));
+    f2 k = mul2(G, dL_dalpha);
+    const float k0 = (ok0 && !(ta0 > null_thr)) ? lo(k) : 0.f;  // 0.99 clamp (backward.cu:620,687); +inf threshold with AR's convention
+    const float k1 = (ok1 && !(ta1 > null_thr)) ? hi(k) : 0.f;
+    k = pk(k0, k1);
     // Per pair only the moments of k = G * dL_dalpha over (dx, dy) are accumulated; the splat-constant factors (conic,
-    // opacity, 0.5*W, 0.5*H, -0.5) of backward.cu:676-702 are applied once per (tile, splat) when the sums are flushed:
-    //   dL_dmean2D.x = -opac * 0.5W * (con.x * S[k dx] + con.y * S[k dy]),   dL_dconic.xx = -0.5 * opac * S[k dx dx], ...
-    const float k = G * dL_dalpha;
-    const float kdx = k * dx, kdy = k * dy;
-    v[0] += kdx;
-    v[1] += kdy;
-    v[2] = fmaf(kdx, dx, v[2]);
-    v[3] = fmaf(kdx, dy, v[3]);
-    v[4] = fmaf(kdy, dy, v[4]);
-    if (LOD) v[5] = fmaf(t - __powf(1.0f - my_alpha, frac - 1.0f) * (t - 1.0f) * frac, k, v[5]);
-    else v[5] += k;
+    // opacity, 0.5*W, 0.5*H, -0.5) of backward.cu:676-702 are applied once per (tile, splat) when the sums are flushed.
+    const f2 kdx = mul2(k, bc(dx)), kdy = mul2(k, dy);
+    v[0] += hsum(kdx);
+    v[1] += hsum(kdy);
+    v[2] += hsum(mul2(kdx, bc(dx)));
+    v[3] += hsum(mul2(kdx, dy));
+    v[4] += hsum(mul2(kdy, dy));
+    if (LOD) {
+        const float m0 = t - __powf(1.0f - ma0, frac - 1.0f) * (t - 1.0f) * frac;
+        const float m1 = t - __powf(1.0f - ma1, frac - 1.0f) * (t - 1.0f) * frac;
+        v[5] += fmaf(m0, k0, m1 * k1);
+    } else {
+        v[5] += k0 + k1;
+    }
     return true;
 }
 
@@ -152,29 +211,39 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
     const size_t HW = (size_t)H * W;
     const float bg0 = bg_color[0], bg1 = bg_color[1], bg2 = bg_color[2];
 
-    BwdPix px[2];
+    BwdPix2 p2;
+    {
+        float Tf[2], g0[2], g1[2], g2[2], gd[2];
+        unsigned last[2];
 #pragma unroll
-    for (int h = 0; h < 2; h++) {
-        BwdPix& p = px[h];
-        const unsigned y = pix_y0 + h;
-        const bool inside = pix_x < (unsigned)W && y < (unsigned)H;
-        const uint32_t pix_id = W * y + pix_x;
-        p.px = (float)pix_x;
-        p.py = (float)y;
-        p.T_final = inside ? final_Ts[pix_id] : 0.f;
-        p.T = p.T_final;
-        p.last_contributor = inside ? n_contrib[pix_id] : 0u;
-        p.last_alpha = 0.f;
-        p.lc0 = p.lc1 = p.lc2 = p.ar0 = p.ar1 = p.ar2 = p.last_invd = p.ar_invd = 0.f;
-        p.g0 = inside ? dL_dpixels[0 * HW + pix_id] : 0.f;
-        p.g1 = inside ? dL_dpixels[1 * HW + pix_id] : 0.f;
-        p.g2 = inside ? dL_dpixels[2 * HW + pix_id] : 0.f;
-        p.gd = (DEPTH && inside) ? dL_invdepths[pix_id] : 0.f;
-        p.bg_dot = bg_mult * (bg0 * p.g0 + bg1 * p.g1 + bg2 * p.g2);
+        for (int h = 0; h < 2; h++) {
+            const unsigned y = pix_y0 + h;
+            const bool inside = pix_x < (unsigned)W && y < (unsigned)H;
+            const uint32_t pix_id = W * y + pix_x;
+            Tf[h] = inside ? final_Ts[pix_id] : 0.f;
+            last[h] = inside ? n_contrib[pix_id] : 0u;
+            g0[h] = inside ? dL_dpixels[0 * HW + pix_id] : 0.f;
+            g1[h] = inside ? dL_dpixels[1 * HW + pix_id] : 0.f;
+            g2[h] = inside ? dL_dpixels[2 * HW + pix_id] : 0.f;
+            gd[h] = (DEPTH && inside) ? dL_invdepths[pix_id] : 0.f;
+        }
+        p2.px = (float)pix_x;
+        p2.npy = pk(-(float)pix_y0, -(float)(pix_y0 + 1u));
+        p2.T_final = pk(Tf[0], Tf[1]);
+        p2.T = p2.T_final;
+        p2.last0 = last[0];
+        p2.last1 = last[1];
+        p2.last_alpha = p2.ar0 = p2.ar1 = p2.ar2 = p2.ar_invd = bc(0.f);
+        p2.lc0 = p2.lc1 = p2.lc2 = p2.last_invd = 0.f;
+        p2.g0 = pk(g0[0], g0[1]);
+        p2.g1 = pk(g1[0], g1[1]);
+        p2.g2 = pk(g2[0], g2[1]);
+        p2.gd = pk(gd[0], gd[1]);
+        p2.nbg_dot = pk(-bg_mult * (bg0 * g0[0] + bg1 * g1[0] + bg2 * g2[0]), -bg_mult * (bg0 * g0[1] + bg1 * g1[1] + bg2 * g2[1]));
     }
 
     // the replay only has to cover splats up to the tile's deepest contributor
-    const unsigned wmax = __reduce_max_sync(0xffffffffu, max(px[0].last_contributor, px[1].last_contributor));
+    const unsigned wmax = __reduce_max_sync(0xffffffffu, max(p2.last0, p2.last1));
     if (lane == 0) sm.warp_max[warp] = wmax;
     if (tid == 0) {
         mbar_init(&sm.bar[0], BWD_THREADS);
@@ -280,16 +349,11 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
         float* accp = &sm.acc[s][jtop * NV];
         unsigned pos = lo + (unsigned)jtop;  // 0-based position in the tile's list == contributor index - 1
         for (int j = jtop; j >= 0; j--, rp -= 3, accp -= NV, pos--) {
-            const bool act0 = pos < px[0].last_contributor, act1 = pos < px[1].last_contributor;
             float v[NV];
 #pragma unroll
             for (int k = 0; k < NV; k++) v[k] = 0.f;
             const float4 q0 = rp[0], q1 = rp[1], q2 = rp[2];
-            bool contrib = false;
-            // the thread's two pixels share the column: dx and its two products are computed once
-            const float dx = __fsub_rn(q0.x, px[0].px), dxa = __fmul_rn(dx, q0.z), dxb = __fmul_rn(dx, q0.w);
-            if (act0) contrib |= bwd_pair<LOD, DEPTH>(px[0], dx, dxa, dxb, q0, q1, q2, null_thr, v);
-            if (act1) contrib |= bwd_pair<LOD, DEPTH>(px[1], dx, dxa, dxb, q0, q1, q2, null_thr, v);
+            const bool contrib = bwd_pair2<LOD, DEPTH>(p2, pos, q0, q1, q2, null_thr, v);
             if (!__any_sync(0xffffffffu, contrib)) continue;
             int slot;
             const float total = warp_reduce10(v, lane, slot);
