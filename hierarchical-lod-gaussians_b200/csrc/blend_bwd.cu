@@ -71,40 +71,6 @@ __device__ __forceinline__ float warp_reduce10(const float (&v)[NV], unsigned la
 // Splat constants enter as broadcast operands (mov.b64 {x,x} folds into the instruction). ptxas contracts mul+add pairs of
 // packed operations even with .rn; harmless here (gradients are held to 1e-3, not bit-exact), which is why the FORWARD
 // kernel, whose rounding is pinned, keeps scalar instructions.
-typedef unsigned long long f2;
-__device__ __forceinline__ f2 pk(float lo, float hi) {
-    f2 r;
-    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-    return r;
-}
-__device__ __forceinline__ f2 bc(float x) { return pk(x, x); }
-__device__ __forceinline__ float lo(f2 v) {
-    float a, b;
-    asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
-    return a;
-}
-__device__ __forceinline__ float hi(f2 v) {
-    float a, b;
-    asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
-    return b;
-}
-__device__ __forceinline__ float hsum(f2 v) { return lo(v) + hi(v); }
-__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) {
-    f2 r;
-    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
-    return r;
-}
-__device__ __forceinline__ f2 mul2(f2 a, f2 b) {
-    f2 r;
-    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-    return r;
-}
-__device__ __forceinline__ f2 add2(f2 a, f2 b) {
-    f2 r;
-    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-    return r;
-}
-
 // Replay state of the thread's two pixels (lo = upper pixel, hi = the one below it).
 struct BwdPix2 {
     f2 npy, T, T_final, last_alpha, ar0, ar1, ar2, ar_invd, g0, g1, g2, gd, nbg_dot;

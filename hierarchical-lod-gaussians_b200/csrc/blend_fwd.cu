@@ -22,40 +22,62 @@ struct BlendSmem {
     uint64_t bar[2];
 };
 
-struct PixState {
-    float px, py, T, C0, C1, C2, D;
-    uint32_t last;
+// Blend state of the thread's two pixels in packed FP32 pairs (lo = upper pixel, hi = the one below it).
+struct PixState2 {
+    f2 npy, T, C0, C1, C2, D;
+    float px;
+    uint32_t last0, last1;
 };
 
-// One (pixel, splat) pair; rounding pinned to the reference build's PTX for renderCUDA (forward.cu:529-585):
-// power = (dx*(dx*con.x) + dy*(dy*con.z)) * -0.5 - dy*(dx*con.y), C += T * (alpha * c).
-// dx, dxa = dx*con.x and dxb = dx*con.y are shared by the thread's two pixels (same column) and come from the caller.
+// One splat against the thread's two pixels, rounding pinned to the reference build's SASS for renderCUDA (forward.cu:529-585):
+//   power = (dx*(dx*con.x) + dy*(dy*con.z)) * -0.5 - dy*(dx*con.y),   C += T * (alpha * c),   T *= (1 - alpha)
+// evaluated on packed pairs: every half performs exactly the IEEE operations of the scalar code —
+//   dy = y + (-py);  quad = fma(dx, dx*con.x, dy*(dy*con.z));  power = fma(quad, -0.5, dy*(-(dx*con.y)))  [quad * -0.5 is exact,
+//   so the fused form equals the reference's rounded product minus rounded product];  1 - alpha = fma(alpha, -1, 1);
+//   C = fma(T, alpha*c, C) — and only sequences ptxas cannot re-contract are used (see common.cuh).
+// A pixel that does not take the splat (saturated, power > 0, below the cut-off, alpha < 1/255, or saturating on this splat)
+// rides along with alpha 0: fma(T, 0*c, C) == C and its T is kept by a select, so its results are untouched bit for bit.
 template <bool LOD, bool DEPTH, bool SEEN>
-__device__ __forceinline__ void blend_pair(PixState& p, unsigned& done, const float dx, const float dxa, const float dxb, const float4 q0,
-                                           const float4 q1, const float4 q2, uint32_t contributor, uint8_t* flagp) {
-    const float dy = __fsub_rn(q0.y, p.py);
-    const float quad = __fmaf_rn(dx, dxa, __fmul_rn(dy, __fmul_rn(dy, q1.x)));
-    const float power = __fsub_rn(__fmul_rn(quad, -0.5f), __fmul_rn(dy, dxb));
-    if (power > 0.0f) return;
-    if (!LOD && power < q2.z) return;  // alpha is certainly below 1/255 (cut-off precomputed per splat, see preprocess_one)
-    float alpha = fminf(0.99f, __fmul_rn(q1.y, expf(power)));
+__device__ __forceinline__ void blend_pair2(PixState2& p, unsigned& done0, unsigned& done1, const float4 q0, const float4 q1,
+                                            const float4 q2, uint32_t contributor, uint8_t* flagp) {
+    const float dx = __fsub_rn(q0.x, p.px), dxa = __fmul_rn(dx, q0.z), ndxb = -__fmul_rn(dx, q0.w);
+    const f2 dy = add2(bc(q0.y), p.npy);
+    const f2 quad = fma2(bc(dx), bc(dxa), mul2(dy, mul2(dy, bc(q1.x))));
+    const f2 power = fma2(quad, bc(-0.5f), mul2(dy, bc(ndxb)));
+    const float pw0 = lo(power), pw1 = hi(power);
+    bool ok0 = !done0 && !(pw0 > 0.0f), ok1 = !done1 && !(pw1 > 0.0f);
+    if (!LOD) {  // alpha is certainly below 1/255 (cut-off precomputed per splat, see preprocess_one)
+        ok0 = ok0 && !(pw0 < q2.z);
+        ok1 = ok1 && !(pw1 < q2.z);
+    }
+    if (!ok0 && !ok1) return;
+    const f2 al = mul2(bc(q1.y), pk(expf(pw0), expf(pw1)));
+    float a0 = fminf(0.99f, lo(al)), a1 = fminf(0.99f, hi(al));
     if (LOD) {
-        const float kidsqrt_alpha = __fsub_rn(1.0f, __powf(__fsub_rn(1.0f, alpha), q2.w));
-        alpha = __fmaf_rn(alpha, q2.z, __fmul_rn(__fsub_rn(1.0f, q2.z), kidsqrt_alpha));
+        const float k0 = __fsub_rn(1.0f, __powf(__fsub_rn(1.0f, a0), q2.w)), k1 = __fsub_rn(1.0f, __powf(__fsub_rn(1.0f, a1), q2.w));
+        const float omt = __fsub_rn(1.0f, q2.z);
+        a0 = __fmaf_rn(a0, q2.z, __fmul_rn(omt, k0));
+        a1 = __fmaf_rn(a1, q2.z, __fmul_rn(omt, k1));
     }
-    if (alpha < 1.0f / 255.0f) return;
-    const float test_T = __fmul_rn(p.T, __fsub_rn(1.0f, alpha));
-    if (test_T < 0.0001f) {
-        done = 1u;
-        return;
-    }
+    ok0 = ok0 && !(a0 < 1.0f / 255.0f);
+    ok1 = ok1 && !(a1 < 1.0f / 255.0f);
+    if (!ok0 && !ok1) return;
+    const f2 test_T = mul2(p.T, fma2(pk(a0, a1), bc(-1.0f), bc(1.0f)));
+    const float t0 = lo(test_T), t1 = hi(test_T);
+    const bool sat0 = ok0 && t0 < 0.0001f, sat1 = ok1 && t1 < 0.0001f;
+    if (sat0) done0 = 1u;
+    if (sat1) done1 = 1u;
+    const bool bl0 = ok0 && !sat0, bl1 = ok1 && !sat1;
+    if (!bl0 && !bl1) return;
     if (SEEN) *flagp = 1;
-    p.C0 = __fmaf_rn(p.T, __fmul_rn(alpha, q1.z), p.C0);
-    p.C1 = __fmaf_rn(p.T, __fmul_rn(alpha, q1.w), p.C1);
-    p.C2 = __fmaf_rn(p.T, __fmul_rn(alpha, q2.x), p.C2);
-    if (DEPTH) p.D = __fmaf_rn(p.T, __fmul_rn(alpha, q2.y), p.D);  // q2.y = rcp.rn(depth), precomputed per instance
-    p.T = test_T;
-    p.last = contributor;
+    const f2 ae = pk(bl0 ? a0 : 0.f, bl1 ? a1 : 0.f);
+    p.C0 = fma2(p.T, mul2(ae, bc(q1.z)), p.C0);
+    p.C1 = fma2(p.T, mul2(ae, bc(q1.w)), p.C1);
+    p.C2 = fma2(p.T, mul2(ae, bc(q2.x)), p.C2);
+    if (DEPTH) p.D = fma2(p.T, mul2(ae, bc(q2.y)), p.D);  // q2.y = rcp.rn(depth), precomputed per Gaussian
+    p.T = pk(bl0 ? t0 : lo(p.T), bl1 ? t1 : hi(p.T));
+    if (bl0) p.last0 = contributor;
+    if (bl1) p.last1 = contributor;
 }
 
 template <bool LOD, bool DEPTH, bool SEEN>
@@ -72,8 +94,12 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* _
     const bool inside0 = pix_x < (unsigned)W && pix_y0 < (unsigned)H;
     const bool inside1 = pix_x < (unsigned)W && pix_y0 + 1u < (unsigned)H;
     unsigned done0 = inside0 ? 0u : 1u, done1 = inside1 ? 0u : 1u;
-    PixState p0 = {(float)pix_x, (float)pix_y0, 1.0f, 0.f, 0.f, 0.f, 0.f, 0u};
-    PixState p1 = {(float)pix_x, (float)(pix_y0 + 1u), 1.0f, 0.f, 0.f, 0.f, 0.f, 0u};
+    PixState2 p;
+    p.px = (float)pix_x;
+    p.npy = pk(-(float)pix_y0, -(float)(pix_y0 + 1u));
+    p.T = bc(1.0f);
+    p.C0 = p.C1 = p.C2 = p.D = bc(0.f);
+    p.last0 = p.last1 = 0u;
 
     const uint2 range = ranges[blockIdx.y * horizontal_blocks + blockIdx.x];
     const int total = (int)(range.y - range.x);
@@ -170,9 +196,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* _
             const float4 q0 = rp[0];  // x y conx cony
             const float4 q1 = rp[1];  // conz opac r g
             const float4 q2 = rp[2];  // b 1/depth t 1/kids
-            const float dx = __fsub_rn(q0.x, p0.px), dxa = __fmul_rn(dx, q0.z), dxb = __fmul_rn(dx, q0.w);
-            if (!done0) blend_pair<LOD, DEPTH, SEEN>(p0, done0, dx, dxa, dxb, q0, q1, q2, contributor, fl);
-            if (!done1) blend_pair<LOD, DEPTH, SEEN>(p1, done1, dx, dxa, dxb, q0, q1, q2, contributor, fl);
+            blend_pair2<LOD, DEPTH, SEEN>(p, done0, done1, q0, q1, q2, contributor, fl);
         }
     }
     if (SEEN) {
@@ -183,21 +207,21 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* _
     const float bg0 = bg_color[0], bg1 = bg_color[1], bg2 = bg_color[2];
     if (inside0) {
         const uint32_t pix_id = W * pix_y0 + pix_x;
-        final_T[pix_id] = p0.T;
-        n_contrib[pix_id] = p0.last;
-        out_color[0 * HW + pix_id] = __fmaf_rn(p0.T, bg0, p0.C0);
-        out_color[1 * HW + pix_id] = __fmaf_rn(p0.T, bg1, p0.C1);
-        out_color[2 * HW + pix_id] = __fmaf_rn(p0.T, bg2, p0.C2);
-        if (DEPTH) out_invdepth[pix_id] = p0.D;
+        final_T[pix_id] = lo(p.T);
+        n_contrib[pix_id] = p.last0;
+        out_color[0 * HW + pix_id] = __fmaf_rn(lo(p.T), bg0, lo(p.C0));
+        out_color[1 * HW + pix_id] = __fmaf_rn(lo(p.T), bg1, lo(p.C1));
+        out_color[2 * HW + pix_id] = __fmaf_rn(lo(p.T), bg2, lo(p.C2));
+        if (DEPTH) out_invdepth[pix_id] = lo(p.D);
     }
     if (inside1) {
         const uint32_t pix_id = W * (pix_y0 + 1u) + pix_x;
-        final_T[pix_id] = p1.T;
-        n_contrib[pix_id] = p1.last;
-        out_color[0 * HW + pix_id] = __fmaf_rn(p1.T, bg0, p1.C0);
-        out_color[1 * HW + pix_id] = __fmaf_rn(p1.T, bg1, p1.C1);
-        out_color[2 * HW + pix_id] = __fmaf_rn(p1.T, bg2, p1.C2);
-        if (DEPTH) out_invdepth[pix_id] = p1.D;
+        final_T[pix_id] = hi(p.T);
+        n_contrib[pix_id] = p.last1;
+        out_color[0 * HW + pix_id] = __fmaf_rn(hi(p.T), bg0, hi(p.C0));
+        out_color[1 * HW + pix_id] = __fmaf_rn(hi(p.T), bg1, hi(p.C1));
+        out_color[2 * HW + pix_id] = __fmaf_rn(hi(p.T), bg2, hi(p.C2));
+        if (DEPTH) out_invdepth[pix_id] = hi(p.D);
     }
 }
 

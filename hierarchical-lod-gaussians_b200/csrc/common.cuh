@@ -117,6 +117,43 @@ __device__ __forceinline__ unsigned long long lookback_warp(const unsigned long 
     return exclusive;
 }
 
+// ---- packed FP32 pairs (sm_100: FFMA2 / FMUL2 / FADD2 take one issue slot for two lanes of work). mov.b64 {x,x} folds into
+// the instruction as a broadcast operand. NOTE: ptxas contracts a packed mul feeding a packed add into one FFMA2 even when both
+// carry .rn — code whose rounding is pinned must only use sequences where that cannot happen (explicit fma2, mul feeding mul/fma).
+typedef unsigned long long f2;
+__device__ __forceinline__ f2 pk(float lo, float hi) {
+    f2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ f2 bc(float x) { return pk(x, x); }
+__device__ __forceinline__ float lo(f2 v) {
+    float a, b;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+    return a;
+}
+__device__ __forceinline__ float hi(f2 v) {
+    float a, b;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+    return b;
+}
+__device__ __forceinline__ float hsum(f2 v) { return lo(v) + hi(v); }
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) {
+    f2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) {
+    f2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f2 add2(f2 a, f2 b) {
+    f2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 // ---- mbarrier + 1-D bulk async copy (TMA unit; SASS: UBLKCP)
