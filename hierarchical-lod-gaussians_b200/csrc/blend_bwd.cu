@@ -125,14 +125,14 @@ __device__ __forceinline__ bool bwd_pair2(BwdPix2& p, const unsigned pos, const 
     f2 dL_dalpha = mul2(fma2(p.ar0, bc(-1.0f), bc(q1.z)), p.g0);
     dL_dalpha = fma2(fma2(p.ar1, bc(-1.0f), bc(q1.w)), p.g1, dL_dalpha);
     dL_dalpha = fma2(fma2(p.ar2, bc(-1.0f), bc(q2.x)), p.g2, dL_dalpha);
-    v[6] += hsum(mul2(weight, p.g0));
-    v[7] += hsum(mul2(weight, p.g1));
-    v[8] += hsum(mul2(weight, p.g2));
+    v[6] = hsum(mul2(weight, p.g0));
+    v[7] = hsum(mul2(weight, p.g1));
+    v[8] = hsum(mul2(weight, p.g2));
     if (DEPTH) {
         p.ar_invd = fma2(p.last_alpha, bc(p.last_invd), mul2(oml, p.ar_invd));
         p.last_invd = q2.y;
         dL_dalpha = fma2(fma2(p.ar_invd, bc(-1.0f), bc(q2.y)), p.gd, dL_dalpha);
-        v[9] += hsum(mul2(weight, p.gd));
+        v[9] = hsum(mul2(weight, p.gd));
     }
     p.last_alpha = alpha;
     dL_dalpha = fma2(mul2(p.T_final, rcp1ma), p.nbg_dot, mul2(dL_dalpha, p.T));
@@ -143,17 +143,17 @@ __device__ __forceinline__ bool bwd_pair2(BwdPix2& p, const unsigned pos, const 
     // Per pair only the moments of k = G * dL_dalpha over (dx, dy) are accumulated; the splat-constant factors (conic,
     // opacity, 0.5*W, 0.5*H, -0.5) of backward.cu:676-702 are applied once per (tile, splat) when the sums are flushed.
     const f2 kdx = mul2(k, bc(dx)), kdy = mul2(k, dy);
-    v[0] += hsum(kdx);
-    v[1] += hsum(kdy);
-    v[2] += hsum(mul2(kdx, bc(dx)));
-    v[3] += hsum(mul2(kdx, dy));
-    v[4] += hsum(mul2(kdy, dy));
+    v[0] = hsum(kdx);
+    v[1] = hsum(kdy);
+    v[2] = hsum(mul2(kdx, bc(dx)));
+    v[3] = hsum(mul2(kdx, dy));
+    v[4] = hsum(mul2(kdy, dy));
     if (LOD) {
         const float m0 = t - __powf(1.0f - ma0, frac - 1.0f) * (t - 1.0f) * frac;
         const float m1 = t - __powf(1.0f - ma1, frac - 1.0f) * (t - 1.0f) * frac;
-        v[5] += fmaf(m0, k0, m1 * k1);
+        v[5] = fmaf(m0, k0, m1 * k1);
     } else {
-        v[5] += k0 + k1;
+        v[5] = k0 + k1;
     }
     return true;
 }

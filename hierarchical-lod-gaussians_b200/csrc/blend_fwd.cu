@@ -68,13 +68,12 @@ __device__ __forceinline__ void blend_pair2(PixState2& p, unsigned& done0, unsig
     if (sat0) done0 = 1u;
     if (sat1) done1 = 1u;
     const bool bl0 = ok0 && !sat0, bl1 = ok1 && !sat1;
-    if (!bl0 && !bl1) return;
-    if (SEEN) *flagp = 1;
+    if (SEEN && (bl0 || bl1)) *flagp = 1;
     const f2 ae = pk(bl0 ? a0 : 0.f, bl1 ? a1 : 0.f);
-    p.C0 = fma2(p.T, mul2(ae, bc(q1.z)), p.C0);
-    p.C1 = fma2(p.T, mul2(ae, bc(q1.w)), p.C1);
-    p.C2 = fma2(p.T, mul2(ae, bc(q2.x)), p.C2);
-    if (DEPTH) p.D = fma2(p.T, mul2(ae, bc(q2.y)), p.D);  // q2.y = rcp.rn(depth), precomputed per Gaussian
+    fma2_acc(p.C0, p.T, mul2(ae, bc(q1.z)));
+    fma2_acc(p.C1, p.T, mul2(ae, bc(q1.w)));
+    fma2_acc(p.C2, p.T, mul2(ae, bc(q2.x)));
+    if (DEPTH) fma2_acc(p.D, p.T, mul2(ae, bc(q2.y)));  // q2.y = rcp.rn(depth), precomputed per Gaussian
     p.T = pk(bl0 ? t0 : lo(p.T), bl1 ? t1 : hi(p.T));
     if (bl0) p.last0 = contributor;
     if (bl1) p.last1 = contributor;

@@ -143,6 +143,8 @@ __device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) {
     asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
     return r;
 }
+// c = a * b + c with the accumulator tied to one register pair (keeps ptxas from computing into a temporary and copying back).
+__device__ __forceinline__ void fma2_acc(f2& c, f2 a, f2 b) { asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(c) : "l"(a), "l"(b)); }
 __device__ __forceinline__ f2 mul2(f2 a, f2 b) {
     f2 r;
     asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
