@@ -101,6 +101,34 @@ def get_interpolation_weights_dynamic(indices, size, nodes, positions, scales, v
                                                       float(v[2]), ptr(ts), ptr(num_kids), current_stream()))
 
 
+def get_spt_cut_cuda(number_of_SPTs, gaussian_indices, SPT_starts, SPT_max, SPT_min, SPT_indices, SPT_distances):
+    """GH/torch/torch_interface.cpp:287-316 (GetSPTCut): -> (cut ids i32[K], exclusive prefix sum of the per-slot counts i32[S]),
+    both on the device. Slot i selects table SPT_indices[i] at distance SPT_distances[i]."""
+    if gaussian_indices.device.type != "cuda":
+        raise RuntimeError("get_spt_cut_cuda needs CUDA tensors (there is no CPU path)")
+    dev = gaussian_indices.device
+    S = int(number_of_SPTs)
+    counts = torch.empty(S, dtype=torch.int32, device=dev)
+    if S == 0:
+        return torch.empty(0, dtype=torch.int32, device=dev), counts
+    gi, st = gaussian_indices.contiguous(), SPT_starts.contiguous()
+    mx, mn = SPT_max.contiguous(), SPT_min.contiguous()
+    si, sd = SPT_indices.to(torch.int32).contiguous(), SPT_distances.to(torch.float32).contiguous()
+    for t, dt, name in ((gi, torch.int32, "gaussian_indices"), (st, torch.int32, "SPT_starts"), (mx, torch.float32, "SPT_max"),
+                        (mn, torch.float32, "SPT_min")):
+        if t.dtype != dt:
+            raise RuntimeError("get_spt_cut_cuda: %s must be %s" % (name, dt))
+    n_entries = min(gi.numel(), mx.numel(), mn.numel())
+    ws = torch.empty(lib.lodgs_spt_cut_workspace_bytes(S), dtype=torch.uint8, device=dev)
+    count = C.c_int32(0)
+    check(lib.lodgs_spt_cut_count(S, ptr(gi), n_entries, ptr(st), ptr(mx), ptr(mn), ptr(si), ptr(sd), ptr(counts), ws.data_ptr(), ws.numel(),
+                                  C.addressof(count), current_stream()))
+    cut = torch.empty(int(count.value), dtype=torch.int32, device=dev)
+    check(lib.lodgs_spt_cut_write(S, ptr(gi), n_entries, ptr(st), ptr(mn), ptr(si), ptr(sd), ws.data_ptr(), ptr(cut), cut.numel(),
+                                  current_stream()))
+    return cut, counts
+
+
 def load_hierarchy(filename):
     """-> (pos[P,3], shs[P,16,3], alpha[P,1], scales[P,3], rot[P,4], nodes[N,7] i32, boxes[N,2,4]) CPU tensors."""
     P, N = C.c_int32(0), C.c_int32(0)

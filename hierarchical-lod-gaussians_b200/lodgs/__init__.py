@@ -68,6 +68,9 @@ _SIGS = {
     "lodgs_backward_ex": (_i, [_i, _i, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _f, _f, _p,
                                _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, C.c_uint, _p]),
     "lodgs_mark_visible": (_i, [_i, _p, _p, _p, _p, _p]),
+    "lodgs_spt_cut_workspace_bytes": (_sz, [_i]),
+    "lodgs_spt_cut_count": (_i, [_i, _p, _i, _p, _p, _p, _p, _p, _p, _p, _sz, _p, _p]),
+    "lodgs_spt_cut_write": (_i, [_i, _p, _i, _p, _p, _p, _p, _p, _p, _i, _p]),
     "lodgs_compute_relocation": (_i, [_i, _p, _p, _p, _p, _i, _p, _p, _p]),
     "lodgs_geom_layout": (_i, [_i, _p]),
     "lodgs_binning_layout": (_i, [_i, _p]),

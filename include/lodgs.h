@@ -92,6 +92,23 @@ int lodgs_get_interpolation_weights_dynamic(const int32_t* node_indices, int K, 
                                             const float* positions, const float* scales, float vx, float vy, float vz,
                                             float* ts, int32_t* num_siblings, void* stream);
 
+/* Cut through the selected SPTs. Replaces Switching::getSPTCut (GH/runtime_switching.cu:881-994, kernels :784-852) as bound by
+ * gaussian_hierarchy._C.get_spt_cut_cuda (GH/torch/torch_interface.cpp:287-316). Table t is the run
+ * [SPT_starts[t], SPT_starts[t+1]) of (gaussian_indices, SPT_min, SPT_max) entries, sorted by SPT_max descending; slot i selects
+ * table SPT_indices[i] at distance SPT_distances[i]. The result is the reference's entry for entry: ids of the entries with
+ * SPT_min < distance inside the bisected prefix of each run (with the reference's one-entry shift of that window, see
+ * csrc/cut_spt.cu), id 0 dropped, in slot order; counts_out[S] = exclusive prefix sum of the per-slot kept entries.
+ * Two calls because the caller allocates the result: lodgs_spt_cut_count fills counts_out and the workspace and returns the
+ * number of ids through *count_host (one 12-byte read-back; pass NULL to stay asynchronous), lodgs_spt_cut_write then writes at
+ * most `capacity` ids. n_entries = length of the three entry arrays; an entry index >= n_entries is treated as not kept. */
+size_t lodgs_spt_cut_workspace_bytes(int S);
+int lodgs_spt_cut_count(int S, const int32_t* gaussian_indices, int n_entries, const int32_t* SPT_starts, const float* SPT_max,
+                        const float* SPT_min, const int32_t* SPT_indices, const float* SPT_distances, int32_t* counts_out,
+                        void* ws, size_t ws_bytes, int32_t* count_host, void* stream);
+int lodgs_spt_cut_write(int S, const int32_t* gaussian_indices, int n_entries, const int32_t* SPT_starts, const float* SPT_min,
+                        const int32_t* SPT_indices, const float* SPT_distances, const void* ws, int32_t* cut_out, int capacity,
+                        void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Hierarchy file I/O (host only). Replaces HierarchyLoader::load (GH/hierarchy_loader.cpp:26-128)
  * behind gaussian_hierarchy._C.load_hierarchy (torch_interface.cpp:9-40), and HierarchyWriter::write

@@ -9,6 +9,7 @@
 #include "oracle.h"
 #include <float.h>
 #include <math.h>
+#include <stdlib.h>
 
 static float box_size(const float* b, const float* v) {
     const float* mn = b;
@@ -151,4 +152,52 @@ void orc_get_interpolation_weights_dynamic(const int32_t* indices, int K, float 
         ts[idx] = t;
         kids[idx] = n[1] < 0 ? 1 : nodes[(long)n[1] * 6 + 2];
     }
+}
+
+/* ---- SPT cut: Switching::getSPTCut (GH/runtime_switching.cu:881-994), thread loops of binary_search_SPTs (:784-810) and
+ * populate_SPT (:812-852) restated one to one, then DeviceSelect::If(!= 0) and the exclusive sum of the per-slot counts.
+ * cut must hold the concatenation length (sum of the interval sizes; call with cut = NULL to get it through *positions).
+ * n_entries guards the one-past-the-end probe (the reference reads out of bounds there); such a probe counts as not kept. */
+int orc_get_spt_cut(int S, const int32_t* gaussian_indices, int n_entries, const int32_t* starts, const float* spt_max, const float* spt_min,
+                    const int32_t* spt_indices, const float* spt_distances, int32_t* cut, int32_t* counts_prefix, int32_t* positions) {
+    if (S <= 0) { if (positions) *positions = 0; return 0; }
+    int32_t* sizes = (int32_t*)malloc(sizeof(int32_t) * (size_t)S);
+    int32_t* prefix = (int32_t*)malloc(sizeof(int32_t) * (size_t)S);
+    int32_t* counts = (int32_t*)calloc((size_t)S, sizeof(int32_t));
+    for (int idx = 0; idx < S; idx++) {
+        int index = spt_indices[idx];
+        float distance = spt_distances[idx];
+        int low = starts[index], high = starts[index + 1];
+        int pivot = (low + high) / 2;
+        while ((high - low) > 1) {
+            if (spt_max[pivot] > distance) low = pivot; else high = pivot;
+            pivot = (low + high) / 2;
+        }
+        sizes[idx] = high - starts[index];
+    }
+    int sum = 0;
+    for (int i = 0; i < S; i++) { prefix[i] = sum; sum += sizes[i]; }
+    if (positions) *positions = sum;
+    int K = 0;
+    if (cut) {
+        for (int idx = 0; idx < sum; idx++) {
+            int low = 0, high = S, interval = S / 2;
+            while (high - low > 1) {
+                if (prefix[interval] >= idx) high = interval; else low = interval;
+                interval = (high + low) / 2;
+            }
+            int offset = idx - prefix[interval];
+            long g = (long)starts[spt_indices[interval]] + offset;
+            int result = 0;
+            if (g >= 0 && g < n_entries && spt_min[g] < spt_distances[interval]) {
+                counts[interval] += 1;
+                result = gaussian_indices[g];
+            }
+            if (result != 0) cut[K++] = result;
+        }
+    }
+    int run = 0;
+    for (int i = 0; i < S; i++) { if (counts_prefix) counts_prefix[i] = run; run += counts[i]; }
+    free(sizes); free(prefix); free(counts);
+    return K;
 }

@@ -42,6 +42,8 @@ def lib():
         _lib.orc_expand_to_size_dynamic.restype = C.c_int
         _lib.orc_expand_to_size_dynamic.argtypes = [_ip, _fp, _fp, C.c_int, C.c_float, _fp, _fp, _ip, _ip, _ip]
         _lib.orc_get_interpolation_weights_dynamic.argtypes = [_ip, C.c_int, C.c_float, _ip, _fp, _fp, _fp, _fp, _ip]
+        _lib.orc_get_spt_cut.restype = C.c_int
+        _lib.orc_get_spt_cut.argtypes = [C.c_int, _ip, C.c_int, _ip, _fp, _fp, _ip, _fp, _ip, _ip, _ip]
         _lib.orc_forward.restype = C.c_int
         _lib.orc_forward.argtypes = [C.POINTER(Scene), C.POINTER(State)]
         _lib.orc_backward.argtypes = [C.POINTER(Scene), C.POINTER(State)] + [_fp] * 12
@@ -98,6 +100,19 @@ def get_interpolation_weights_dynamic(node_ids, tau, nodes, positions, scales, v
     ts, kids = np.zeros(K, np.float32), np.zeros(K, np.int32)
     lib().orc_get_interpolation_weights_dynamic(_i(idx), K, float(tau), _i(nodes), _f(pos), _f(sca), _f(vp), _f(ts), _i(kids))
     return ts, kids
+
+
+def get_spt_cut(gaussian_indices, SPT_starts, SPT_max, SPT_min, SPT_indices, SPT_distances):
+    """Switching::getSPTCut restated on numpy arrays -> (cut i32[K], exclusive prefix of the per-slot counts i32[S])."""
+    gi, st, si = _c(gaussian_indices, np.int32), _c(SPT_starts, np.int32), _c(SPT_indices, np.int32)
+    mx, mn, sd = _c(SPT_max, np.float32), _c(SPT_min, np.float32), _c(SPT_distances, np.float32)
+    S, n = si.size, min(gi.size, mx.size, mn.size)
+    pos = np.zeros(1, np.int32)
+    lib().orc_get_spt_cut(S, _i(gi), n, _i(st), _f(mx), _f(mn), _i(si), _f(sd), None, None, _i(pos))
+    cut = np.zeros(max(int(pos[0]), 1), np.int32)
+    counts = np.zeros(S, np.int32)
+    K = lib().orc_get_spt_cut(S, _i(gi), n, _i(st), _f(mx), _f(mn), _i(si), _f(sd), _i(cut), _i(counts), _i(pos))
+    return cut[:K].copy(), counts
 
 
 def _scene(sc, cam, bg, indices, parent_indices, ts, kids, do_depth, colors, keep):

@@ -103,6 +103,27 @@ REF_API void ref_get_ts_indexed_dynamic(int K, int* indices, float target_size, 
     Switching::getTsIndexedDynamic(K, indices, target_size, nodes, positions, scales, vx, vy, vz, zx, zy, zz, ts, kids, stream);
 }
 
+// Switching::getSPTCut returns two device allocations; _run keeps them until _fetch copies them into the caller's buffers.
+static int* g_spt_cut = nullptr;
+static int* g_spt_counts = nullptr;
+REF_API int ref_get_spt_cut_run(int S, int* gaussian_indices, int* SPT_starts, float* SPT_max, float* SPT_min, int* SPT_indices,
+                                float* SPT_distances) {
+    if (g_spt_cut) cudaFree(g_spt_cut);
+    if (g_spt_counts) cudaFree(g_spt_counts);
+    g_spt_cut = g_spt_counts = nullptr;
+    return Switching::getSPTCut(S, gaussian_indices, SPT_starts, SPT_max, SPT_min, SPT_indices, SPT_distances, &g_spt_cut, &g_spt_counts);
+}
+REF_API int ref_get_spt_cut_fetch(int K, int S, int* cut_out, int* counts_out) {
+    cudaError_t e = cudaSuccess;
+    if (K > 0) e = cudaMemcpy(cut_out, g_spt_cut, (size_t)K * sizeof(int), cudaMemcpyDeviceToDevice);
+    if (e == cudaSuccess && S > 0) e = cudaMemcpy(counts_out, g_spt_counts, (size_t)S * sizeof(int), cudaMemcpyDeviceToDevice);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (g_spt_cut) cudaFree(g_spt_cut);
+    if (g_spt_counts) cudaFree(g_spt_counts);
+    g_spt_cut = g_spt_counts = nullptr;
+    return (int)e;
+}
+
 REF_API int ref_copy_d2d(void* dst, const void* src, size_t nbytes) {
     cudaError_t e = cudaMemcpy(dst, src, nbytes, cudaMemcpyDeviceToDevice);
     if (e == cudaSuccess) e = cudaDeviceSynchronize();

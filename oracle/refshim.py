@@ -39,7 +39,25 @@ def lib():
         _lib.ref_expand_to_size_dynamic.argtypes = [_i, _f, _p, _p, _p, _p, _f, _f, _f, _p, _p, _p]
         _lib.ref_get_ts_indexed_dynamic.restype = None
         _lib.ref_get_ts_indexed_dynamic.argtypes = [_i, _p, _f, _p, _p, _p, _f, _f, _f, _f, _f, _f, _p, _p, _p]
+        _lib.ref_get_spt_cut_run.restype = _i
+        _lib.ref_get_spt_cut_run.argtypes = [_i, _p, _p, _p, _p, _p, _p]
+        _lib.ref_get_spt_cut_fetch.restype = _i
+        _lib.ref_get_spt_cut_fetch.argtypes = [_i, _i, _p, _p]
     return _lib
+
+
+def get_spt_cut(gaussian_indices, SPT_starts, SPT_max, SPT_min, SPT_indices, SPT_distances):
+    """Switching::getSPTCut on CUDA tensors -> (cut i32[K], counts prefix i32[S]) as CUDA tensors."""
+    S = SPT_indices.numel()
+    torch.cuda.synchronize()
+    K = lib().ref_get_spt_cut_run(S, gaussian_indices.data_ptr(), SPT_starts.data_ptr(), SPT_max.data_ptr(), SPT_min.data_ptr(),
+                                  SPT_indices.data_ptr(), SPT_distances.data_ptr())
+    cut = torch.empty(max(K, 0), dtype=torch.int32, device="cuda")
+    counts = torch.empty(S, dtype=torch.int32, device="cuda")
+    rc = lib().ref_get_spt_cut_fetch(max(K, 0), S, cut.data_ptr() if K > 0 else None, counts.data_ptr())
+    if rc != 0:
+        raise RuntimeError("ref_get_spt_cut_fetch: cuda error %d" % rc)
+    return cut, counts
 
 
 def ptr(t):

@@ -78,3 +78,12 @@ for vi, (v, z) in enumerate(dviews):
         res[key + "_ts"], res[key + "_kids"] = ts[:K].cpu().numpy(), kids[:K].cpu().numpy()
         print("dyn", key, "K", K)
 np.savez_compressed(os.path.join(OUT, "cut_dynamic.npz"), **res)
+
+# ---- SPT cut (Switching::getSPTCut)
+res = {}
+for name in cases.SPT_CASES:
+    arrs = [torch.from_numpy(a).cuda() for a in cases.make_spt_case(name)]
+    cut, counts = refshim.get_spt_cut(*arrs)
+    res[name + "_cut"], res[name + "_counts"] = cut.cpu().numpy(), counts.cpu().numpy()
+    print("spt", name, "K", cut.numel())
+np.savez_compressed(os.path.join(OUT, "cut_spt.npz"), **res)

@@ -138,6 +138,8 @@ def test_plugin_surface_matches_reference_names():
         "nodes", "positions", "scales", "size", "viewpoint", "viewdir", "render_indices", "parent_indices", "nodes_for_render_indices"]
     assert list(inspect.signature(ghc.get_interpolation_weights_dynamic).parameters) == [
         "indices", "size", "nodes", "positions", "scales", "viewpoint", "viewdir", "ts", "num_kids"]
+    assert list(inspect.signature(ghc.get_spt_cut_cuda).parameters) == [
+        "number_of_SPTs", "gaussian_indices", "SPT_starts", "SPT_max", "SPT_min", "SPT_indices", "SPT_distances"]
     from lodgs.optim import Adam
     assert list(inspect.signature(Adam.step).parameters)[:2] == ["self", "relevant"]
     r = d.GaussianRasterizer(None)

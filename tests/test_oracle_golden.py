@@ -85,3 +85,16 @@ def test_raster_oracle_matches_reference(name):
         assert rel_l2(gr[k], g[k]) < 1e-3, k
     if name != "lod":  # reference LOD mean gradients are racy / read uninitialised flags
         assert rel_l2(gr["dL_dmean3D"], g["dL_dmean3D"]) < 1e-3
+
+
+def test_spt_cut_oracle_matches_reference_and_window_model():
+    """Switching::getSPTCut restatement vs the reference's outputs (cut_spt.npz), and the per-slot window formulation the CUDA
+    kernels use (cases.spt_cut_model) vs the restatement."""
+    g = np.load(os.path.join(GOLD, "cut_spt.npz"))
+    for name in cases.SPT_CASES:
+        arrs = cases.make_spt_case(name)
+        cut, counts = orc.get_spt_cut(*arrs)
+        assert np.array_equal(cut, g[name + "_cut"]) and np.array_equal(counts, g[name + "_counts"]), name
+        if name != "large":
+            m_cut, m_counts = cases.spt_cut_model(*arrs)
+            assert np.array_equal(cut, m_cut) and np.array_equal(counts, m_counts), name
