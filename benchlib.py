@@ -293,8 +293,21 @@ def _eager_index_adam(arm, relevant, grads):
         arm.tp[k][relevant] = param
 
 
+def _ncu_traffic():
+    """DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of each kernel from the newest committed
+    `ncu --set full` capture of this same workload (profiles/*ncu_traffic*.json); ({}, None) when there is none."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*ncu_traffic*.json")))
+    if not files:
+        return {}, None
+    with open(files[-1]) as fh:
+        t = json.load(fh)
+    return {k: max(e["dram_bytes"] for e in v) for k, v in t.get("kernels", {}).items()}, os.path.relpath(files[-1], ROOT)
+
+
 def _roofline(prof, steps, work, sm_count):
     hbm_peak, sm_max_mhz, which = _peaks()
+    traffic, traffic_src = _ncu_traffic()
     fp32_peak = sm_count * 128 * 2 * sm_max_mhz * 1e6 / 1e12  # TFLOP/s at max clock
     per_kernel = []
     for name, (ms, n) in prof.items():
@@ -315,7 +328,7 @@ def _roofline(prof, steps, work, sm_count):
     roof = None
     if dom is not None:
         roof = {"kernel": dom["kernel"], "bound": dom["bound"], "achieved": dom["achieved"], "peak": dom["peak"], "unit": dom["unit"],
-                "frac": dom["frac"], "traffic": None,
+                "frac": dom["frac"], "traffic": traffic.get(dom["kernel"]), "traffic_source": traffic_src,
                 "peak_source": ("%s HBM copy bandwidth (MEASURED_PEAKS.json)" % which) if dom["bound"] == "hbm" else
                 "nominal FP32 pipe: SMs x 128 lanes x 2 x max SM clock (no tensor cores on this path)"}
     return roof, per_kernel

@@ -314,7 +314,7 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
         const float4* __restrict__ rp = reinterpret_cast<const float4*>(&sm.recs[s][0]) + 3 * jtop;
         float* accp = &sm.acc[s][jtop * NV];
         unsigned pos = lo + (unsigned)jtop;  // 0-based position in the tile's list == contributor index - 1
-        for (int j = jtop; j >= 0; j--, rp -= 3, accp -= NV, pos--) {
+        _Pragma("unroll 2") for (int j = jtop; j >= 0; j--, rp -= 3, accp -= NV, pos--) {
             float v[NV];
 #pragma unroll
             for (int k = 0; k < NV; k++) v[k] = 0.f;

@@ -188,7 +188,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* _
         const float4* __restrict__ rp = reinterpret_cast<const float4*>(&sm.recs[s][0]);
         uint8_t* fl = &sm.flag[s][0];
         uint32_t contributor = (uint32_t)b * BLEND_BATCH;
-        for (int j = 0; j < cnt; j++, rp += 3, fl++) {
+        _Pragma("unroll 2") for (int j = 0; j < cnt; j++, rp += 3, fl++) {
             contributor++;
             // ballot-based early termination: the warp stops scanning once all of its 64 pixels are saturated
             if (__all_sync(0xffffffffu, (done0 & done1) != 0u)) break;
