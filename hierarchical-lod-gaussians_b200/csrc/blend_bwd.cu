@@ -81,7 +81,9 @@ struct BwdPix2 {
 // One splat against both pixels (backward.cu:600-716). A pixel the splat does not contribute to (behind its last contributor,
 // power > 0, below the cut-off or alpha < 1/255) takes part as a ZERO-ALPHA splat: T / (1 - 0) = T, the running colour
 // recurrence ar' = last_alpha*lc + (1-last_alpha)*ar passes through it unchanged (the next splat sees last_alpha = 0), and
-// its k is forced to 0 — so no per-pixel branches and no per-pixel copies of the previous colour are needed.
+// its k is forced to 0 — so no per-pixel branches and no per-pixel copies of the previous colour are needed. The same holds
+// for a whole LANE: the two early-outs are warp votes (the return value is warp-uniform), a lane whose pixels both skip the
+// splat produces ten exact zeros, so there is no divergence inside the loop and nothing to clear before the reduction.
 template <bool LOD, bool DEPTH>
 __device__ __forceinline__ bool bwd_pair2(BwdPix2& p, const unsigned pos, const float4 q0, const float4 q1, const float4 q2,
                                           const float null_thr, float (&v)[NV]) {
@@ -95,7 +97,7 @@ __device__ __forceinline__ bool bwd_pair2(BwdPix2& p, const unsigned pos, const 
         ok0 = ok0 && !(pw0 < q2.z);
         ok1 = ok1 && !(pw1 < q2.z);
     }
-    if (!ok0 && !ok1) return false;
+    if (!__any_sync(0xffffffffu, ok0 || ok1)) return false;  // warp-uniform: lanes without a contribution ride along with alpha 0
     // ex2.approx instead of the forward's full-range expf: alpha moves by ~1e-7 relative, far inside the gradient budget
     const float G0 = __expf(pw0), G1 = __expf(pw1);
     const f2 G = pk(G0, G1);
@@ -111,7 +113,7 @@ __device__ __forceinline__ bool bwd_pair2(BwdPix2& p, const unsigned pos, const 
     }
     ok0 = ok0 && !(a0 < 1.0f / 255.0f);
     ok1 = ok1 && !(a1 < 1.0f / 255.0f);
-    if (!ok0 && !ok1) return false;
+    if (!__any_sync(0xffffffffu, ok0 || ok1)) return false;
     const f2 alpha = pk(ok0 ? a0 : 0.f, ok1 ? a1 : 0.f);
     const f2 oma = fma2(alpha, bc(-1.0f), bc(1.0f));
     const f2 rcp1ma = pk(rcp_approx(lo(oma)), rcp_approx(hi(oma)));  // 1-alpha in [0.01,1]; rcp.approx(1) == 1 exactly
@@ -316,11 +318,8 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
         unsigned pos = lo + (unsigned)jtop;  // 0-based position in the tile's list == contributor index - 1
         _Pragma("unroll 2") for (int j = jtop; j >= 0; j--, rp -= 3, accp -= NV, pos--) {
             float v[NV];
-#pragma unroll
-            for (int k = 0; k < NV; k++) v[k] = 0.f;
             const float4 q0 = rp[0], q1 = rp[1], q2 = rp[2];
-            const bool contrib = bwd_pair2<LOD, DEPTH>(p2, pos, q0, q1, q2, null_thr, v);
-            if (!__any_sync(0xffffffffu, contrib)) continue;
+            if (!bwd_pair2<LOD, DEPTH>(p2, pos, q0, q1, q2, null_thr, v)) continue;  // the same answer in every lane
             int slot;
             const float total = warp_reduce10(v, lane, slot);
             if (slot >= 0 && (DEPTH || slot < 9) && total != 0.f) atomicAdd(accp + slot, total);
