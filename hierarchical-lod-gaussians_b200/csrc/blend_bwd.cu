@@ -69,8 +69,8 @@ __device__ __forceinline__ float warp_reduce10(const float (&v)[NV], unsigned la
 // ---- packed FP32 (sm_100 FFMA2 / FMUL2 / FADD2): the thread's two pixels ride in the halves of one 64-bit register pair, so
 // the arithmetic of a (splat, pixel pair) costs one issue slot instead of two (the kernel is issue-bound, not FP-pipe-bound).
 // Splat constants enter as broadcast operands (mov.b64 {x,x} folds into the instruction). ptxas contracts mul+add pairs of
-// packed operations even with .rn; harmless here (gradients are held to 1e-3, not bit-exact), which is why the FORWARD
-// kernel, whose rounding is pinned, keeps scalar instructions.
+// packed operations even with .rn; harmless here (gradients are held to 1e-3, not bit-exact) — the FORWARD kernel, whose
+// rounding is pinned, restricts itself to the packed forms ptxas cannot re-contract (see blend_fwd.cu).
 // Replay state of the thread's two pixels (lo = upper pixel, hi = the one below it).
 struct BwdPix2 {
     f2 npy, T, T_final, last_alpha, ar0, ar1, ar2, ar_invd, g0, g1, g2, gd, nbg_dot;
