@@ -129,6 +129,19 @@ def get_spt_cut_cuda(number_of_SPTs, gaussian_indices, SPT_starts, SPT_max, SPT_
     return cut, counts
 
 
+def get_morton_indices(xyz, min, max, code):  # noqa: A002  (the reference's argument names)
+    """GH/torch/torch_interface.cpp GetMortonCode: writes the 63-bit Morton code of every row of `xyz` into `code` (i64[P], CUDA)."""
+    if xyz.device.type != "cuda" or code.device.type != "cuda":
+        raise RuntimeError("get_morton_indices needs CUDA tensors (there is no CPU path)")
+    if code.dtype != torch.int64 or not code.is_contiguous() or code.numel() < xyz.size(0):
+        raise RuntimeError("get_morton_indices: code must be a contiguous int64 tensor with one entry per point")
+    dev = xyz.device
+    x = xyz.detach().to(torch.float32).contiguous()
+    mn = min.detach().to(device=dev, dtype=torch.float32).contiguous()
+    mx = max.detach().to(device=dev, dtype=torch.float32).contiguous()
+    check(lib.lodgs_get_morton_codes(ptr(x), ptr(mn), ptr(mx), code.data_ptr(), x.size(0), current_stream()))
+
+
 def load_hierarchy(filename):
     """-> (pos[P,3], shs[P,16,3], alpha[P,1], scales[P,3], rot[P,4], nodes[N,7] i32, boxes[N,2,4]) CPU tensors."""
     P, N = C.c_int32(0), C.c_int32(0)

@@ -71,6 +71,7 @@ _SIGS = {
     "lodgs_spt_cut_workspace_bytes": (_sz, [_i]),
     "lodgs_spt_cut_count": (_i, [_i, _p, _i, _p, _p, _p, _p, _p, _p, _p, _sz, _p, _p]),
     "lodgs_spt_cut_write": (_i, [_i, _p, _i, _p, _p, _p, _p, _p, _p, _i, _p]),
+    "lodgs_get_morton_codes": (_i, [_p, _p, _p, _p, _i, _p]),
     "lodgs_compute_relocation": (_i, [_i, _p, _p, _p, _p, _i, _p, _p, _p]),
     "lodgs_geom_layout": (_i, [_i, _p]),
     "lodgs_binning_layout": (_i, [_i, _p]),

@@ -109,6 +109,11 @@ int lodgs_spt_cut_write(int S, const int32_t* gaussian_indices, int n_entries, c
                         const int32_t* SPT_indices, const float* SPT_distances, const void* ws, int32_t* cut_out, int capacity,
                         void* stream);
 
+/* Morton codes. Replaces MORTON::getMortonCode (GH/morton.cu:9-60) as bound by gaussian_hierarchy._C.get_morton_indices
+ * (torch_interface.cpp GetMortonCode; scene/gaussian_model.py:574). xyz f32[P,3]; min3/max3 = 3 floats each ON THE DEVICE;
+ * codes i64[P]: bits 0..20 of trunc((c - min) / (max - min) * 2^21) per axis, interleaved x, y, z from bit 0. */
+int lodgs_get_morton_codes(const float* xyz, const float* min3_dev, const float* max3_dev, int64_t* codes, int P, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Hierarchy file I/O (host only). Replaces HierarchyLoader::load (GH/hierarchy_loader.cpp:26-128)
  * behind gaussian_hierarchy._C.load_hierarchy (torch_interface.cpp:9-40), and HierarchyWriter::write

@@ -10,6 +10,7 @@
 #include <float.h>
 #include <math.h>
 #include <stdlib.h>
+#include <stdint.h>
 
 static float box_size(const float* b, const float* v) {
     const float* mn = b;
@@ -200,4 +201,32 @@ int orc_get_spt_cut(int S, const int32_t* gaussian_indices, int n_entries, const
     for (int i = 0; i < S; i++) { if (counts_prefix) counts_prefix[i] = run; run += counts[i]; }
     free(sizes); free(prefix); free(counts);
     return K;
+}
+
+/* ---- Morton codes: getMortonCodeCUDA (GH/morton.cu:9-42), thread body restated; the float -> int64 conversion follows the
+ * device's cvt.rzi.s64.f32 (NaN -> 0, saturating) instead of C's undefined behaviour out of range. */
+static int64_t f2ll_rz(float v) {
+    if (v != v) return 0;
+    if (v >= 9223372036854775808.0f) return INT64_MAX;
+    if (v <= -9223372036854775808.0f) return INT64_MIN;
+    return (int64_t)v;
+}
+
+void orc_get_morton_codes(const float* xyz, const float* mn, const float* mx, int64_t* codes, int P) {
+    float box[3] = {mx[0] - mn[0], mx[1] - mn[1], mx[2] - mn[2]};
+    for (int idx = 0; idx < P; idx++) {
+        int64_t q[3];
+        for (int c = 0; c < 3; c++) {
+            float v = (xyz[3 * (long)idx + c] - mn[c]) / box[c];
+            v = v * (float)(1 << 21);
+            q[c] = f2ll_rz(v);
+        }
+        int64_t code = 0;
+        for (int i = 0; i < 21; ++i) {
+            code = code | (q[0] >> i & 1) << (3 * i);
+            code = code | (q[1] >> i & 1) << (3 * i + 1);
+            code = code | (q[2] >> i & 1) << (3 * i + 2);
+        }
+        codes[idx] = code;
+    }
 }

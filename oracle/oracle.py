@@ -44,6 +44,7 @@ def lib():
         _lib.orc_get_interpolation_weights_dynamic.argtypes = [_ip, C.c_int, C.c_float, _ip, _fp, _fp, _fp, _fp, _ip]
         _lib.orc_get_spt_cut.restype = C.c_int
         _lib.orc_get_spt_cut.argtypes = [C.c_int, _ip, C.c_int, _ip, _fp, _fp, _ip, _fp, _ip, _ip, _ip]
+        _lib.orc_get_morton_codes.argtypes = [_fp, _fp, _fp, C.POINTER(C.c_int64), C.c_int]
         _lib.orc_forward.restype = C.c_int
         _lib.orc_forward.argtypes = [C.POINTER(Scene), C.POINTER(State)]
         _lib.orc_backward.argtypes = [C.POINTER(Scene), C.POINTER(State)] + [_fp] * 12
@@ -113,6 +114,14 @@ def get_spt_cut(gaussian_indices, SPT_starts, SPT_max, SPT_min, SPT_indices, SPT
     counts = np.zeros(S, np.int32)
     K = lib().orc_get_spt_cut(S, _i(gi), n, _i(st), _f(mx), _f(mn), _i(si), _f(sd), _i(cut), _i(counts), _i(pos))
     return cut[:K].copy(), counts
+
+
+def get_morton_codes(xyz, mn, mx):
+    """MORTON::getMortonCode restated on numpy arrays -> i64[P]."""
+    x, lo, hi = _c(xyz, np.float32), _c(mn, np.float32), _c(mx, np.float32)
+    codes = np.zeros(x.shape[0], np.int64)
+    lib().orc_get_morton_codes(_f(x), _f(lo), _f(hi), codes.ctypes.data_as(C.POINTER(C.c_int64)), x.shape[0])
+    return codes
 
 
 def _scene(sc, cam, bg, indices, parent_indices, ts, kids, do_depth, colors, keep):

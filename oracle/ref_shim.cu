@@ -13,6 +13,7 @@
 #include "cuda_rasterizer/rasterizer.h"
 #include "cuda_rasterizer/rasterizer_impl.h"
 #include "runtime_switching.h"
+#include "morton.h"
 
 namespace {
 struct Buf {
@@ -123,6 +124,8 @@ REF_API int ref_get_spt_cut_fetch(int K, int S, int* cut_out, int* counts_out) {
     g_spt_cut = g_spt_counts = nullptr;
     return (int)e;
 }
+
+REF_API void ref_get_morton_code(float* xyz, float* mn, float* mx, int64_t* codes, int P) { MORTON::getMortonCode(xyz, mn, mx, codes, P); }
 
 REF_API int ref_copy_d2d(void* dst, const void* src, size_t nbytes) {
     cudaError_t e = cudaMemcpy(dst, src, nbytes, cudaMemcpyDeviceToDevice);

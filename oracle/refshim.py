@@ -39,6 +39,8 @@ def lib():
         _lib.ref_expand_to_size_dynamic.argtypes = [_i, _f, _p, _p, _p, _p, _f, _f, _f, _p, _p, _p]
         _lib.ref_get_ts_indexed_dynamic.restype = None
         _lib.ref_get_ts_indexed_dynamic.argtypes = [_i, _p, _f, _p, _p, _p, _f, _f, _f, _f, _f, _f, _p, _p, _p]
+        _lib.ref_get_morton_code.restype = None
+        _lib.ref_get_morton_code.argtypes = [_p, _p, _p, _p, _i]
         _lib.ref_get_spt_cut_run.restype = _i
         _lib.ref_get_spt_cut_run.argtypes = [_i, _p, _p, _p, _p, _p, _p]
         _lib.ref_get_spt_cut_fetch.restype = _i

@@ -132,3 +132,13 @@ def spt_cut_model(ids, starts, spt_max, spt_min, sel, dist):
     prefix = np.zeros(S, np.int32)
     prefix[1:] = np.cumsum(counts)[:-1]
     return np.array(cut, np.int32), prefix
+
+
+def make_morton_case(P=20000, seed=31, degenerate=False):
+    """Positions + (min, max) as scene/gaussian_model.py:574 passes them (extent of the points); the extreme points sit exactly on
+    the box faces (their scaled coordinate is 2^21, bit 21, which the code drops). `degenerate`: all z equal -> 0/0 on that axis."""
+    rng = np.random.default_rng(seed)
+    xyz = (rng.normal(0, 1, (P, 3)) * np.array([30.0, 12.0, 3.0])).astype(np.float32)
+    if degenerate:
+        xyz[:, 2] = 1.5
+    return xyz, xyz.min(0), xyz.max(0)

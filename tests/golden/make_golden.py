@@ -87,3 +87,16 @@ for name in cases.SPT_CASES:
     res[name + "_cut"], res[name + "_counts"] = cut.cpu().numpy(), counts.cpu().numpy()
     print("spt", name, "K", cut.numel())
 np.savez_compressed(os.path.join(OUT, "cut_spt.npz"), **res)
+
+# ---- Morton codes (MORTON::getMortonCode)
+res = {}
+for name, deg in (("plain", False), ("flat_z", True)):
+    xyz, mn, mx = cases.make_morton_case(degenerate=deg)
+    t = [torch.from_numpy(a).cuda() for a in (xyz, mn, mx)]
+    codes = torch.zeros(xyz.shape[0], dtype=torch.int64, device="cuda")
+    torch.cuda.synchronize()
+    L.ref_get_morton_code(t[0].data_ptr(), t[1].data_ptr(), t[2].data_ptr(), codes.data_ptr(), xyz.shape[0])
+    torch.cuda.synchronize()
+    res[name] = codes.cpu().numpy()
+    print("morton", name, int(codes.max()))
+np.savez_compressed(os.path.join(OUT, "morton.npz"), **res)

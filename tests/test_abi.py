@@ -140,6 +140,7 @@ def test_plugin_surface_matches_reference_names():
         "indices", "size", "nodes", "positions", "scales", "viewpoint", "viewdir", "ts", "num_kids"]
     assert list(inspect.signature(ghc.get_spt_cut_cuda).parameters) == [
         "number_of_SPTs", "gaussian_indices", "SPT_starts", "SPT_max", "SPT_min", "SPT_indices", "SPT_distances"]
+    assert list(inspect.signature(ghc.get_morton_indices).parameters) == ["xyz", "min", "max", "code"]
     from lodgs.optim import Adam
     assert list(inspect.signature(Adam.step).parameters)[:2] == ["self", "relevant"]
     r = d.GaussianRasterizer(None)

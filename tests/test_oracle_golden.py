@@ -98,3 +98,11 @@ def test_spt_cut_oracle_matches_reference_and_window_model():
         if name != "large":
             m_cut, m_counts = cases.spt_cut_model(*arrs)
             assert np.array_equal(cut, m_cut) and np.array_equal(counts, m_counts), name
+
+
+def test_morton_oracle_matches_reference():
+    """getMortonCodeCUDA restatement vs the reference kernel's outputs (morton.npz), including the 0/0 axis."""
+    g = np.load(os.path.join(GOLD, "morton.npz"))
+    for name, deg in (("plain", False), ("flat_z", True)):
+        xyz, mn, mx = cases.make_morton_case(degenerate=deg)
+        assert np.array_equal(orc.get_morton_codes(xyz, mn, mx), g[name]), name
