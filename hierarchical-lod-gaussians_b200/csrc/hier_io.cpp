@@ -169,3 +169,62 @@ extern "C" int lodgs_hier_write(const char* filename, int P, int N, const float*
     if (!ok) { lodgs::set_error("lodgs_hier_write: short write"); return LODGS_E_IO; }
     return LODGS_OK;
 }
+
+// ---- dynamic hierarchy files (the format this fork's creator writes and scene/gaussian_model.py create_from_hier loads).
+// HierarchyLoader::loadDynamic (GH/hierarchy_loader.cpp:129-189) / HierarchyWriter::writeDynamic (GH/hierarchy_writer.cpp:122-168):
+// int P, int sh_degree, pos[P,3], rot[P,4], log-scales[P,3], opacities[P], SH[P, 3*(deg+1)^2] packed, int N, HierarchyNode[N]
+// (6 x i32). The reference loader reads the node count but then loads exactly P nodes (one node per Gaussian); so does this one,
+// and the probe reports both numbers.
+namespace {
+inline int sh_floats(int degree) { return 3 * (degree + 1) * (degree + 1); }
+}  // namespace
+
+extern "C" int lodgs_dhier_probe(const char* filename, int32_t* P, int32_t* sh_degree, int32_t* N_in_file) {
+    if (!filename || !P || !sh_degree) { lodgs::set_error("lodgs_dhier_probe: null argument"); return LODGS_E_ARG; }
+    File in(filename, "rb");
+    if (!in.f) { lodgs::set_error("File not found!"); return LODGS_E_IO; }
+    int32_t p = 0, deg = 0, n = 0;
+    if (!in.rd(&p, 4) || !in.rd(&deg, 4)) { lodgs::set_error("lodgs_dhier_probe: truncated header in %s", filename); return LODGS_E_IO; }
+    if (p < 0 || deg < 0 || deg > 3) { lodgs::set_error("lodgs_dhier_probe: bad header in %s (P %d, SH degree %d)", filename, p, deg); return LODGS_E_IO; }
+    const long long body = (long long)p * (12 + 16 + 12 + 4 + 4ll * sh_floats(deg));
+    if (fseeko(in.f, (off_t)body, SEEK_CUR) != 0 || !in.rd(&n, 4)) {
+        lodgs::set_error("lodgs_dhier_probe: truncated file %s", filename);
+        return LODGS_E_IO;
+    }
+    *P = p;
+    *sh_degree = deg;
+    if (N_in_file) *N_in_file = n;
+    return LODGS_OK;
+}
+
+extern "C" int lodgs_dhier_load(const char* filename, float* pos, float* shs, float* alpha, float* scales, float* rot, int32_t* nodes) {
+    if (!filename) { lodgs::set_error("lodgs_dhier_load: null argument"); return LODGS_E_ARG; }
+    File in(filename, "rb");
+    if (!in.f) { lodgs::set_error("File not found!"); return LODGS_E_IO; }
+    int32_t p = 0, deg = 0, n = 0;
+    if (!in.rd(&p, 4) || !in.rd(&deg, 4) || p < 0 || deg < 0 || deg > 3) { lodgs::set_error("lodgs_dhier_load: bad header in %s", filename); return LODGS_E_IO; }
+    const size_t P = (size_t)p;
+    if (P && (!pos || !shs || !alpha || !scales || !rot || !nodes)) { lodgs::set_error("lodgs_dhier_load: null output"); return LODGS_E_ARG; }
+    if (!in.rd(pos, P * 12) || !in.rd(rot, P * 16) || !in.rd(scales, P * 12) || !in.rd(alpha, P * 4) ||
+        !in.rd(shs, P * 4 * (size_t)sh_floats(deg)) || !in.rd(&n, 4) || !in.rd(nodes, P * 24)) {
+        lodgs::set_error("lodgs_dhier_load: truncated file %s", filename);
+        return LODGS_E_IO;
+    }
+    return LODGS_OK;
+}
+
+extern "C" int lodgs_dhier_write(const char* filename, int P, int N, int sh_degree, const float* pos, const float* shs, const float* alpha,
+                                 const float* scales, const float* rot, const int32_t* nodes) {
+    if (!filename || P < 0 || N < 0 || sh_degree < 0 || sh_degree > 3) { lodgs::set_error("lodgs_dhier_write: bad argument"); return LODGS_E_ARG; }
+    if ((P && (!pos || !shs || !alpha || !scales || !rot)) || (N && !nodes)) { lodgs::set_error("lodgs_dhier_write: null input"); return LODGS_E_ARG; }
+    File out(filename, "wb");
+    if (!out.f) { lodgs::set_error("File not created!"); return LODGS_E_IO; }
+    const int32_t p = P, n = N, deg = sh_degree;
+    const size_t Ps = (size_t)P;
+    if (!out.wr(&p, 4) || !out.wr(&deg, 4) || !out.wr(pos, Ps * 12) || !out.wr(rot, Ps * 16) || !out.wr(scales, Ps * 12) ||
+        !out.wr(alpha, Ps * 4) || !out.wr(shs, Ps * 4 * (size_t)sh_floats(deg)) || !out.wr(&n, 4) || !out.wr(nodes, (size_t)N * 24)) {
+        lodgs::set_error("lodgs_dhier_write: write failed for %s", filename);
+        return LODGS_E_IO;
+    }
+    return LODGS_OK;
+}

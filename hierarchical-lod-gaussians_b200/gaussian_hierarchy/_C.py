@@ -165,3 +165,31 @@ def write_hierarchy(filename, pos, shs, opacities, log_scales, rotations, nodes,
     check(lib.lodgs_hier_write(str(filename).encode(), t[0].size(0), nodes_c.size(0), t[0].data_ptr(), t[1].data_ptr(),
                                t[2].data_ptr(), t[3].data_ptr(), t[4].data_ptr(), nodes_c.data_ptr(), boxes_c.data_ptr(),
                                1 if compressed else 0))
+
+
+def load_dynamic_hierarchy(filename):
+    """GH/torch/torch_interface.cpp:43-75 (LoadDynamicHierarchy) -> (pos[P,3], shs[P,(deg+1)^2,3], alpha[P,1], scales[P,3], rot[P,4],
+    nodes[P,6] i32) CPU tensors; one node per Gaussian, as the reference loads them."""
+    P, deg, N = C.c_int32(0), C.c_int32(0), C.c_int32(0)
+    fn = str(filename).encode()
+    try:
+        check(lib.lodgs_dhier_probe(fn, C.addressof(P), C.addressof(deg), C.addressof(N)))
+    except LodgsError as e:
+        raise RuntimeError(str(e).split(": ", 1)[-1])
+    P, deg = P.value, deg.value
+    pos, shs = torch.empty(P, 3), torch.empty(P, (deg + 1) ** 2, 3)
+    alpha, scales, rot = torch.empty(P, 1), torch.empty(P, 3), torch.empty(P, 4)
+    nodes = torch.empty(P, 6, dtype=torch.int32)
+    check(lib.lodgs_dhier_load(fn, pos.data_ptr(), shs.data_ptr(), alpha.data_ptr(), scales.data_ptr(), rot.data_ptr(), nodes.data_ptr()))
+    return pos, shs, alpha, scales, rot, nodes
+
+
+def write_dynamic_hierarchy(filename, pos, shs, opacities, log_scales, rotations, nodes, SH_degree):
+    """GH/torch/torch_interface.cpp:107-134 (WriteDynamicHierarchy): tensors on any device; shs holds 3*(SH_degree+1)^2 floats per row."""
+    t = [x.detach().to("cpu", torch.float32).contiguous() for x in (pos, shs, opacities, log_scales, rotations)]
+    nodes_c = nodes.detach().to("cpu", torch.int32).contiguous()
+    P, deg = t[0].size(0), int(SH_degree)
+    if not 0 <= deg <= 3 or t[1].numel() != P * 3 * (deg + 1) ** 2:
+        raise RuntimeError("write_dynamic_hierarchy: shs must hold 3*(SH_degree+1)^2 floats per Gaussian")
+    check(lib.lodgs_dhier_write(str(filename).encode(), P, nodes_c.size(0), deg, t[0].data_ptr(), t[1].data_ptr(), t[2].data_ptr(),
+                                t[3].data_ptr(), t[4].data_ptr(), nodes_c.data_ptr()))

@@ -128,6 +128,17 @@ int lodgs_hier_write(const char* filename, int P, int N, const float* pos, const
                      const float* scales, const float* rot, const int32_t* nodes, const float* boxes,
                      int compressed);
 
+/* Dynamic hierarchy files (host only). Replaces HierarchyLoader::loadDynamic (GH/hierarchy_loader.cpp:129-189) behind
+ * gaussian_hierarchy._C.load_dynamic_hierarchy (torch_interface.cpp:43-75) and HierarchyWriter::writeDynamic
+ * (GH/hierarchy_writer.cpp:122-168) behind write_dynamic_hierarchy (torch_interface.cpp:107-134). Layout: int P, int sh_degree,
+ * pos[P,3], rot[P,4], log-scales[P,3], opacities[P], SH[P, 3*(deg+1)^2], int N, HierarchyNode[N] (6 x i32). As in the reference
+ * the loader returns exactly P nodes whatever N says; lodgs_dhier_probe reports P, the SH degree and the N stored in the file,
+ * the caller allocates pos[P,3] shs[P,(deg+1)^2,3] alpha[P] scales[P,3] rot[P,4] nodes[P,6] and calls lodgs_dhier_load. */
+int lodgs_dhier_probe(const char* filename, int32_t* P, int32_t* sh_degree, int32_t* N_in_file);
+int lodgs_dhier_load(const char* filename, float* pos, float* shs, float* alpha, float* scales, float* rot, int32_t* nodes);
+int lodgs_dhier_write(const char* filename, int P, int N, int sh_degree, const float* pos, const float* shs, const float* alpha,
+                      const float* scales, const float* rot, const int32_t* nodes);
+
 /* ------------------------------------------------------------------------------------------------
  * Rasterizer. Replaces CudaRasterizer::Rasterizer::forward / backward / markVisible
  * (HR/cuda_rasterizer/rasterizer.h:20-109, rasterizer_impl.cu:203-517) as bound by

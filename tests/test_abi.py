@@ -100,6 +100,41 @@ def test_hier_roundtrip_half_matches_numpy_float16(tmp_path):
             assert torch.equal(got, h(want))
 
 
+@pytest.mark.parametrize("deg", [0, 1, 2, 3])
+def test_dynamic_hier_layout_and_roundtrip(tmp_path, deg):
+    """.dhier byte layout (GH/hierarchy_writer.cpp:122-168) written by hand with numpy, read by the loader; then writer -> loader."""
+    P, M = 29, (deg + 1) ** 2
+    g = torch.Generator().manual_seed(deg)
+    pos, rot, sca = torch.randn(P, 3, generator=g), torch.randn(P, 4, generator=g), torch.randn(P, 3, generator=g)
+    a, shs = torch.rand(P, 1, generator=g), torch.randn(P, M, 3, generator=g)
+    nodes = torch.randint(-1, 30000, (P, 6), generator=g, dtype=torch.int32)
+    f = tmp_path / "hand.dhier"
+    with open(f, "wb") as fh:
+        np.array([P, deg], np.int32).tofile(fh)
+        for t in (pos, rot, sca, a, shs):
+            t.numpy().tofile(fh)
+        np.array([P + 5], np.int32).tofile(fh)   # the stored node count is ignored by the reference loader: it reads P nodes
+        nodes.numpy().tofile(fh)
+    out = gh.load_dynamic_hierarchy(str(f))
+    for x, y in zip(out, (pos, shs, a, sca, rot, nodes)):
+        assert x.shape == y.shape and x.dtype == y.dtype and torch.equal(x, y)
+    f2 = tmp_path / "w.dhier"
+    gh.write_dynamic_hierarchy(str(f2), pos, shs, a, sca, rot, nodes, deg)
+    assert os.path.getsize(f2) == 8 + P * (12 + 16 + 12 + 4 + 12 * M) + 4 + P * 24
+    with open(f, "rb") as fa, open(f2, "rb") as fb:
+        ba, bb = bytearray(fa.read()), bytearray(fb.read())
+    off = 8 + P * (44 + 12 * M)
+    assert ba[:off] == bb[:off] and ba[off + 4:] == bb[off + 4:] and np.frombuffer(bytes(bb[off:off + 4]), np.int32)[0] == P
+    with pytest.raises(RuntimeError, match="File not found"):
+        gh.load_dynamic_hierarchy("/nonexistent/x.dhier")
+    with pytest.raises(RuntimeError, match="shs must hold"):
+        gh.write_dynamic_hierarchy(str(f2), pos, shs[:, :1] if deg else torch.zeros(P, 4, 3), a, sca, rot, nodes, deg)
+    with open(tmp_path / "short.dhier", "wb") as fh:
+        fh.write(bytes(ba[:off - 7]))
+    with pytest.raises(RuntimeError, match="truncated"):
+        gh.load_dynamic_hierarchy(str(tmp_path / "short.dhier"))
+
+
 def test_load_missing_file_raises_like_reference():
     with pytest.raises(RuntimeError, match="File not found"):
         gh.load_hierarchy("/nonexistent/x.hier")
@@ -141,6 +176,9 @@ def test_plugin_surface_matches_reference_names():
     assert list(inspect.signature(ghc.get_spt_cut_cuda).parameters) == [
         "number_of_SPTs", "gaussian_indices", "SPT_starts", "SPT_max", "SPT_min", "SPT_indices", "SPT_distances"]
     assert list(inspect.signature(ghc.get_morton_indices).parameters) == ["xyz", "min", "max", "code"]
+    assert list(inspect.signature(ghc.load_dynamic_hierarchy).parameters) == ["filename"]
+    assert list(inspect.signature(ghc.write_dynamic_hierarchy).parameters) == [
+        "filename", "pos", "shs", "opacities", "log_scales", "rotations", "nodes", "SH_degree"]
     from lodgs.optim import Adam
     assert list(inspect.signature(Adam.step).parameters)[:2] == ["self", "relevant"]
     r = d.GaussianRasterizer(None)
