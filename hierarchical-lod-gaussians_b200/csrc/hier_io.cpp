@@ -228,3 +228,29 @@ extern "C" int lodgs_dhier_write(const char* filename, int P, int N, int sh_degr
     }
     return LODGS_OK;
 }
+
+// ---- depth-target cut on the host. Replaces Traversal::expandToTarget (GH/traversal.cpp:15-39, bound as expand_to_target,
+// torch_interface.cpp:136-142): pre-order walk from node 0; every visited node contributes its leaf Gaussians, a node at
+// depth <= target also its merged Gaussians and is not descended. The recursion is unrolled on an explicit stack (children
+// pushed in reverse so they pop in id order). Two-call use: out = NULL returns the count only.
+extern "C" int lodgs_expand_to_target(const int32_t* nodes, int N, int target, int32_t* out, int64_t capacity, int64_t* count) {
+    if (!nodes || N <= 0 || !count) { lodgs::set_error("lodgs_expand_to_target: bad argument"); return LODGS_E_ARG; }
+    std::vector<int32_t> stack(1, 0);
+    int64_t n = 0;
+    while (!stack.empty()) {
+        const int32_t id = stack.back();
+        stack.pop_back();
+        if (id < 0 || id >= N) { lodgs::set_error("lodgs_expand_to_target: node id %d outside [0, %d)", id, N); return LODGS_E_ARG; }
+        const int32_t* nd = nodes + 7 * (size_t)id;  // depth parent start count_leafs count_merged start_children count_children
+        int64_t take = nd[3];
+        const bool stop = nd[0] <= target;
+        if (stop) take += nd[4];
+        for (int64_t i = 0; i < take; i++, n++)
+            if (out && n < capacity) out[n] = nd[2] + (int32_t)i;
+        if (!stop)
+            for (int32_t c = nd[6] - 1; c >= 0; c--) stack.push_back(nd[5] + c);
+    }
+    *count = n;
+    if (out && n > capacity) { lodgs::set_error("lodgs_expand_to_target: %lld entries, capacity %lld", (long long)n, (long long)capacity); return LODGS_E_WORKSPACE; }
+    return LODGS_OK;
+}

@@ -193,3 +193,13 @@ def write_dynamic_hierarchy(filename, pos, shs, opacities, log_scales, rotations
         raise RuntimeError("write_dynamic_hierarchy: shs must hold 3*(SH_degree+1)^2 floats per Gaussian")
     check(lib.lodgs_dhier_write(str(filename).encode(), P, nodes_c.size(0), deg, t[0].data_ptr(), t[1].data_ptr(), t[2].data_ptr(),
                                 t[3].data_ptr(), t[4].data_ptr(), nodes_c.data_ptr()))
+
+
+def expand_to_target(nodes, target):
+    """GH/torch/torch_interface.cpp:136-142 (ExpandToTarget): depth-target cut on the host -> i32 CPU tensor of Gaussian ids."""
+    n = nodes.detach().to("cpu", torch.int32).contiguous()
+    count = C.c_int64(0)
+    check(lib.lodgs_expand_to_target(n.data_ptr(), n.size(0), int(target), None, 0, C.addressof(count)))
+    out = torch.empty(count.value, dtype=torch.int32)
+    check(lib.lodgs_expand_to_target(n.data_ptr(), n.size(0), int(target), out.data_ptr(), out.numel(), C.addressof(count)))
+    return out

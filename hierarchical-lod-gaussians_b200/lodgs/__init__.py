@@ -55,6 +55,7 @@ _SIGS = {
     "lodgs_hier_probe": (_i, [C.c_char_p, _p, _p]),
     "lodgs_hier_load": (_i, [C.c_char_p, _p, _p, _p, _p, _p, _p, _p]),
     "lodgs_hier_write": (_i, [C.c_char_p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _i]),
+    "lodgs_expand_to_target": (_i, [_p, _i, _i, _p, C.c_int64, _p]),
     "lodgs_dhier_probe": (_i, [C.c_char_p, _p, _p, _p]),
     "lodgs_dhier_load": (_i, [C.c_char_p, _p, _p, _p, _p, _p, _p]),
     "lodgs_dhier_write": (_i, [C.c_char_p, _i, _i, _i, _p, _p, _p, _p, _p, _p]),

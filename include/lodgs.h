@@ -139,6 +139,12 @@ int lodgs_dhier_load(const char* filename, float* pos, float* shs, float* alpha,
 int lodgs_dhier_write(const char* filename, int P, int N, int sh_degree, const float* pos, const float* shs, const float* alpha,
                       const float* scales, const float* rot, const int32_t* nodes);
 
+/* Depth-target cut (host only). Replaces Traversal::expandToTarget (GH/traversal.cpp:15-39) behind
+ * gaussian_hierarchy._C.expand_to_target (torch_interface.cpp:136-142): pre-order walk of nodes[N,7] from node 0, Gaussian ids
+ * of the leaves of every visited node plus the merged Gaussians of nodes at depth <= target (which are not descended).
+ * out = NULL: only *count is produced. */
+int lodgs_expand_to_target(const int32_t* nodes, int N, int target, int32_t* out, int64_t capacity, int64_t* count);
+
 /* ------------------------------------------------------------------------------------------------
  * Rasterizer. Replaces CudaRasterizer::Rasterizer::forward / backward / markVisible
  * (HR/cuda_rasterizer/rasterizer.h:20-109, rasterizer_impl.cu:203-517) as bound by

@@ -230,3 +230,20 @@ void orc_get_morton_codes(const float* xyz, const float* mn, const float* mx, in
         codes[idx] = code;
     }
 }
+
+/* ---- depth-target cut: recExpand / Traversal::expandToTarget (GH/traversal.cpp:15-39) restated with the same recursion. */
+static void orc_rec_expand(int node_id, const int32_t* nodes, int32_t* out, long* n, int target) {
+    const int32_t* node = nodes + 7 * (long)node_id;
+    for (int i = 0; i < node[3]; i++) { if (out) out[*n] = node[2] + i; (*n)++; }
+    if (node[0] <= target) {
+        for (int i = 0; i < node[4]; i++) { if (out) out[*n] = node[2] + node[3] + i; (*n)++; }
+    } else {
+        for (int i = 0; i < node[6]; i++) orc_rec_expand(node[5] + i, nodes, out, n, target);
+    }
+}
+
+long orc_expand_to_target(const int32_t* nodes, int target, int32_t* out) {
+    long n = 0;
+    orc_rec_expand(0, nodes, out, &n, target);
+    return n;
+}

@@ -45,6 +45,8 @@ def lib():
         _lib.orc_get_spt_cut.restype = C.c_int
         _lib.orc_get_spt_cut.argtypes = [C.c_int, _ip, C.c_int, _ip, _fp, _fp, _ip, _fp, _ip, _ip, _ip]
         _lib.orc_get_morton_codes.argtypes = [_fp, _fp, _fp, C.POINTER(C.c_int64), C.c_int]
+        _lib.orc_expand_to_target.restype = C.c_long
+        _lib.orc_expand_to_target.argtypes = [_ip, C.c_int, _ip]
         _lib.orc_forward.restype = C.c_int
         _lib.orc_forward.argtypes = [C.POINTER(Scene), C.POINTER(State)]
         _lib.orc_backward.argtypes = [C.POINTER(Scene), C.POINTER(State)] + [_fp] * 12
@@ -122,6 +124,15 @@ def get_morton_codes(xyz, mn, mx):
     codes = np.zeros(x.shape[0], np.int64)
     lib().orc_get_morton_codes(_f(x), _f(lo), _f(hi), codes.ctypes.data_as(C.POINTER(C.c_int64)), x.shape[0])
     return codes
+
+
+def expand_to_target(nodes, target):
+    """Traversal::expandToTarget restated -> i32 Gaussian ids."""
+    n = _c(nodes, np.int32)
+    cnt = lib().orc_expand_to_target(_i(n), int(target), None)
+    out = np.zeros(max(cnt, 1), np.int32)
+    lib().orc_expand_to_target(_i(n), int(target), _i(out))
+    return out[:cnt].copy()
 
 
 def _scene(sc, cam, bg, indices, parent_indices, ts, kids, do_depth, colors, keep):

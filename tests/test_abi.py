@@ -135,6 +135,19 @@ def test_dynamic_hier_layout_and_roundtrip(tmp_path, deg):
         gh.load_dynamic_hierarchy(str(tmp_path / "short.dhier"))
 
 
+def test_expand_to_target_matches_restated_recursion():
+    """Depth-target cut (GH/traversal.cpp:15-39): explicit-stack walk in the library vs the recursion restated in oracle/."""
+    from oracle import oracle as orc
+    import cases
+    nodes, boxes, views = cases.make_cut_case(L=700, seed=3)
+    depths = nodes[:, 0]
+    for target in (-1, 0, 1, int(np.median(depths)), int(depths.max()), int(depths.max()) + 3):
+        mine = gh.expand_to_target(torch.from_numpy(nodes), target)
+        want = orc.expand_to_target(nodes, target)
+        assert mine.dtype == torch.int32 and np.array_equal(mine.numpy(), want), target
+    assert len(orc.expand_to_target(nodes, int(depths.max()) + 3)) == nodes[0, 3] + nodes[0, 4]
+
+
 def test_load_missing_file_raises_like_reference():
     with pytest.raises(RuntimeError, match="File not found"):
         gh.load_hierarchy("/nonexistent/x.hier")
@@ -179,6 +192,7 @@ def test_plugin_surface_matches_reference_names():
     assert list(inspect.signature(ghc.load_dynamic_hierarchy).parameters) == ["filename"]
     assert list(inspect.signature(ghc.write_dynamic_hierarchy).parameters) == [
         "filename", "pos", "shs", "opacities", "log_scales", "rotations", "nodes", "SH_degree"]
+    assert list(inspect.signature(ghc.expand_to_target).parameters) == ["nodes", "target"]
     from lodgs.optim import Adam
     assert list(inspect.signature(Adam.step).parameters)[:2] == ["self", "relevant"]
     r = d.GaussianRasterizer(None)
