@@ -16,9 +16,9 @@
 //   3. keeps an entry when min distance < the slot's distance, counts kept entries per slot, drops kept entries whose gaussian id
 //      is 0 (DeviceSelect::If(!= 0)), and returns the surviving ids in position order plus the exclusive prefix sum of the counts.
 // The output is reproduced entry for entry, including 2.'s shifted window, because train_post.py indexes render lists with the
-// returned counts. The reference spends ~10 cudaMalloc/cudaFree and ~10 device synchronisations per call on it; here it is three
-// launches and one 4-byte read-back: a warp per slot bisects and counts, one block scans the per-slot totals, a warp per slot
-// writes its ids at the scanned offset. An entry index at or past n_entries (possible only for the one-past-the-end probe of a
+// returned counts. The reference spends ~10 cudaMalloc/cudaFree and ~10 device synchronisations per call on it; here it is four
+// launches and one 12-byte read-back: a thread per slot bisects, a warp per slot counts, one block scans the per-slot totals, a
+// warp per slot writes its ids at the scanned offset. An entry index at or past n_entries (possible only for the one-past-the-end probe of a
 // table that ends the arrays, where the reference reads out of bounds) counts as not kept.
 #include "state.cuh"
 
@@ -163,8 +163,8 @@ extern "C" int lodgs_spt_cut_count(int S, const int32_t* gaussian_indices, int n
     SptHeader* hdr = (SptHeader*)ws;
     int32_t* sizes = spt_sizes(ws);
     int32_t* offsets = spt_offsets(ws, S);
-    const SptHeader init = {-1, 0, 0};
-    LODGS_CUDA(cudaMemcpyAsync(hdr, &init, sizeof(init), cudaMemcpyHostToDevice, s));
+    LODGS_CUDA(cudaMemsetAsync(&hdr->last_nonempty, 0xff, sizeof(int), s));  // -1
+    LODGS_CUDA(cudaMemsetAsync(&hdr->total, 0, 2 * sizeof(int), s));
     spt_search_kernel<<<(S + SPT_THREADS - 1) / SPT_THREADS, SPT_THREADS, 0, s>>>(S, SPT_starts, SPT_max, SPT_indices, SPT_distances, sizes, hdr);
     LODGS_LAUNCHED("spt_search_kernel");
     spt_slot_kernel<false><<<(S + SPT_WARPS - 1) / SPT_WARPS, SPT_THREADS, 0, s>>>(S, gaussian_indices, n_entries, SPT_starts, SPT_min, SPT_indices,
