@@ -128,31 +128,43 @@ class OursArm:
         relevant = (self.last[2] > 0).nonzero().reshape(-1)
         self.adam(relevant, grads)
 
-    def step_e2e(self):
-        """One end-to-end step: inputs leave pinned host memory, results land in pinned host memory. Three streams
-        (H2D, compute, D2H) and two buffer slots let step i's copies overlap its neighbours' kernels; every step still
-        moves its own inputs and its own results, and the timed region ends only after the last D2H has landed."""
-        if self.pipe is None:
-            self.pipe = {"h2d": torch.cuda.Stream(), "d2h": torch.cuda.Stream(), "i": 0,
-                         "in": [None, None], "ev_in": [None, None], "ev_free": [None, None], "ev_out": [None, None],
-                         "out": [None, None], "keep": [None, None]}
+    def _enqueue_h2d(self, slot):
+        """Copy one step's inputs from pinned host memory into buffer slot `slot` on the H2D stream."""
         pp = self.pipe
-        slot = pp["i"] & 1
-        pp["i"] += 1
-        comp = torch.cuda.current_stream()
         if pp["in"][slot] is None:
             pp["in"][slot] = ({k: torch.empty_like(self.d[k]) for k in PARAM_KEYS}, torch.empty_like(self.target))
         d, target = pp["in"][slot]
         with torch.cuda.stream(pp["h2d"]):
             if pp["ev_free"][slot] is not None:
-                pp["h2d"].wait_event(pp["ev_free"][slot])       # the kernels of step i-2 have finished reading this slot
+                pp["h2d"].wait_event(pp["ev_free"][slot])       # the kernels of the step that last used this slot have finished
             for k in PARAM_KEYS:
                 d[k].copy_(self.host[k], non_blocking=True)
             target.copy_(self.target_host, non_blocking=True)
-            pp["ev_in"][slot] = pp["h2d"].record_event()
+            pp["ev_in"][slot] = pp["h2d"].record_event(self._ev())
+
+    def step_e2e(self):
+        """One end-to-end step: inputs leave pinned host memory, results land in pinned host memory. Three streams
+        (H2D, compute, D2H) and two buffer slots: while step i computes, the inputs of step i+1 are already being copied
+        into the other slot (a prefetching loader) and the results of step i-1 are on their way back. Every step moves its
+        own inputs and its own results; the timed region ends only after the last D2H AND the last prefetch have landed, so
+        K steps contain K complete input copies."""
+        if self.pipe is None:
+            self.pipe = {"h2d": torch.cuda.Stream(), "d2h": torch.cuda.Stream(), "i": 0, "prefetched": -1,
+                         "in": [None, None], "ev_in": [None, None], "ev_free": [None, None], "ev_out": [None, None],
+                         "out": [None, None], "keep": [None, None]}
+        pp = self.pipe
+        i = pp["i"]
+        slot = i & 1
+        pp["i"] += 1
+        comp = torch.cuda.current_stream()
+        if pp["prefetched"] != i:
+            self._enqueue_h2d(slot)
+        self._enqueue_h2d(slot ^ 1)
+        pp["prefetched"] = i + 1
+        d, target = pp["in"][slot]
         comp.wait_event(pp["ev_in"][slot])
         color, g = self.fwd_bwd(d, target)
-        pp["ev_free"][slot] = comp.record_event()
+        pp["ev_free"][slot] = comp.record_event(self._ev())
         outs = (color, g[3], g[5], g[2], g[6], g[7])  # image, dL_dmeans3D, dL_dsh, dL_dopacity, dL_dscales, dL_drotations
         if pp["out"][slot] is None:
             pp["out"][slot] = [torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in outs]
@@ -164,13 +176,17 @@ class OursArm:
             for h, o in zip(pp["out"][slot], outs):
                 o.record_stream(pp["d2h"])
                 h.copy_(o, non_blocking=True)
-            pp["ev_out"][slot] = pp["d2h"].record_event()
+            pp["ev_out"][slot] = pp["d2h"].record_event(self._ev())
         pp["keep"][slot] = outs
 
+    def _ev(self):
+        return torch.cuda.Event(enable_timing=getattr(self, "ev_timing", False))  # timing only for tools/e2e_timeline.py
+
     def finish_e2e(self):
-        """Called inside the timed region after the last step: the compute stream waits for every outstanding D2H."""
+        """Called inside the timed region after the last step: the compute stream waits for every outstanding D2H and for
+        the input copy prefetched by the last step."""
         if self.pipe is not None:
-            for ev in self.pipe["ev_out"]:
+            for ev in self.pipe["ev_out"] + self.pipe["ev_in"]:
                 if ev is not None:
                     torch.cuda.current_stream().wait_event(ev)
 

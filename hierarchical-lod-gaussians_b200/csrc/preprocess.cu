@@ -261,6 +261,12 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means, cons
     present[i] = !(z <= 0.2f);
 }
 
+// Publishes the instance count into a host-mapped word (see lodgs_forward_preprocess_ex).
+__global__ void publish_count_kernel(const unsigned* __restrict__ count, int32_t* __restrict__ host_word) {
+    *reinterpret_cast<volatile int32_t*>(host_word) = (int32_t)*count;
+    __threadfence_system();
+}
+
 }  // namespace lodgs
 
 using namespace lodgs;
@@ -332,15 +338,21 @@ extern "C" int lodgs_forward_preprocess_ex(int P, int D, int M, int W, int H, co
     LODGS_LAUNCHED("preprocess_fwd_kernel");
     // The count goes back to the host (the caller sizes the binning buffer from it, rasterizer_impl.cu:330-333) while the
     // GPU already orders the Gaussians by depth for the emission stage: the host waits on an event recorded right after
-    // the 4-byte copy, not on the stream.
-    // (the copy lands in a pinned staging word: a copy to pageable memory would block the host until the kernel has run
-    // and the launches below would no longer be queued behind it)
+    // the count is published, not on the stream. The count is published by a one-thread kernel that stores it into a
+    // MAPPED pinned word instead of a 4-byte cudaMemcpyAsync: a device-to-host copy is queued on the D2H copy engine behind
+    // whatever bulk transfer the application has in flight (measured in bench.py's end-to-end pipeline: up to 5 ms behind
+    // the previous step's results), a store over PCIe is not.
     static thread_local cudaEvent_t ev = nullptr;
     static thread_local int32_t* pinned = nullptr;
+    static thread_local int32_t* pinned_dev = nullptr;
     if (num_rendered_host) {
         if (!ev) LODGS_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-        if (!pinned) LODGS_CUDA(cudaHostAlloc((void**)&pinned, sizeof(int32_t), cudaHostAllocDefault));
-        LODGS_CUDA(cudaMemcpyAsync(pinned, &g.hdr->num_rendered, sizeof(int), cudaMemcpyDeviceToHost, s));
+        if (!pinned) {
+            LODGS_CUDA(cudaHostAlloc((void**)&pinned, sizeof(int32_t), cudaHostAllocMapped));
+            LODGS_CUDA(cudaHostGetDevicePointer((void**)&pinned_dev, pinned, 0));
+        }
+        publish_count_kernel<<<1, 1, 0, s>>>(&g.hdr->num_rendered, pinned_dev);
+        LODGS_LAUNCHED("publish_count_kernel");
         LODGS_CUDA(cudaEventRecord(ev, s));
     }
     int rc = sort_pairs32_device(g.depth_keys, nullptr, g.depth_keys_sorted, g.order, g.sort_tmp_k, g.sort_tmp_v, P, 0, 32, g.sort_ws, s, "sort_depth_pass_kernel",
