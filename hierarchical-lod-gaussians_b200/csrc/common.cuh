@@ -16,6 +16,12 @@ void count_launch();
 int check_cuda(cudaError_t e, const char* what);
 void prof_stage_begin(cudaStream_t s);
 void prof_mark(const char* name);
+// Small device->host results (counts the caller sizes buffers from) are published by a store into a mapped pinned word,
+// not by a cudaMemcpy: a device-to-host copy queues on the D2H copy engine behind whatever bulk transfer the application has
+// in flight. publish_words enqueues a one-thread kernel copying n <= 8 ints from `src_dev` and records an event;
+// wait_words blocks the host on that event and returns the host copy (thread-local, valid until the next publish).
+int publish_words(const int32_t* src_dev, int n, cudaStream_t s);
+const int32_t* wait_words();
 
 #define LODGS_CUDA(call)                                              \
     do {                                                              \

@@ -504,9 +504,10 @@ extern "C" int lodgs_expand_to_size(const int32_t* nodes, const float* boxes, in
         LODGS_LAUNCHED("cut_compact_kernel");
     }
     if (count_host) {
-        int h[3];
-        LODGS_CUDA(cudaMemcpyAsync(h, c.hdr, 3 * sizeof(int), cudaMemcpyDeviceToHost, s));
-        LODGS_CUDA(cudaStreamSynchronize(s));
+        const int prc = publish_words(reinterpret_cast<const int32_t*>(c.hdr), 3, s);  // mapped pinned words, not a D2H copy
+        if (prc) return prc;
+        const int32_t* h = wait_words();
+        if (!h) { set_error("lodgs_expand_to_size: waiting for the count failed"); return LODGS_E_CUDA; }
         *count_host = h[0];
         if (h[2]) { set_error("lodgs_expand_to_size: cut has %d entries, output capacity is %d", h[0], capacity); return LODGS_E_WORKSPACE; }
     }

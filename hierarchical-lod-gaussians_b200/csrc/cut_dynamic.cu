@@ -224,9 +224,10 @@ extern "C" int lodgs_expand_to_size_dynamic(const int32_t* nodes, const float* p
                                                     parent_indices, nodes_for_render_indices, capacity, hdr, states);
     LODGS_LAUNCHED("cut_dynamic_kernel");
     if (count_host) {
-        int h[3];
-        LODGS_CUDA(cudaMemcpyAsync(h, hdr, 3 * sizeof(int), cudaMemcpyDeviceToHost, s));
-        LODGS_CUDA(cudaStreamSynchronize(s));
+        const int prc = publish_words(reinterpret_cast<const int32_t*>(hdr), 3, s);  // mapped pinned words, not a D2H copy
+        if (prc) return prc;
+        const int32_t* h = wait_words();
+        if (!h) { set_error("lodgs_expand_to_size_dynamic: waiting for the count failed"); return LODGS_E_CUDA; }
         *count_host = h[0];
         if (h[2]) { set_error("lodgs_expand_to_size_dynamic: cut has %d entries, output capacity is %d", h[0], capacity); return LODGS_E_WORKSPACE; }
     }

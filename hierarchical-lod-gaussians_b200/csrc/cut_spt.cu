@@ -173,10 +173,11 @@ extern "C" int lodgs_spt_cut_count(int S, const int32_t* gaussian_indices, int n
     spt_scan_kernel<<<1, SPT_SCAN_THREADS, 0, s>>>(S, counts_out, offsets, sizes, hdr);
     LODGS_LAUNCHED("spt_scan_kernel");
     if (count_host) {
-        SptHeader h;
-        LODGS_CUDA(cudaMemcpyAsync(&h, hdr, sizeof(h), cudaMemcpyDeviceToHost, s));
-        LODGS_CUDA(cudaStreamSynchronize(s));
-        *count_host = h.total;
+        const int prc = publish_words(reinterpret_cast<const int32_t*>(hdr), 3, s);  // mapped pinned words, not a D2H copy
+        if (prc) return prc;
+        const int32_t* h = wait_words();
+        if (!h) { set_error("lodgs_spt_cut_count: waiting for the count failed"); return LODGS_E_CUDA; }
+        *count_host = h[1];  // SptHeader::total
     }
     return LODGS_OK;
 }

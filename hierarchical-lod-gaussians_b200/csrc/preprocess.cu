@@ -261,12 +261,6 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means, cons
     present[i] = !(z <= 0.2f);
 }
 
-// Publishes the instance count into a host-mapped word (see lodgs_forward_preprocess_ex).
-__global__ void publish_count_kernel(const unsigned* __restrict__ count, int32_t* __restrict__ host_word) {
-    *reinterpret_cast<volatile int32_t*>(host_word) = (int32_t)*count;
-    __threadfence_system();
-}
-
 }  // namespace lodgs
 
 using namespace lodgs;
@@ -339,21 +333,12 @@ extern "C" int lodgs_forward_preprocess_ex(int P, int D, int M, int W, int H, co
     // The count goes back to the host (the caller sizes the binning buffer from it, rasterizer_impl.cu:330-333) while the
     // GPU already orders the Gaussians by depth for the emission stage: the host waits on an event recorded right after
     // the count is published, not on the stream. The count is published by a one-thread kernel that stores it into a
-    // MAPPED pinned word instead of a 4-byte cudaMemcpyAsync: a device-to-host copy is queued on the D2H copy engine behind
-    // whatever bulk transfer the application has in flight (measured in bench.py's end-to-end pipeline: up to 5 ms behind
-    // the previous step's results), a store over PCIe is not.
-    static thread_local cudaEvent_t ev = nullptr;
-    static thread_local int32_t* pinned = nullptr;
-    static thread_local int32_t* pinned_dev = nullptr;
+    // MAPPED pinned word instead of a 4-byte cudaMemcpyAsync (publish_words, common.cuh): a device-to-host copy is queued on the
+    // D2H copy engine behind whatever bulk transfer the application has in flight (measured in bench.py's end-to-end
+    // pipeline: up to 5 ms behind the previous step's results), a store over PCIe is not.
     if (num_rendered_host) {
-        if (!ev) LODGS_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-        if (!pinned) {
-            LODGS_CUDA(cudaHostAlloc((void**)&pinned, sizeof(int32_t), cudaHostAllocMapped));
-            LODGS_CUDA(cudaHostGetDevicePointer((void**)&pinned_dev, pinned, 0));
-        }
-        publish_count_kernel<<<1, 1, 0, s>>>(&g.hdr->num_rendered, pinned_dev);
-        LODGS_LAUNCHED("publish_count_kernel");
-        LODGS_CUDA(cudaEventRecord(ev, s));
+        const int prc = publish_words(reinterpret_cast<const int32_t*>(&g.hdr->num_rendered), 1, s);
+        if (prc) return prc;
     }
     int rc = sort_pairs32_device(g.depth_keys, nullptr, g.depth_keys_sorted, g.order, g.sort_tmp_k, g.sort_tmp_v, P, 0, 32, g.sort_ws, s, "sort_depth_pass_kernel",
                                  "sort_depth_hist_kernel");
@@ -361,8 +346,9 @@ extern "C" int lodgs_forward_preprocess_ex(int P, int D, int M, int W, int H, co
     rc = launch_scan_sorted(P, g, s);
     if (rc) return rc;
     if (num_rendered_host) {
-        LODGS_CUDA(cudaEventSynchronize(ev));
-        *num_rendered_host = *pinned;
+        const int32_t* w = wait_words();
+        if (!w) { set_error("lodgs_forward_preprocess: waiting for the instance count failed"); return LODGS_E_CUDA; }
+        *num_rendered_host = w[0];
     }
     return LODGS_OK;
 }

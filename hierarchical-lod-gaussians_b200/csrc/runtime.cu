@@ -50,6 +50,35 @@ int check_cuda(cudaError_t e, const char* what) {
     return LODGS_E_CUDA;
 }
 
+// ---- mapped pinned result words (see common.cuh)
+constexpr int RESULT_WORDS = 8;
+static thread_local int32_t* t_words = nullptr;
+static thread_local int32_t* t_words_dev = nullptr;
+static thread_local cudaEvent_t t_words_ev = nullptr;
+
+__global__ void publish_words_kernel(const int32_t* __restrict__ src, int32_t* __restrict__ host_words, int n) {
+    for (int i = 0; i < n; i++) reinterpret_cast<volatile int32_t*>(host_words)[i] = src[i];
+    __threadfence_system();
+}
+
+int publish_words(const int32_t* src_dev, int n, cudaStream_t s) {
+    if (n < 1 || n > RESULT_WORDS) { set_error("publish_words: bad word count %d", n); return LODGS_E_ARG; }
+    if (!t_words) {
+        LODGS_CUDA(cudaHostAlloc((void**)&t_words, RESULT_WORDS * sizeof(int32_t), cudaHostAllocMapped | cudaHostAllocPortable));
+        LODGS_CUDA(cudaEventCreateWithFlags(&t_words_ev, cudaEventDisableTiming));
+    }
+    LODGS_CUDA(cudaHostGetDevicePointer((void**)&t_words_dev, t_words, 0));  // per current device
+    publish_words_kernel<<<1, 1, 0, s>>>(src_dev, t_words_dev, n);
+    LODGS_LAUNCHED("publish_words_kernel");
+    LODGS_CUDA(cudaEventRecord(t_words_ev, s));
+    return LODGS_OK;
+}
+
+const int32_t* wait_words() {
+    if (!t_words_ev || cudaEventSynchronize(t_words_ev) != cudaSuccess) return nullptr;
+    return t_words;
+}
+
 }  // namespace lodgs
 
 extern "C" const char* lodgs_last_error(void) { return lodgs::g_err; }
