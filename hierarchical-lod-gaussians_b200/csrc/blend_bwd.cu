@@ -23,6 +23,12 @@ struct BwdSmem {
     unsigned warp_max[BWD_THREADS / 32];
 };
 
+__device__ __forceinline__ float ex2_ftz(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
 __device__ __forceinline__ float rcp_approx(float x) {
     float r;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
@@ -98,9 +104,10 @@ __device__ __forceinline__ bool bwd_pair2(BwdPix2& p, const unsigned pos, const 
         ok1 = ok1 && !(pw1 < q2.z);
     }
     if (!__any_sync(0xffffffffu, ok0 || ok1)) return false;  // warp-uniform: lanes without a contribution ride along with alpha 0
-    // ex2.approx instead of the forward's full-range expf: alpha moves by ~1e-7 relative, far inside the gradient budget
-    const float G0 = __expf(pw0), G1 = __expf(pw1);
-    const f2 G = pk(G0, G1);
+    // ex2.approx.ftz on power * log2(e) instead of the forward's full-range expf: alpha moves by ~1e-7 relative, far inside the
+    // gradient budget; flushing results below 2^-126 is immaterial (alpha < 1/255 is skipped two lines further down)
+    const f2 pl = mul2(power, bc(1.4426950408889634f));
+    const f2 G = pk(ex2_ftz(lo(pl)), ex2_ftz(hi(pl)));
     const f2 ta = mul2(bc(q1.y), G);
     const float ta0 = lo(ta), ta1 = hi(ta);
     const float ma0 = fminf(0.99f, ta0), ma1 = fminf(0.99f, ta1);
