@@ -112,16 +112,28 @@ class OursArm:
         self.tm = {k: torch.zeros_like(v) for k, v in self.tp.items()}
         self.tv = {k: torch.zeros_like(v) for k, v in self.tp.items()}
         self.tstep = 0
+        self._adam_tab = None
 
     def adam(self, relevant, grads):
+        """All parameter tensors in one foreign call (lodgs_adam_step_multi), as lodgs.optim.Adam.step(relevant) issues it."""
+        import ctypes as C
+
         import lodgs
         self.tstep += 1
-        for k in PARAM_KEYS:
-            p, g = self.tp[k], grads[self.GRAD_OF[k]].contiguous()
-            rows = p.size(0)
-            lodgs.check(lodgs.lib.lodgs_adam_step(p.data_ptr(), g.data_ptr(), self.tm[k].data_ptr(), self.tv[k].data_ptr(), relevant.data_ptr(),
-                                                  relevant.numel(), None, rows, p.numel() // rows, self.LR[k], 0.9, 0.999, 1e-15, self.tstep,
-                                                  1, lodgs.current_stream()))
+        n = len(PARAM_KEYS)
+        if getattr(self, "_adam_tab", None) is None:
+            P4 = C.c_void_p * n
+            rows = [self.tp[k].size(0) for k in PARAM_KEYS]
+            self._adam_tab = (P4(*[self.tp[k].data_ptr() for k in PARAM_KEYS]), P4(*[self.tm[k].data_ptr() for k in PARAM_KEYS]),
+                              P4(*[self.tv[k].data_ptr() for k in PARAM_KEYS]), (C.c_int64 * n)(*rows),
+                              (C.c_int32 * n)(*[self.tp[k].numel() // r for k, r in zip(PARAM_KEYS, rows)]),
+                              (C.c_double * n)(*[self.LR[k] for k in PARAM_KEYS]), (C.c_double * n)(*[0.9] * n), (C.c_double * n)(*[0.999] * n),
+                              (C.c_double * n)(*[1e-15] * n))
+        tp, tm, tv, rows, widths, lrs, b1, b2, eps = self._adam_tab
+        gs = [grads[self.GRAD_OF[k]].contiguous() for k in PARAM_KEYS]
+        lodgs.check(lodgs.lib.lodgs_adam_step_multi(n, tp, (C.c_void_p * n)(*[g.data_ptr() for g in gs]), tm, tv, relevant.data_ptr(),
+                                                    relevant.numel(), None, rows, widths, lrs, b1, b2, eps, (C.c_int64 * n)(*[self.tstep] * n), 1,
+                                                    lodgs.current_stream()))
 
     def step_train(self):
         color, grads = self.fwd_bwd(self.tp, self.target)

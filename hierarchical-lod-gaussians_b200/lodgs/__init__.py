@@ -87,6 +87,7 @@ _SIGS = {
     "lodgs_backward_overwrites_dsh": (_i, [_i, _i, _i, _p, _p]),
     "lodgs_backward_overwrites_geometry": (_i, [_i, _i]),
     "lodgs_adam_step": (_i, [_p, _p, _p, _p, _p, _i64, _p, _i64, _i, _d, _d, _d, _d, _i64, _i, _p]),
+    "lodgs_adam_step_multi": (_i, [_i, _p, _p, _p, _p, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p]),
 }
 
 

@@ -9,6 +9,8 @@
 
 There is no eager fallback: parameters must be contiguous float32 CUDA tensors.
 """
+import ctypes as C
+
 import torch
 
 from . import check, current_stream, lib, ptr
@@ -20,7 +22,8 @@ def _require(p, what):
 
 
 class Adam(torch.optim.Adam):
-    """scene/OurAdam.py Adam: `step(relevant)` with an index list of the rows to update."""
+    """scene/OurAdam.py Adam: `step(relevant)` with an index list of the rows to update. All parameter tensors are updated by ONE
+    foreign call (`lodgs_adam_step_multi`); the pointer tables are rebuilt only when a tensor was reallocated."""
 
     @torch.no_grad()
     def step(self, relevant=None, closure=None):
@@ -30,6 +33,7 @@ class Adam(torch.optim.Adam):
                 loss = closure()
         if relevant is not None:
             relevant = relevant.to(torch.int64).contiguous()
+        todo, keep = [], []
         for group in self.param_groups:
             if group.get("amsgrad") or group.get("weight_decay", 0) != 0 or group.get("maximize"):
                 raise NotImplementedError("lodgs.optim.Adam: amsgrad / weight_decay / maximize are not used by the reference's training and "
@@ -47,15 +51,22 @@ class Adam(torch.optim.Adam):
                     state["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
                 state["step"] += 1
                 _require(p, "parameter")
-                grad = p.grad.contiguous()
+                grad = p.grad if p.grad.is_contiguous() else p.grad.contiguous()
+                keep.append(grad)
                 rows = p.size(0)
-                width = p.numel() // max(rows, 1)
-                n_rel = relevant.numel() if relevant is not None else 0
-                if relevant is not None and n_rel == 0:
-                    continue
-                check(lib.lodgs_adam_step(p.data_ptr(), grad.data_ptr(), state["exp_avg"].data_ptr(), state["exp_avg_sq"].data_ptr(),
-                                          ptr(relevant) if relevant is not None else None, n_rel, None, rows, width, float(group["lr"]),
-                                          float(beta1), float(beta2), float(group["eps"]), int(state["step"].item()), 1, current_stream()))
+                todo.append((p.data_ptr(), grad.data_ptr(), state["exp_avg"].data_ptr(), state["exp_avg_sq"].data_ptr(), rows,
+                             p.numel() // max(rows, 1), float(group["lr"]), float(beta1), float(beta2), float(group["eps"]),
+                             int(state["step"].item())))
+        n = len(todo)
+        if n == 0 or (relevant is not None and relevant.numel() == 0):   # the steps above are still counted, as in the reference
+            return loss
+        cols = list(zip(*todo))
+        P4 = C.c_void_p * n
+        check(lib.lodgs_adam_step_multi(n, P4(*cols[0]), P4(*cols[1]), P4(*cols[2]), P4(*cols[3]),
+                                        ptr(relevant) if relevant is not None else None, relevant.numel() if relevant is not None else 0, None,
+                                        (C.c_int64 * n)(*cols[4]), (C.c_int32 * n)(*cols[5]), (C.c_double * n)(*cols[6]),
+                                        (C.c_double * n)(*cols[7]), (C.c_double * n)(*cols[8]), (C.c_double * n)(*cols[9]),
+                                        (C.c_int64 * n)(*cols[10]), 1, current_stream()))
         return loss
 
 

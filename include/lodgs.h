@@ -316,6 +316,13 @@ int lodgs_adam_step(float* param, const float* grad, float* exp_avg, float* exp_
                     int width, double lr, double beta1, double beta2, double eps, int64_t step,
                     int bias_correction, void* stream);
 
+/* The same update for all parameter tensors of one optimizer step in ONE call (launches issued back to back from C): tensor t has
+ * rows[t] rows of widths[t] floats and its own lr / betas / eps / step; the row list or visibility mask is shared. */
+int lodgs_adam_step_multi(int n_tensors, float* const* params, const float* const* grads, float* const* exp_avgs,
+                          float* const* exp_avg_sqs, const int64_t* relevant, int64_t n_relevant, const uint8_t* visible,
+                          const int64_t* rows, const int32_t* widths, const double* lrs, const double* betas1, const double* betas2,
+                          const double* epss, const int64_t* steps, int bias_correction, void* stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif
