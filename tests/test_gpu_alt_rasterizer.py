@@ -176,3 +176,35 @@ def test_index_list_adam_matches_torch():
         st["exp_avg_sq"][mask] = v_before[mask]
     assert float((w.data - ref.data).abs().max()) <= 2e-6
     assert torch.equal(w.data[mask], p0[mask])
+
+
+def test_multi_tensor_adam_step_equals_per_tensor_steps():
+    """lodgs.optim.Adam updates all tensors of a step in one foreign call (lodgs_adam_step_multi): bit-identical to one lodgs_adam_step
+    per tensor, for the six parameter shapes of a Gaussian model, with a row list and dense, over several steps."""
+    import lodgs
+    from lodgs.optim import Adam
+    g = torch.Generator(device="cuda").manual_seed(9)
+    rows = 5000
+    shapes = [(rows, 3), (rows, 1, 3), (rows, 15, 3), (rows, 1), (rows, 3), (rows, 4)]
+    lrs = [1.6e-4, 2.5e-3, 1.25e-4, 2.5e-2, 5e-3, 1e-3]
+    init = [torch.randn(*s, device="cuda", generator=g) for s in shapes]
+    ps = [torch.nn.Parameter(t.clone()) for t in init]
+    opt = Adam([{"params": [p], "lr": lr} for p, lr in zip(ps, lrs)], lr=0.0, eps=1e-15)
+    qs = [t.clone() for t in init]
+    ms, vs = [torch.zeros_like(t) for t in init], [torch.zeros_like(t) for t in init]
+    rel = torch.randperm(rows, device="cuda", generator=g)[:3500].sort().values
+    for it in range(4):
+        grads = [torch.randn(*s, device="cuda", generator=g) * 1e-2 for s in shapes]
+        r = rel if it != 2 else None
+        for p, gr in zip(ps, grads):
+            p.grad = gr.clone()
+        opt.step(r)
+        for q, gr, m, v, lr in zip(qs, grads, ms, vs, lrs):
+            lodgs.check(lodgs.lib.lodgs_adam_step(q.data_ptr(), gr.data_ptr(), m.data_ptr(), v.data_ptr(), r.data_ptr() if r is not None else None,
+                                                  r.numel() if r is not None else 0, None, rows, q.numel() // rows, lr, 0.9, 0.999, 1e-15, it + 1, 1,
+                                                  lodgs.current_stream()))
+        for p, q in zip(ps, qs):
+            assert torch.equal(p.data, q)
+    for p, m, v in zip(ps, ms, vs):
+        assert torch.equal(opt.state[p]["exp_avg"], m) and torch.equal(opt.state[p]["exp_avg_sq"], v)
+    assert not torch.equal(ps[2].data, init[2])
