@@ -94,3 +94,4 @@ if __name__ == "__main__":
         run(50000, 640, 360)
         run(20000, 320, 200, lod=True)
         run(1000000, 1920, 1080)
+        run(1000000, 1920, 1080, lod=True)
