@@ -25,7 +25,12 @@ def _worker(rank, world, port, q):
     g = torch.Generator().manual_seed(100 + rank)
     grads = [torch.randn(50, 3, generator=g), None, torch.randn(50, 16, 3, generator=g), torch.randn(50, 1, generator=g)]
     want = None
+    # rank 0 takes the flat-bucket path for every tensor, rank 1 would too; the second call forces the in-place path for the
+    # 9600-byte tensor (threshold 1000 bytes) and keeps the bucket for the others — both must give the same sums
+    again = [None if x is None else x.clone() for x in grads]
     nbytes = parallel.allreduce_gradients(grads)
+    nbytes2 = parallel.allreduce_gradients(again, inplace_min_bytes=1000)
+    assert nbytes2 == nbytes and all(a is None or torch.equal(a, b) for a, b in zip(again, grads))
     lo, hi = parallel.shard_range(11, rank, world)
     t = parallel.gather_timings(torch.arange(lo, hi, dtype=torch.float64))
     # numpy arrays travel by value; torch tensors would be passed as shared-memory handles that die with this process
