@@ -12,7 +12,10 @@ from lodgs import LodgsError, check, current_stream, lib, ptr
 
 _ws_cache = {}          # (device index) -> workspace tensor (grown on demand; the reference mallocs per call)
 _traversable = {}       # (nodes ptr, N) -> bool, from lodgs_cut_prepare
+_last_count = {}        # (nodes ptr, N) -> K of the previous cut of this hierarchy (the next frame's is close to it)
 TRAVERSAL_MIN_NODES = 16_000_000   # below this the single-pass flat kernel is faster than ~25 grid-synchronised levels
+TRAVERSAL_MAX_CUT_FRACTION = 0.10  # traversal time grows with the nodes it visits (about 2 K), the flat pass reads all N at
+#                                    ~3 TB/s: measured cross-over on 33.5 M nodes is K ~ 0.12 N (profiles/r1_cut_k24_s15.json)
 
 
 def _workspace(N, dev):
@@ -43,8 +46,11 @@ def expand_to_size(nodes, boxes, size, viewpoint, viewdir, render_indices, paren
     nodes, boxes = nodes.contiguous(), boxes.contiguous()
     N = nodes.size(0)
     vp = viewpoint.to(device=dev, dtype=torch.float32).contiguous()
+    key = (nodes.data_ptr(), N)
     if mode is None:
-        mode = 1 if (N >= TRAVERSAL_MIN_NODES and _traversable.get((nodes.data_ptr(), N), False)) else 0
+        # traversal only pays on a big hierarchy cut shallowly; the previous frame's K is the predictor (first call: flat)
+        mode = 1 if (N >= TRAVERSAL_MIN_NODES and _traversable.get(key, False)
+                     and _last_count.get(key, N) < TRAVERSAL_MAX_CUT_FRACTION * N) else 0
     if mode == 1 and not _traversable.get((nodes.data_ptr(), N), False):
         if not prepare_hierarchy(nodes, boxes):
             mode = 0
@@ -55,6 +61,7 @@ def expand_to_size(nodes, boxes, size, viewpoint, viewdir, render_indices, paren
     check(lib.lodgs_expand_to_size(ptr(nodes), ptr(boxes), N, float(size), ptr(vp), ptr(render_indices), ptr(parent_indices),
                                    ptr(nodes_for_render_indices), int(capacity), ws.data_ptr(), ws.numel(), int(mode),
                                    C.addressof(count), current_stream()))
+    _last_count[key] = int(count.value)
     return int(count.value)
 
 

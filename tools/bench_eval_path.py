@@ -162,6 +162,16 @@ def main():
     ph_o = {"cut_ms": 0.0, "weights_ms": 0.0, "forward_ms": 0.0}
     for cam in cams[:n_ph]:
         ours_frame(cam, ph_o)
+    if os.environ.get("EVAL_DEBUG") and rank == 0:   # per-kernel device times of this library over 10 frames (lodgs.profile)
+        import lodgs
+        lodgs.profile(True)
+        for cam in cams[:10]:
+            ours_frame(cam)
+        torch.cuda.synchronize()
+        prof = lodgs.profile_dump()
+        lodgs.profile(False)
+        for name, (ms, n) in sorted(prof.items(), key=lambda kv: -kv[1][0]):
+            print("   %-28s %4.1f/frame %.4f ms/frame" % (name, n / 10, ms / 10), file=sys.stderr)
     t_ours = job_time(ours_frame)
     out = {"metric": "eval frames/s (cut + weights + forward, 1080p)", "n_gpus": world, "frames": args.frames, "frames_per_rank": len(cams),
            "nodes": N, "gaussians": N, "tau_px": args.tau, "scaling": "strong", "data": "synthetic",
