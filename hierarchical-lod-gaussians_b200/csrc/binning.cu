@@ -188,6 +188,76 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(int R, const uint32_t*
     }
 }
 
+// Blend CTAs take the tiles with the longest lists first (the grid's hardware order is CTA index order): a view that puts most
+// instances into a band of tiles (a slab seen from its edge) otherwise starts its longest lists in the middle of the launch and ends
+// on them with most SMs idle. Four classes by list length relative to the longest (>= 1/2, >= 1/4, >= 1/8, rest), tile-id order kept
+// inside a class (a stable partition: neighbouring tiles share splat records in L2; a full sort by length was measured slower on the
+// eval path for that reason). One CTA, every thread owns a contiguous run of tiles. A tile's result does not depend on when it runs.
+constexpr int ORDER_CLASSES = 4;
+__device__ __forceinline__ int order_class(unsigned len, unsigned mx) {
+    return len >= (mx >> 1) ? 0 : len >= (mx >> 2) ? 1 : len >= (mx >> 3) ? 2 : 3;
+}
+__global__ void __launch_bounds__(1024) tile_order_kernel(const uint2* __restrict__ ranges, uint32_t* __restrict__ order, int ntiles) {
+    __shared__ unsigned s_max, s_warp[ORDER_CLASSES][32], s_base[ORDER_CLASSES];
+    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_max = 0;
+    __syncthreads();
+    const int per = (ntiles + 1023) / 1024, lo = min(ntiles, (int)tid * per), hi = min(ntiles, lo + per);
+    unsigned m = 0;
+    for (int t = lo; t < hi; t++) {
+        const uint2 r = ranges[t];
+        m = max(m, r.y - r.x);
+    }
+    m = __reduce_max_sync(0xffffffffu, m);
+    if (lane == 0) atomicMax(&s_max, m);
+    __syncthreads();
+    const unsigned mx = max(s_max, 8u);
+    unsigned cnt[ORDER_CLASSES] = {0, 0, 0, 0}, incl[ORDER_CLASSES];
+    for (int t = lo; t < hi; t++) {
+        const uint2 r = ranges[t];
+        const int c = order_class(r.y - r.x, mx);
+#pragma unroll
+        for (int k = 0; k < ORDER_CLASSES; k++) cnt[k] += (c == k);
+    }
+#pragma unroll
+    for (int k = 0; k < ORDER_CLASSES; k++) {
+        unsigned v = cnt[k];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned t = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= (unsigned)o) v += t;
+        }
+        incl[k] = v;
+        if (lane == 31) s_warp[k][warp] = v;
+    }
+    __syncthreads();
+    if (warp < ORDER_CLASSES) {
+        const unsigned w = s_warp[warp][lane];
+        unsigned wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned t = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= (unsigned)o) wi += t;
+        }
+        s_warp[warp][lane] = wi - w;
+        if (lane == 31) s_base[warp] = wi;   // class total
+    }
+    __syncthreads();
+    unsigned pos[ORDER_CLASSES], base = 0;
+#pragma unroll
+    for (int k = 0; k < ORDER_CLASSES; k++) {
+        pos[k] = base + s_warp[k][warp] + incl[k] - cnt[k];
+        base += s_base[k];
+    }
+    for (int t = lo; t < hi; t++) {
+        const uint2 r = ranges[t];
+        const int c = order_class(r.y - r.x, mx);
+#pragma unroll
+        for (int k = 0; k < ORDER_CLASSES; k++)
+            if (c == k) order[pos[k]++] = (uint32_t)t;
+    }
+}
+
 // LOD rendering: the last two slots of every blend record become the interpolation weight and 1/kids.
 __global__ void __launch_bounds__(256) lod_patch_kernel(int P, const float* __restrict__ ts, const int32_t* __restrict__ kids,
                                                        SplatRec* __restrict__ recs) {
@@ -222,6 +292,11 @@ int launch_tile_ranges(int R, const BinningState& b, uint2* ranges, size_t ntile
     const int threads = (R + RANGE_ITEMS - 1) / RANGE_ITEMS;
     tile_ranges_kernel<<<(threads + 255) / 256, 256, 0, s>>>(R, b.tiles_sorted, ranges);
     LODGS_LAUNCHED("tile_ranges_kernel");
+    return LODGS_OK;
+}
+int launch_tile_order(const uint2* ranges, uint32_t* order, size_t ntiles, cudaStream_t s) {
+    tile_order_kernel<<<1, 1024, 0, s>>>(ranges, order, (int)ntiles);
+    LODGS_LAUNCHED("tile_order_kernel");
     return LODGS_OK;
 }
 int launch_lod_patch(int P, const GeomState& g, const float* ts, const int32_t* kids, cudaStream_t s) {

@@ -9,6 +9,7 @@
 // array through the same async-copy ring as the forward, and the replay starts at the tile's last contributing
 // splat instead of the end of its range.
 #include "state.cuh"
+#include <cstdlib>
 
 namespace lodgs {
 
@@ -168,7 +169,7 @@ __device__ __forceinline__ bool bwd_pair2(BwdPix2& p, const unsigned pos, const 
 }
 
 template <bool LOD, bool DEPTH>
-__global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
+__global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const SplatRec* __restrict__ recs,
                                                                const uint32_t* __restrict__ point_list, int W, int H,
                                                                const float* __restrict__ bg_color, const float bg_mult,
                                                                const float null_thr, const int32_t* __restrict__ indices,
@@ -181,8 +182,11 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
     BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, tx = tid & 15u, ty = tid >> 4;
     const unsigned horizontal_blocks = (W + TILE_X - 1) / TILE_X;
-    const unsigned pix_x = blockIdx.x * TILE_X + tx, pix_y0 = blockIdx.y * TILE_Y + 2u * ty;
-    const uint2 range = ranges[blockIdx.y * horizontal_blocks + blockIdx.x];
+    const unsigned cta = blockIdx.y * horizontal_blocks + blockIdx.x;
+    const unsigned tile = tile_order ? __ldg(tile_order + cta) : cta;   // longest lists first (binning.cu)
+    const unsigned tile_x = tile % horizontal_blocks, tile_y = tile / horizontal_blocks;
+    const unsigned pix_x = tile_x * TILE_X + tx, pix_y0 = tile_y * TILE_Y + 2u * ty;
+    const uint2 range = ranges[tile];
     const size_t HW = (size_t)H * W;
     const float bg0 = bg_color[0], bg1 = bg_color[1], bg2 = bg_color[2];
 
@@ -349,7 +353,9 @@ int launch_blend_bwd(bool lod, bool depth, const ImageState& img, const BinningS
         attr_set = true;
     }
     const size_t smem = sizeof(BwdSmem);
-#define LODGS_BWD_ARGS img.ranges, recs, bin.point_list, W, H, bg, bg_mult, null_thr, indices, img.final_T, img.n_contrib, dL_dpix, dL_dinvdepth_pix, \
+    static const bool tile_id_order = getenv("LODGS_BLEND_TILE_ID_ORDER") != nullptr;  // A/B: CTAs in tile-id order
+    const uint32_t* order = tile_id_order ? nullptr : img.tile_order;
+#define LODGS_BWD_ARGS img.ranges, order, recs, bin.point_list, W, H, bg, bg_mult, null_thr, indices, img.final_T, img.n_contrib, dL_dpix, dL_dinvdepth_pix, \
                        dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dinvdepth
     if (lod && depth) blend_bwd_kernel<true, true><<<grid, block, smem, s>>>(LODGS_BWD_ARGS);
     else if (lod) blend_bwd_kernel<true, false><<<grid, block, smem, s>>>(LODGS_BWD_ARGS);

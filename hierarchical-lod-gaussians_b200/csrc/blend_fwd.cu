@@ -10,6 +10,7 @@
 // The arithmetic keeps the reference's expression order (quadratic form, expf, __powf, blend FMAs) so that
 // n_contrib — an integer output decided by the alpha<1/255 and T<1e-4 tests — and the image are bit-identical.
 #include "state.cuh"
+#include <cstdlib>
 
 namespace lodgs {
 
@@ -80,7 +81,7 @@ __device__ __forceinline__ void blend_pair2(PixState2& p, unsigned& done0, unsig
 }
 
 template <bool LOD, bool DEPTH, bool SEEN>
-__global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
+__global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const SplatRec* __restrict__ recs,
                                                                  const uint32_t* __restrict__ point_list, int W, int H,
                                                                  const float* __restrict__ bg_color, float* __restrict__ final_T,
                                                                  uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
@@ -89,7 +90,10 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* _
     BlendSmem& sm = *reinterpret_cast<BlendSmem*>(smem_raw);
     const unsigned tid = threadIdx.x, tx = tid & 15u, ty = tid >> 4;
     const unsigned horizontal_blocks = (W + TILE_X - 1) / TILE_X;
-    const unsigned pix_x = blockIdx.x * TILE_X + tx, pix_y0 = blockIdx.y * TILE_Y + 2u * ty;
+    const unsigned cta = blockIdx.y * horizontal_blocks + blockIdx.x;
+    const unsigned tile = tile_order ? __ldg(tile_order + cta) : cta;   // longest lists first (binning.cu)
+    const unsigned tile_x = tile % horizontal_blocks, tile_y = tile / horizontal_blocks;
+    const unsigned pix_x = tile_x * TILE_X + tx, pix_y0 = tile_y * TILE_Y + 2u * ty;
     const bool inside0 = pix_x < (unsigned)W && pix_y0 < (unsigned)H;
     const bool inside1 = pix_x < (unsigned)W && pix_y0 + 1u < (unsigned)H;
     unsigned done0 = inside0 ? 0u : 1u, done1 = inside1 ? 0u : 1u;
@@ -100,7 +104,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* _
     p.C0 = p.C1 = p.C2 = p.D = bc(0.f);
     p.last0 = p.last1 = 0u;
 
-    const uint2 range = ranges[blockIdx.y * horizontal_blocks + blockIdx.x];
+    const uint2 range = ranges[tile];
     const int total = (int)(range.y - range.x);
     const int rounds = (total + BLEND_BATCH - 1) / BLEND_BATCH;
 
@@ -225,36 +229,38 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* _
 }
 
 template <bool LOD, bool DEPTH, bool SEEN>
-static int launch_blend_one(dim3 grid, cudaStream_t s, const uint2* ranges, const SplatRec* recs, const uint32_t* point_list, int W, int H,
+static int launch_blend_one(dim3 grid, cudaStream_t s, const uint2* ranges, const uint32_t* order, const SplatRec* recs, const uint32_t* point_list, int W, int H,
                             const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_invdepth, int32_t* seen) {
     static bool attr_set = false;
     if (!attr_set) {
         LODGS_CUDA(cudaFuncSetAttribute(blend_fwd_kernel<LOD, DEPTH, SEEN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BlendSmem)));
         attr_set = true;
     }
-    blend_fwd_kernel<LOD, DEPTH, SEEN><<<grid, BLEND_THREADS, sizeof(BlendSmem), s>>>(ranges, recs, point_list, W, H, bg, final_T, n_contrib,
+    blend_fwd_kernel<LOD, DEPTH, SEEN><<<grid, BLEND_THREADS, sizeof(BlendSmem), s>>>(ranges, order, recs, point_list, W, H, bg, final_T, n_contrib,
                                                                                   out_color, out_invdepth, seen);
     LODGS_LAUNCHED("blend_fwd_kernel");
     return LODGS_OK;
 }
 
 template <bool LOD, bool DEPTH>
-static int launch_blend_seen(bool has_seen, dim3 grid, dim3 block, cudaStream_t s, const uint2* ranges, const SplatRec* recs,
+static int launch_blend_seen(bool has_seen, dim3 grid, dim3 block, cudaStream_t s, const uint2* ranges, const uint32_t* order, const SplatRec* recs,
                              const uint32_t* point_list, int W, int H, const float* bg, float* final_T, uint32_t* n_contrib,
                              float* out_color, float* out_invdepth, int32_t* seen) {
     (void)block;
-    if (has_seen) return launch_blend_one<LOD, DEPTH, true>(grid, s, ranges, recs, point_list, W, H, bg, final_T, n_contrib, out_color, out_invdepth, seen);
-    return launch_blend_one<LOD, DEPTH, false>(grid, s, ranges, recs, point_list, W, H, bg, final_T, n_contrib, out_color, out_invdepth, seen);
+    if (has_seen) return launch_blend_one<LOD, DEPTH, true>(grid, s, ranges, order, recs, point_list, W, H, bg, final_T, n_contrib, out_color, out_invdepth, seen);
+    return launch_blend_one<LOD, DEPTH, false>(grid, s, ranges, order, recs, point_list, W, H, bg, final_T, n_contrib, out_color, out_invdepth, seen);
 }
 
 int launch_blend_fwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, const SplatRec* recs, int W, int H,
                      const float* bg, float* out_color, float* out_invdepth, int32_t* seen, cudaStream_t s) {
     dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1), block(TILE_X, TILE_Y, 1);
     const bool hs = seen != nullptr;
-    if (lod && depth) return launch_blend_seen<true, true>(hs, grid, block, s, img.ranges, recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
-    if (lod && !depth) return launch_blend_seen<true, false>(hs, grid, block, s, img.ranges, recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
-    if (!lod && depth) return launch_blend_seen<false, true>(hs, grid, block, s, img.ranges, recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
-    return launch_blend_seen<false, false>(hs, grid, block, s, img.ranges, recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
+    static const bool tile_id_order = getenv("LODGS_BLEND_TILE_ID_ORDER") != nullptr;  // A/B: CTAs in tile-id order
+    const uint32_t* order = tile_id_order ? nullptr : img.tile_order;
+    if (lod && depth) return launch_blend_seen<true, true>(hs, grid, block, s, img.ranges, order, recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
+    if (lod && !depth) return launch_blend_seen<true, false>(hs, grid, block, s, img.ranges, order, recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
+    if (!lod && depth) return launch_blend_seen<false, true>(hs, grid, block, s, img.ranges, order, recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
+    return launch_blend_seen<false, false>(hs, grid, block, s, img.ranges, order, recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
 }
 
 // Work counters of the blend (bench.py roofline): replays the forward's per-pixel decisions and counts

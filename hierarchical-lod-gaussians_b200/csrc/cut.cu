@@ -76,7 +76,6 @@ constexpr int CUT_BLOCK = 512;
 // (TMA-staged records, persistent prefetching CTAs and wider look-back windows were all measured, profiles/).
 constexpr int FLAT_THREADS = 512;
 constexpr int FLAT_ROWS = 8;
-constexpr int FLAT_BATCH = 4;  // rows whose loads are in flight together
 constexpr int FLAT_TILE = FLAT_THREADS * FLAT_ROWS;
 constexpr int FLAT_PARTS = FLAT_ROWS * (FLAT_THREADS / 32);  // 64 (row, warp) partial sums per tile
 
@@ -98,56 +97,21 @@ __global__ void __launch_bounds__(FLAT_THREADS, 2) cut_flat_kernel(const int32_t
     const float vx = __ldg(viewpoint), vy = __ldg(viewpoint + 1), vz = __ldg(viewpoint + 2);
 
     int count[FLAT_ROWS], start[FLAT_ROWS], pgauss[FLAT_ROWS], incl[FLAT_ROWS];
-    // Rows go through the memory system FLAT_BATCH at a time, every stage of the dependent chain (own box + parent id ->
-    // size -> parent record / parent box -> count) issued for the whole batch before any of it is consumed. Written row by
-    // row, the IEEE sqrt/divide slow-path branches of node_size keep ptxas from hoisting the next row's loads, and a thread
-    // then waits for three DRAM round trips per row, 24 per tile (seen in the SASS of the first version). Indices are
-    // clamped instead of predicated (a row past the end re-reads node N-1, a node whose parent box is not needed re-reads its
-    // own box from L1), so the loads sit in straight-line code.
-    const float4* boxes4 = reinterpret_cast<const float4*>(boxes);
-#pragma unroll
-    for (int h = 0; h < FLAT_ROWS / FLAT_BATCH; h++) {
-        float4 bmin[FLAT_BATCH], bmax[FLAT_BATCH];
-        int parent[FLAT_BATCH], node[FLAT_BATCH];
-        float size[FLAT_BATCH];
-#pragma unroll
-        for (int q = 0; q < FLAT_BATCH; q++) {
-            const int j = (h * FLAT_BATCH + q) * FLAT_THREADS + (int)tid;
-            node[q] = min(base + j, N - 1);
-            bmin[q] = __ldg(boxes4 + (size_t)node[q] * 2);
-            bmax[q] = __ldg(boxes4 + (size_t)node[q] * 2 + 1);
-            parent[q] = __ldg(nodes + (size_t)node[q] * 7 + 1);
-        }
-#pragma unroll
-        for (int q = 0; q < FLAT_BATCH; q++) size[q] = node_size(bmin[q], bmax[q], vx, vy, vz);
-        int depth[FLAT_BATCH], leafs[FLAT_BATCH], merged[FLAT_BATCH];
-#pragma unroll
-        for (int q = 0; q < FLAT_BATCH; q++) {
-            const int r = h * FLAT_BATCH + q;
-            const bool need = !(size[q] >= tau) && parent[q] != -1;
-            const int pb = need ? parent[q] : node[q];
-            bmin[q] = __ldg(boxes4 + (size_t)pb * 2);
-            bmax[q] = __ldg(boxes4 + (size_t)pb * 2 + 1);
-            // the parent's Gaussian id is needed by every emitted entry
-            pgauss[r] = __ldg(nodes + (size_t)max(parent[q], 0) * 7 + 2);
-            const int32_t* rec = nodes + (size_t)node[q] * 7;  // same lines as the parent index above: L1
-            depth[q] = __ldg(rec + 0); start[r] = __ldg(rec + 2); leafs[q] = __ldg(rec + 3); merged[q] = __ldg(rec + 4);
-        }
-#pragma unroll
-        for (int q = 0; q < FLAT_BATCH; q++) {
-            const int r = h * FLAT_BATCH + q;
-            const int j = r * FLAT_THREADS + (int)tid;
-            const bool need = !(size[q] >= tau) && parent[q] != -1;
-            const float psize = node_size(bmin[q], bmax[q], vx, vy, vz);
-            int c = 0;
-            if (size[q] >= tau) c = leafs[q];
-            else if (need && psize >= tau) c = leafs[q] + (depth[q] != 0 ? merged[q] : 0);
-            count[r] = j < cnt ? c : 0;
-            if (parent[q] == -1) pgauss[r] = -1;
-        }
-    }
 #pragma unroll
     for (int r = 0; r < FLAT_ROWS; r++) {
+        const int j = r * FLAT_THREADS + (int)tid;
+        count[r] = 0; start[r] = 0; pgauss[r] = -1;
+        if (j < cnt) {
+            const int i = base + j;
+            const float4* b = reinterpret_cast<const float4*>(boxes) + (size_t)i * 2;
+            const float4 bmin = __ldg(b), bmax = __ldg(b + 1);
+            const NodeRec n = load_node(nodes, i);
+            // the parent's Gaussian id is needed by every emitted entry: fetch it now, off the critical path
+            if (n.parent != -1) pgauss[r] = __ldg(nodes + (size_t)n.parent * 7 + 2);
+            const float size = node_size(bmin, bmax, vx, vy, vz);
+            count[r] = render_count(n, size, boxes, tau, vx, vy, vz);
+            start[r] = n.start;
+        }
         int v = count[r];
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {

@@ -8,6 +8,7 @@ int sort_pairs32_device(const uint32_t* keys_in, const uint32_t* vals_in, uint32
                         uint32_t* vals_tmp, int n, int begin_bit, int end_bit, void* ws, cudaStream_t s, const char* pass_name,
                         const char* hist_name);
 int launch_tile_ranges(int R, const BinningState& b, uint2* ranges, size_t ntiles, cudaStream_t s);
+int launch_tile_order(const uint2* ranges, uint32_t* order, size_t ntiles, cudaStream_t s);
 int launch_lod_patch(int P, const GeomState& g, const float* ts, const int32_t* kids, cudaStream_t s);
 int launch_sorted_keys(int R, const BinningState& b, const GeomState& g, uint64_t* keys, cudaStream_t s);
 int sort_pairs_device(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, uint64_t* keys_tmp,
@@ -93,6 +94,8 @@ extern "C" int lodgs_forward_render(int P, int W, int H, int R, const float* bac
                                  bit, bf.b.sort_ws, s, "sort_tile_pass_kernel", "sort_tile_hist_kernel");
         if (rc) return rc;
         rc = launch_tile_ranges(R, bf.b, img.ranges, (size_t)gx * gy, s);
+        if (rc) return rc;
+        rc = launch_tile_order(img.ranges, img.tile_order, (size_t)gx * gy, s);
         if (rc) return rc;
         if (ts != nullptr && kids != nullptr) {
             rc = launch_lod_patch(P, g, ts, kids, s);

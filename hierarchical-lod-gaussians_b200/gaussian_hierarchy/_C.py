@@ -15,7 +15,7 @@ _traversable = {}       # (nodes ptr, N) -> bool, from lodgs_cut_prepare
 _last_count = {}        # (nodes ptr, N) -> K of the previous cut of this hierarchy (the next frame's is close to it)
 TRAVERSAL_MIN_NODES = 16_000_000   # below this the single-pass flat kernel is faster than ~25 grid-synchronised levels
 TRAVERSAL_MAX_CUT_FRACTION = 0.10  # traversal time grows with the nodes it visits (about 2 K), the flat pass reads all N at
-#                                    ~3 TB/s: measured cross-over on 33.5 M nodes is K ~ 0.12 N (profiles/r1_cut_k24_s15.json)
+#                                    ~3 TB/s: measured cross-over on 33.5 M nodes is K ~ 0.12 N (profiles/r1_cut_flat_ab_s15.json)
 
 
 def _workspace(N, dev):

@@ -90,13 +90,17 @@ class SparseGaussianAdam(torch.optim.Adam):
         super().__init__(params=params, lr=lr, eps=eps)
 
     @torch.no_grad()
-    def step(self, visibility, N):
+    def step(self, visibility, N, wait=None):
+        """`wait` (not in the reference): {param: work handle of its gradient's all-reduce}; the handle is waited for on the current
+        stream right before that parameter's update, so earlier groups update while later gradients are still being reduced."""
         for group in self.param_groups:
             lr, eps = group["lr"], group["eps"]
             assert len(group["params"]) == 1, "more than one tensor in group"
             param = group["params"][0]
             if param.grad is None:
                 continue
+            if wait is not None and wait.get(param) is not None:
+                wait[param].wait()
             state = self.state[param]
             if len(state) == 0:
                 state["step"] = torch.tensor(0.0, dtype=torch.float32)

@@ -49,6 +49,20 @@ def allreduce_gradients(grads, group=None, inplace_min_bytes=INPLACE_MIN_BYTES):
     return nbytes
 
 
+def allreduce_gradients_async(grads, group=None):
+    """Start one in-place sum all-reduce per (contiguous) gradient tensor, in list order, and return the work handles without waiting:
+    `handle.wait()` makes the CURRENT STREAM wait for that tensor only, so the optimizer can update the tensors that have arrived
+    while the later ones are still on the wire (`SparseGaussianAdam.step(..., wait=...)`). NCCL runs the calls in issue order: put
+    the tensor the step needs first (dL_dopacity, the visibility mask) first and the largest next. -> (handles, bytes)"""
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return [None] * len(grads), 0
+    for g in grads:
+        if g is None or not g.is_contiguous():
+            raise ValueError("allreduce_gradients_async needs contiguous gradient tensors")
+    works = [dist.all_reduce(g, op=dist.ReduceOp.SUM, group=group, async_op=True) for g in grads]
+    return works, sum(g.numel() * g.element_size() for g in grads)
+
+
 def gather_timings(values, group=None):
     """All ranks contribute a 1-D float64 tensor of per-frame timings; rank 0 gets the list of all."""
     if not dist.is_initialized() or dist.get_world_size(group) == 1:

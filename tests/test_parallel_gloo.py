@@ -28,9 +28,16 @@ def _worker(rank, world, port, q):
     # rank 0 takes the flat-bucket path for every tensor, rank 1 would too; the second call forces the in-place path for the
     # 9600-byte tensor (threshold 1000 bytes) and keeps the bucket for the others — both must give the same sums
     again = [None if x is None else x.clone() for x in grads]
+    grads0 = [x.clone() for x in grads if x is not None]
     nbytes = parallel.allreduce_gradients(grads)
     nbytes2 = parallel.allreduce_gradients(again, inplace_min_bytes=1000)
     assert nbytes2 == nbytes and all(a is None or torch.equal(a, b) for a, b in zip(again, grads))
+    # per-tensor handles (the optimizer waits for each parameter's gradient on its own)
+    third = [x.clone() for x in grads0]
+    handles, nbytes3 = parallel.allreduce_gradients_async(third)
+    for h in handles:
+        h.wait()
+    assert nbytes3 == nbytes and all(torch.equal(a, b) for a, b in zip(third, [g for g in grads if g is not None]))
     lo, hi = parallel.shard_range(11, rank, world)
     t = parallel.gather_timings(torch.arange(lo, hi, dtype=torch.float64))
     # numpy arrays travel by value; torch tensors would be passed as shared-memory handles that die with this process

@@ -1,8 +1,9 @@
 #!/usr/bin/env python3
 """BASELINE.json configs[4]: multi-view training of ONE chunk, views split across the GPUs, through the alt-rasterizer surface
 (alt_gaussian_rasterization: dc + shs, antialiasing on — configs/kbuffer.json) — per step and per rank: forward + backward of the
-rank's own 1920x1080 view of the replicated 1 M-Gaussian scene, ONE flat-bucket NCCL sum all-reduce of the six parameter gradients
-(lodgs.parallel.allreduce_gradients, 59 floats per Gaussian = 236 MB), visibility = dL_dopacity != 0 on the reduced gradient
+rank's own 1920x1080 view of the replicated 1 M-Gaussian scene, NCCL sum all-reduce of the six parameter gradients in place
+(lodgs.parallel.allreduce_gradients_async, 59 floats per Gaussian = 236 MB; each parameter's Adam update waits only for its own
+gradient, so updates overlap the rest of the exchange; --no-overlap finishes the exchange first), visibility = dL_dopacity != 0 on the reduced gradient
 (train_single.py:171-172), SparseGaussianAdam.step(visibility, N) on identical sums, so the replicas stay identical (checked at the end
 with an all-reduce of the parameter checksums' min and max).
 
@@ -34,6 +35,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--reference", action="store_true")
+    ap.add_argument("--no-overlap", action="store_true", help="finish the whole all-reduce before the optimizer starts")
     args = ap.parse_args()
     import numpy as np
     import torch
@@ -56,13 +58,16 @@ def main():
     target = torch.rand(3, H, W, device=dev, generator=torch.Generator(device=dev).manual_seed(100 + rank))
     bg = torch.zeros(3, device=dev)
     names = list(LRS)
+    # all-reduce issue order = optimizer group order: dL_dopacity first (the visibility mask needs it), the largest tensor next, so the
+    # remaining 56 MB travel while Adam runs over the 180 MB of shs_rest
+    order = ["opacities", "shs_rest", "means3D", "dc", "scales", "rotations"]
     N = args.P
     ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
     phase = {"fwd_bwd_ms": 0.0, "allreduce_ms": 0.0, "adam_ms": 0.0}
 
     if not args.reference:
         par = {k: torch.nn.Parameter(v) for k, v in par.items()}
-        opt = SparseGaussianAdam([{"params": [par[k]], "lr": LRS[k], "name": k} for k in names], lr=0.0, eps=1e-15)
+        opt = SparseGaussianAdam([{"params": [par[k]], "lr": LRS[k], "name": k} for k in order], lr=0.0, eps=1e-15)
         rs = GaussianRasterizationSettings(H, W, cam["tanfovx"], cam["tanfovy"], bg, 1.0, cam["viewmatrix"], cam["projmatrix"], DEG, cam["campos"],
                                            False, False, True)
         rast = GaussianRasterizer(rs)
@@ -78,11 +83,18 @@ def main():
             loss.backward()
             if timed:
                 e[1].record()
-            nbytes = parallel.allreduce_gradients([par[k].grad for k in names])
+            if args.no_overlap:
+                nbytes = parallel.allreduce_gradients([par[k].grad for k in names])
+                works = {}
+            else:
+                handles, nbytes = parallel.allreduce_gradients_async([par[k].grad for k in order])
+                works = {par[k]: h for k, h in zip(order, handles)}
+                if handles[0] is not None:
+                    handles[0].wait()
             if timed:
-                e[2].record()
+                e[2].record()   # overlapped mode: only dL_dopacity has arrived here; the rest of the exchange is inside adam_ms
             vis = (par["opacities"].grad != 0).reshape(-1)
-            opt.step(vis, N)
+            opt.step(vis, N, wait=works)
             opt.zero_grad(set_to_none=True)
             means2D.grad = None
             if timed:
@@ -152,7 +164,8 @@ def main():
            "mpix_per_s": round(world * W * H / ms / 1e3, 1), "scaling": "weak", "data": "synthetic",
            "phases_ms_max_over_ranks": {k: round(float(v) / args.steps, 4) for k, v in zip(phase, t[1:])},
            "allreduce_bytes": int(nbytes), "allreduce_bus_GBps": (round(2 * (world - 1) / world * nbytes / (float(t[2]) / args.steps * 1e-3) / 1e9, 1)
-                                                                  if world > 1 and float(t[2]) > 0 else None),
+                                                                  if world > 1 and float(t[2]) > 0 and (args.reference or args.no_overlap) else None),
+           "overlap": bool(not args.reference and not args.no_overlap),
            "replicas_identical": bool(torch.equal(lo, hi))}
     if rank == 0:
         print(json.dumps(out), flush=True)
