@@ -22,6 +22,7 @@ struct PreParams {
     const int32_t* indices;
     const int32_t* parent_indices;
     const float* ts;
+    const int32_t* kids;   // sibling counts: when given, the record's last two slots are stored as (t, 1/kids) right here
     const float* means3D;
     const float* shs;
     const float* colors_precomp;
@@ -207,7 +208,8 @@ __device__ __forceinline__ uint32_t preprocess_one(const PreParams& p, const Geo
     float4* out = reinterpret_cast<float4*>(g.recs + t_idx);
     out[0] = {point_image.x, point_image.y, conic.x, conic.y};
     out[1] = {conic.z, opac, rgb.x, rgb.y};
-    out[2] = {rgb.z, __frcp_rn(p_view.z), lim - 1e-4f * (1.0f + fabsf(lim)), 1.0f};  // rcp.rn == the reference's 1/depth per pair
+    if (p.kids) out[2] = {rgb.z, __frcp_rn(p_view.z), __ldg(p.ts + t_idx), 1.0f / (float)__ldg(p.kids + t_idx)};
+    else out[2] = {rgb.z, __frcp_rn(p_view.z), lim - 1e-4f * (1.0f + fabsf(lim)), 1.0f};  // rcp.rn == the reference's 1/depth per pair
     return (rmax.y - rmin.y) * (rmax.x - rmin.x);
 }
 
@@ -290,6 +292,18 @@ extern "C" int lodgs_forward_preprocess_ex(int P, int D, int M, int W, int H, co
                                            const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
                                            const float* campos, float tan_fovx, float tan_fovy, int32_t* radii, void* geom_buffer,
                                            size_t geom_bytes, int32_t* num_rendered_host, unsigned flags, void* stream) {
+    return lodgs_forward_preprocess_lod(P, D, M, W, H, indices, parent_indices, ts, nullptr, means3D, shs, colors_precomp, opacities, scales,
+                                        scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, radii,
+                                        geom_buffer, geom_bytes, num_rendered_host, flags, stream);
+}
+
+extern "C" int lodgs_forward_preprocess_lod(int P, int D, int M, int W, int H, const int32_t* indices, const int32_t* parent_indices,
+                                            const float* ts, const int32_t* kids, const float* means3D, const float* shs,
+                                            const float* colors_precomp, const float* opacities, const float* scales, float scale_modifier,
+                                            const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                                            const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy, int32_t* radii,
+                                            void* geom_buffer, size_t geom_bytes, int32_t* num_rendered_host, unsigned flags, void* stream) {
+    if (kids && !ts) { set_error("lodgs_forward_preprocess_lod: kids without ts"); return LODGS_E_ARG; }
     if (P < 0 || W <= 0 || H <= 0 || D < 0 || D > 3) { set_error("lodgs_forward_preprocess: bad size argument"); return LODGS_E_ARG; }
     if (P == 0) { if (num_rendered_host) *num_rendered_host = 0; return LODGS_OK; }
     if (!means3D || !opacities || !viewmatrix || !projmatrix || !campos || !radii || !geom_buffer) {
@@ -306,7 +320,7 @@ extern "C" int lodgs_forward_preprocess_ex(int P, int D, int M, int W, int H, co
     GeomState g = geom_from_chunk(geom_buffer, P);
     PreParams p;
     p.P = P; p.D = D; p.M = M; p.W = W; p.H = H;
-    p.indices = indices; p.parent_indices = parent_indices; p.ts = ts; p.means3D = means3D; p.shs = shs;
+    p.indices = indices; p.parent_indices = parent_indices; p.ts = ts; p.kids = kids; p.means3D = means3D; p.shs = shs;
     p.colors_precomp = colors_precomp; p.opacities = opacities; p.scales = scales; p.scale_modifier = scale_modifier;
     p.rotations = rotations; p.cov3D_precomp = cov3D_precomp; p.viewmatrix = viewmatrix; p.projmatrix = projmatrix;
     p.campos = campos; p.tan_fovx = tan_fovx; p.tan_fovy = tan_fovy;

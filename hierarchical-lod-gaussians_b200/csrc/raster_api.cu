@@ -108,7 +108,7 @@ extern "C" int lodgs_forward_render(int P, int W, int H, int R, const float* bac
         // reference behaviour: leave out_color untouched.
         return LODGS_OK;
     }
-    const bool lod = ts != nullptr && kids != nullptr;
+    const bool lod = ts != nullptr;  // kids == NULL with ts: stage 1 (lodgs_forward_preprocess_lod) already stored t and 1/kids
     return launch_blend_fwd(lod, out_invdepth != nullptr, img, bf.b, recs, W, H, background, out_color, out_invdepth, seen, s);
 }
 

@@ -14,6 +14,8 @@ NUM_CHANNELS = 3
 # reference hands fresh torch byte tensors back to Python (rasterize_points.cu:85-92) and so do we: they are what
 # autograd saves for backward.
 
+LOD_IN_RECORDS = True   # False: stage 2 patches t and 1/kids into the records (lod_patch_kernel); kept for the C ABI's older call sequence
+
 
 def _byte_buffer(nbytes, device):
     # torch allocations are 512-byte aligned, which satisfies the library's 128-byte requirement
@@ -64,15 +66,18 @@ def forward_impl(background, indices, parent_indices, ts, kids, means3D, colors,
         geom = _byte_buffer(lib.lodgs_geom_bytes(P), dev)
         img = _byte_buffer(lib.lodgs_image_bytes(W, H), dev)
         n = C.c_int32(0)
-        check(lib.lodgs_forward_preprocess_ex(P, int(degree), M, W, H, ptr(indices), ptr(parent_indices), ptr(ts), ptr(means3D),
-                                              ptr(sh), ptr(colors), ptr(opacity), ptr(scales), float(scale_modifier),
-                                              ptr(rotations), ptr(cov3D_precomp), ptr(viewmatrix), ptr(projmatrix), ptr(campos),
-                                              float(tan_fovx), float(tan_fovy), ptr(radii), geom.data_ptr(), geom.numel(),
-                                              C.addressof(n), int(_flags), stream))
+        # with both ts and kids the preprocess kernel stores t and 1/kids into the blend records itself; stage 2 then gets kids = None
+        in_records = LOD_IN_RECORDS and ts.numel() != 0 and kids.numel() != 0
+        check(lib.lodgs_forward_preprocess_lod(P, int(degree), M, W, H, ptr(indices), ptr(parent_indices), ptr(ts),
+                                               ptr(kids) if in_records else None, ptr(means3D),
+                                               ptr(sh), ptr(colors), ptr(opacity), ptr(scales), float(scale_modifier),
+                                               ptr(rotations), ptr(cov3D_precomp), ptr(viewmatrix), ptr(projmatrix), ptr(campos),
+                                               float(tan_fovx), float(tan_fovy), ptr(radii), geom.data_ptr(), geom.numel(),
+                                               C.addressof(n), int(_flags), stream))
         rendered = int(n.value)
         if rendered > 0:
             binning = _byte_buffer(lib.lodgs_binning_bytes(rendered), dev)
-            check(lib.lodgs_forward_render(P, W, H, rendered, ptr(background), ptr(ts), ptr(kids), ptr(colors), ptr(radii),
+            check(lib.lodgs_forward_render(P, W, H, rendered, ptr(background), ptr(ts), None if in_records else ptr(kids), ptr(colors), ptr(radii),
                                            geom.data_ptr(), binning.data_ptr(), binning.numel(), img.data_ptr(), img.numel(),
                                            ptr(out_color), ptr(out_invdepth) if do_depth else None, ptr(seen), stream))
         if debug:

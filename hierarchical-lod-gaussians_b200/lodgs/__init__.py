@@ -66,6 +66,8 @@ _SIGS = {
                                       _p, _sz, _p, _p]),
     "lodgs_forward_preprocess_ex": (_i, [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _f, _f, _p,
                                          _p, _sz, _p, C.c_uint, _p]),
+    "lodgs_forward_preprocess_lod": (_i, [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _f, _f, _p,
+                                          _p, _sz, _p, C.c_uint, _p]),
     "lodgs_forward_render": (_i, [_i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _sz, _p, _sz, _p, _p, _p, _p]),
     "lodgs_backward": (_i, [_i, _i, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _f, _f, _p,
                             _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),

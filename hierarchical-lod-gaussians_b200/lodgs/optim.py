@@ -90,9 +90,14 @@ class SparseGaussianAdam(torch.optim.Adam):
         super().__init__(params=params, lr=lr, eps=eps)
 
     @torch.no_grad()
-    def step(self, visibility, N, wait=None):
-        """`wait` (not in the reference): {param: work handle of its gradient's all-reduce}; the handle is waited for on the current
-        stream right before that parameter's update, so earlier groups update while later gradients are still being reduced."""
+    def step(self, visibility, N):
+        self.step_overlapped(visibility, N, None)
+
+    @torch.no_grad()
+    def step_overlapped(self, visibility, N, wait):
+        """step() for data-parallel training (not in the reference): `wait` = {param: work handle of its gradient's all-reduce}; the
+        handle is waited for on the current stream right before that parameter's update, so earlier groups update while later
+        gradients are still being reduced (lodgs.parallel.allreduce_gradients_async)."""
         for group in self.param_groups:
             lr, eps = group["lr"], group["eps"]
             assert len(group["params"]) == 1, "more than one tensor in group"

@@ -52,7 +52,7 @@ def allreduce_gradients(grads, group=None, inplace_min_bytes=INPLACE_MIN_BYTES):
 def allreduce_gradients_async(grads, group=None):
     """Start one in-place sum all-reduce per (contiguous) gradient tensor, in list order, and return the work handles without waiting:
     `handle.wait()` makes the CURRENT STREAM wait for that tensor only, so the optimizer can update the tensors that have arrived
-    while the later ones are still on the wire (`SparseGaussianAdam.step(..., wait=...)`). NCCL runs the calls in issue order: put
+    while the later ones are still on the wire (`SparseGaussianAdam.step_overlapped`). NCCL runs the calls in issue order: put
     the tensor the step needs first (dL_dopacity, the visibility mask) first and the largest next. -> (handles, bytes)"""
     if not dist.is_initialized() or dist.get_world_size(group) == 1:
         return [None] * len(grads), 0

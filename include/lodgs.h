@@ -204,13 +204,27 @@ int lodgs_forward_preprocess_ex(int P, int D, int M, int W, int H,
                                 float tan_fovx, float tan_fovy, int32_t* radii,
                                 void* geom_buffer, size_t geom_bytes, int32_t* num_rendered_host, unsigned flags, void* stream);
 
+/* lodgs_forward_preprocess_ex for hierarchical-LOD rendering with the sibling counts known at stage 1 (`kids` [P] i32, the
+ * num_node_kids of GaussianRasterizationSettings; requires ts): the interpolation weight and 1/kids are stored into the blend
+ * records by the preprocess kernel itself, so stage 2 has no separate pass over the records. Call lodgs_forward_render with the
+ * same ts and kids = NULL afterwards ("records complete"). kids = NULL here is lodgs_forward_preprocess_ex. */
+int lodgs_forward_preprocess_lod(int P, int D, int M, int W, int H,
+                                 const int32_t* indices, const int32_t* parent_indices, const float* ts, const int32_t* kids,
+                                 const float* means3D, const float* shs, const float* colors_precomp,
+                                 const float* opacities, const float* scales, float scale_modifier,
+                                 const float* rotations, const float* cov3D_precomp,
+                                 const float* viewmatrix, const float* projmatrix, const float* campos,
+                                 float tan_fovx, float tan_fovy, int32_t* radii,
+                                 void* geom_buffer, size_t geom_bytes, int32_t* num_rendered_host, unsigned flags, void* stream);
+
 /* Stage 2: replaces duplicateWithKeys (rasterizer_impl.cu:70-115) + cub::DeviceRadixSort::SortPairs on the 64-bit
  * tile|depth keys (:358-363) + identifyTileRanges (:120-142) + renderCUDA (forward.cu:450-596). Stage 1 has already
  * ordered the Gaussians by depth bits (onesweep radix sort over P u32 keys); stage 2 emits the (tile, Gaussian) instances
  * in that order, sorts them stably by tile id alone (2 onesweep passes at 1080p instead of 6 over 64-bit keys), which
  * yields exactly the reference's sorted list, then finds the tile ranges and blends; the blend kernels gather the
  * per-Gaussian records through the sorted id list, so no per-instance record or key array is written.
- * R is the value stage 1 reported; ts/kids non-NULL select the hierarchical-LOD alpha.
+ * R is the value stage 1 reported; ts non-NULL selects the hierarchical-LOD alpha: with kids the records get t and 1/kids here
+ * (one extra pass), with kids = NULL they must already hold them (stage 1 = lodgs_forward_preprocess_lod).
  * out_color [3,H,W]; out_invdepth [H,W] or NULL; seen [P] i32 or NULL (must be zero-filled by the caller,
  * as the reference's torch::full does). */
 int lodgs_forward_render(int P, int W, int H, int R, const float* background,

@@ -57,6 +57,23 @@ def test_against_golden_reference_outputs(name):
         assert rel_l2(g[k], torch.from_numpy(gold[k]).cuda()) <= 1e-3, k
 
 
+def test_lod_records_stored_at_stage1_or_patched_at_stage2_agree():
+    """lodgs_forward_preprocess_lod (t, 1/kids stored by the preprocess kernel) against the older call sequence
+    (lodgs_forward_preprocess_ex, then lodgs_forward_render patching the records): identical bits, forward and backward."""
+    from diff_gaussian_rasterization import _C as dgr
+    f1, g1 = run_mine("lod")
+    dgr.LOD_IN_RECORDS = False
+    try:
+        f2, g2 = run_mine("lod")
+    finally:
+        dgr.LOD_IN_RECORDS = True
+    assert f1["R"] == f2["R"]
+    for k in ("color", "invdepth", "n_contrib", "final_T", "recs", "point_list", "ranges"):
+        assert torch.equal(f1[k], f2[k]), k
+    for k in GRAD_KEYS:
+        assert rel_l2(g1[k], g2[k]) <= 1e-5, k   # atomics order only
+
+
 @pytest.mark.parametrize("name", ["small", "lod"])
 def test_against_cpu_oracle(name):
     sc, cam, bg, kw, dL, dLi = cases.make_case(name)

@@ -94,7 +94,7 @@ def main():
             if timed:
                 e[2].record()   # overlapped mode: only dL_dopacity has arrived here; the rest of the exchange is inside adam_ms
             vis = (par["opacities"].grad != 0).reshape(-1)
-            opt.step(vis, N, wait=works)
+            opt.step_overlapped(vis, N, works)
             opt.zero_grad(set_to_none=True)
             means2D.grad = None
             if timed:
