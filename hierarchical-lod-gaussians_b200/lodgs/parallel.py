@@ -22,15 +22,26 @@ def shard_range(n_items, rank, world):
 INPLACE_MIN_BYTES = 1 << 20
 
 
-def allreduce_gradients(grads, group=None, inplace_min_bytes=INPLACE_MIN_BYTES):
+def allreduce_gradients(grads, group=None, inplace_min_bytes=INPLACE_MIN_BYTES, coalesce=False):
     """Sum a list of gradient tensors across ranks (NCCL all-reduce over NVLink on a B200 box, gloo on CPU in the tests).
     Contiguous tensors of at least `inplace_min_bytes` are reduced where they lie, back to back on the collective's stream (no
     staging copy: packing 59 floats per Gaussian into a bucket and unpacking it again costs two extra passes over 236 MB at 1 M
     Gaussians); the small ones share one flat bucket so that each does not pay a collective's latency. Tensors are updated in
-    place; returns the number of bytes reduced."""
+    place; returns the number of bytes reduced. `coalesce` issues the in-place calls inside one NCCL group (one launch for all
+    tensors) through torch's coalescing manager."""
     grads = [g for g in grads if g is not None]
     if not grads or not dist.is_initialized() or dist.get_world_size(group) == 1:
         return 0
+    if coalesce:
+        from torch.distributed.distributed_c10d import _coalescing_manager
+        for g in grads:
+            if not g.is_contiguous():
+                raise ValueError("coalesced all-reduce needs contiguous gradient tensors")
+        with _coalescing_manager(group=group, device=grads[0].device, async_ops=True) as cm:
+            for g in grads:
+                dist.all_reduce(g, op=dist.ReduceOp.SUM, group=group)
+        cm.wait()
+        return sum(g.numel() * g.element_size() for g in grads)
     big = [g for g in grads if g.is_contiguous() and g.numel() * g.element_size() >= inplace_min_bytes]
     small = [g for g in grads if not (g.is_contiguous() and g.numel() * g.element_size() >= inplace_min_bytes)]
     works = [dist.all_reduce(g, op=dist.ReduceOp.SUM, group=group, async_op=True) for g in big]

@@ -36,6 +36,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--reference", action="store_true")
     ap.add_argument("--no-overlap", action="store_true", help="finish the whole all-reduce before the optimizer starts")
+    ap.add_argument("--coalesce", action="store_true", help="with --no-overlap: the six in-place all-reduces inside one NCCL group")
     ap.add_argument("--flat-bucket", action="store_true", help="with --no-overlap: pack all gradients into one bucket, one NCCL call")
     args = ap.parse_args()
     import numpy as np
@@ -85,7 +86,8 @@ def main():
             if timed:
                 e[1].record()
             if args.no_overlap:
-                nbytes = parallel.allreduce_gradients([par[k].grad for k in names], inplace_min_bytes=(1 << 62) if args.flat_bucket else parallel.INPLACE_MIN_BYTES)
+                nbytes = parallel.allreduce_gradients([par[k].grad for k in names], inplace_min_bytes=(1 << 62) if args.flat_bucket else parallel.INPLACE_MIN_BYTES,
+                                                        coalesce=args.coalesce)
                 works = {}
             else:
                 handles, nbytes = parallel.allreduce_gradients_async([par[k].grad for k in order])
@@ -166,7 +168,7 @@ def main():
            "phases_ms_max_over_ranks": {k: round(float(v) / args.steps, 4) for k, v in zip(phase, t[1:])},
            "allreduce_bytes": int(nbytes), "allreduce_bus_GBps": (round(2 * (world - 1) / world * nbytes / (float(t[2]) / args.steps * 1e-3) / 1e9, 1)
                                                                   if world > 1 and float(t[2]) > 0 and (args.reference or args.no_overlap) else None),
-           "overlap": bool(not args.reference and not args.no_overlap), "flat_bucket": bool(args.flat_bucket),
+           "overlap": bool(not args.reference and not args.no_overlap), "flat_bucket": bool(args.flat_bucket), "coalesce": bool(args.coalesce),
            "replicas_identical": bool(torch.equal(lo, hi))}
     if rank == 0:
         print(json.dumps(out), flush=True)
