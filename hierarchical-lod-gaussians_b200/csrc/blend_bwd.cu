@@ -10,8 +10,20 @@
 // splat instead of the end of its range.
 #include "state.cuh"
 #include <cstdlib>
+#ifndef LODGS_LOD_CUT_DEFAULT
+#define LODGS_LOD_CUT_DEFAULT 0
+#endif
 
 namespace lodgs {
+
+// LOD-mode alpha cut-off switch (LODGS_LOD_CUT, see blend_pair2): 0 = every pair goes through the exponentials
+__constant__ int c_lod_cut = LODGS_LOD_CUT_DEFAULT;
+static int set_lod_cut() {
+    const char* e = getenv("LODGS_LOD_CUT");
+    const int v = e ? (e[0] != '0') : LODGS_LOD_CUT_DEFAULT;
+    return (int)cudaMemcpyToSymbol(c_lod_cut, &v, sizeof(v));
+}
+
 
 constexpr int BWD_BATCH = 128;
 constexpr int BWD_THREADS = 128;  // 16 x 8 threads, two vertically adjacent pixels each (a warp covers a 16x4 block)
@@ -103,6 +115,10 @@ __device__ __forceinline__ bool bwd_pair2(BwdPix2& p, const unsigned pos, const 
     if (!LOD) {  // certainly below the 1/255 cut (cut-off stored by the preprocess kernel)
         ok0 = ok0 && !(pw0 < q2.z);
         ok1 = ok1 && !(pw1 < q2.z);
+    } else {     // the same cut rebuilt per splat (LOD alpha <= opacity*exp(power) for t in [0,1], kids >= 1; see blend_fwd.cu)
+        const float cut = (c_lod_cut && q2.z >= 0.0f && q2.z <= 1.0f && q2.w > 0.0f && q2.w <= 1.0f) ? -__logf(255.0f * q1.y) - 0.02f : -__builtin_huge_valf();
+        ok0 = ok0 && !(pw0 < cut);
+        ok1 = ok1 && !(pw1 < cut);
     }
     if (!__any_sync(0xffffffffu, ok0 || ok1)) return false;  // warp-uniform: lanes without a contribution ride along with alpha 0
     // ex2.approx.ftz on power * log2(e) instead of the forward's full-range expf: alpha moves by ~1e-7 relative, far inside the
@@ -354,6 +370,8 @@ int launch_blend_bwd(bool lod, bool depth, const ImageState& img, const BinningS
     }
     const size_t smem = sizeof(BwdSmem);
     static const bool tile_id_order = getenv("LODGS_BLEND_TILE_ID_ORDER") != nullptr;  // A/B: CTAs in tile-id order
+    static const int lod_cut_rc = set_lod_cut();
+    if (lod_cut_rc) { set_error("blend: setting the LOD cut-off switch failed"); return LODGS_E_CUDA; }
     const uint32_t* order = tile_id_order ? nullptr : img.tile_order;
 #define LODGS_BWD_ARGS img.ranges, order, recs, bin.point_list, W, H, bg, bg_mult, null_thr, indices, img.final_T, img.n_contrib, dL_dpix, dL_dinvdepth_pix, \
                        dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dinvdepth

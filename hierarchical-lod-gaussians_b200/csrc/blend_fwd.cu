@@ -11,8 +11,20 @@
 // n_contrib — an integer output decided by the alpha<1/255 and T<1e-4 tests — and the image are bit-identical.
 #include "state.cuh"
 #include <cstdlib>
+#ifndef LODGS_LOD_CUT_DEFAULT
+#define LODGS_LOD_CUT_DEFAULT 0
+#endif
 
 namespace lodgs {
+
+// LOD-mode alpha cut-off switch (LODGS_LOD_CUT, see blend_pair2): 0 = every pair goes through the exponentials
+__constant__ int c_lod_cut = LODGS_LOD_CUT_DEFAULT;
+static int set_lod_cut() {
+    const char* e = getenv("LODGS_LOD_CUT");
+    const int v = e ? (e[0] != '0') : LODGS_LOD_CUT_DEFAULT;
+    return (int)cudaMemcpyToSymbol(c_lod_cut, &v, sizeof(v));
+}
+
 
 constexpr int BLEND_BATCH = 256;
 constexpr int BLEND_THREADS = 128;  // 16 x 8 threads, two vertically adjacent pixels each: a warp covers a 16x4 pixel block
@@ -50,6 +62,14 @@ __device__ __forceinline__ void blend_pair2(PixState2& p, unsigned& done0, unsig
     if (!LOD) {  // alpha is certainly below 1/255 (cut-off precomputed per splat, see preprocess_one)
         ok0 = ok0 && !(pw0 < q2.z);
         ok1 = ok1 && !(pw1 < q2.z);
+    } else {
+        // Both spare record slots carry t and 1/kids here, so the cut-off is rebuilt per splat: the LOD alpha
+        // t*a + (1-t)*(1 - (1-a)^(1/kids)) never exceeds a = opacity*exp(power) for t in [0,1] and kids >= 1, and
+        // power < -log(255*opacity) - 0.02 puts a 2 % below 1/255 (the approximations of __logf/__powf move it by ~1e-6), so
+        // exactly pairs the alpha test below would drop are dropped here — before two exponentials and two powers.
+        const float cut = (c_lod_cut && q2.z >= 0.0f && q2.z <= 1.0f && q2.w > 0.0f && q2.w <= 1.0f) ? -__logf(255.0f * q1.y) - 0.02f : -__builtin_huge_valf();
+        ok0 = ok0 && !(pw0 < cut);
+        ok1 = ok1 && !(pw1 < cut);
     }
     if (!ok0 && !ok1) return;
     const f2 al = mul2(bc(q1.y), pk(expf(pw0), expf(pw1)));
@@ -256,6 +276,8 @@ int launch_blend_fwd(bool lod, bool depth, const ImageState& img, const BinningS
     dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1), block(TILE_X, TILE_Y, 1);
     const bool hs = seen != nullptr;
     static const bool tile_id_order = getenv("LODGS_BLEND_TILE_ID_ORDER") != nullptr;  // A/B: CTAs in tile-id order
+    static const int lod_cut_rc = set_lod_cut();
+    if (lod_cut_rc) { set_error("blend: setting the LOD cut-off switch failed"); return LODGS_E_CUDA; }
     const uint32_t* order = tile_id_order ? nullptr : img.tile_order;
     if (lod && depth) return launch_blend_seen<true, true>(hs, grid, block, s, img.ranges, order, recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
     if (lod && !depth) return launch_blend_seen<true, false>(hs, grid, block, s, img.ranges, order, recs, bin.point_list, W, H, bg, img.final_T, img.n_contrib, out_color, out_invdepth, seen);
