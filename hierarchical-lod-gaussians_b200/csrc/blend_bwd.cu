@@ -11,12 +11,12 @@
 #include "state.cuh"
 #include <cstdlib>
 #ifndef LODGS_LOD_CUT_DEFAULT
-#define LODGS_LOD_CUT_DEFAULT 0
+#define LODGS_LOD_CUT_DEFAULT 1
 #endif
 
 namespace lodgs {
 
-// LOD-mode alpha cut-off switch (LODGS_LOD_CUT, see blend_pair2): 0 = every pair goes through the exponentials
+// LOD-mode alpha cut-off switch (see blend_pair2); LODGS_LOD_CUT=0 in the environment sends every pair through the exponentials (A/B)
 __constant__ int c_lod_cut = LODGS_LOD_CUT_DEFAULT;
 static int set_lod_cut() {
     const char* e = getenv("LODGS_LOD_CUT");
