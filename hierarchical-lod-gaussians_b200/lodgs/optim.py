@@ -1,8 +1,8 @@
 """Optimizers of the hot path, same call surface as the reference's, one fused kernel launch per parameter tensor.
 
 * `Adam` mirrors scene/OurAdam.py `Adam.step(relevant)` (:106-176 -> `_single_tensor_adam`, :251-354): Adam with bias
-  correction applied only to the rows listed in `relevant` (i64 indices into dim 0); `relevant=None` updates all rows
-  (`_single_tensor_adam2`, :357-452). The reference does ~10 eager elementwise kernels plus index gathers/scatters per
+  correction applied only to the rows listed in `relevant` (i64 indices into dim 0); an EMPTY list (or None) updates all
+  rows (`_single_tensor_adam2`, :357-452, chosen by `relevant.size(0) == 0` at :214). The reference does ~10 eager elementwise kernels plus index gathers/scatters per
   group; here it is `lodgs_adam_step` (csrc/adam.cu), 28 B per updated scalar.
 * `SparseGaussianAdam` mirrors AR/alt_gaussian_rasterization/__init__.py:246-271 (`_C.adamUpdate`, AR/cuda_rasterizer/
   adam.cu:9-38): rows masked by a bool visibility tensor, no bias correction.
@@ -31,6 +31,8 @@ class Adam(torch.optim.Adam):
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
+        if relevant is not None and relevant.size(0) == 0:
+            relevant = None   # an empty list means "every row" in the reference (OurAdam.py:214 -> _single_tensor_adam2)
         if relevant is not None:
             relevant = relevant.to(torch.int64).contiguous()
         todo, keep = [], []
@@ -58,7 +60,7 @@ class Adam(torch.optim.Adam):
                              p.numel() // max(rows, 1), float(group["lr"]), float(beta1), float(beta2), float(group["eps"]),
                              int(state["step"].item())))
         n = len(todo)
-        if n == 0 or (relevant is not None and relevant.numel() == 0):   # the steps above are still counted, as in the reference
+        if n == 0:
             return loss
         cols = list(zip(*todo))
         P4 = C.c_void_p * n
