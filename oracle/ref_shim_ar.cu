@@ -12,6 +12,7 @@
 #include "cuda_rasterizer/rasterizer.h"
 #include "cuda_rasterizer/adam.h"
 #include "cuda_rasterizer/utils.h"
+#include "cuda_rasterizer/rasterizer_impl.h"
 
 namespace {
 struct Buf {
@@ -68,6 +69,25 @@ REF_API void refar_relocation(int P, float* opacity_old, float* scale_old, int* 
                               float* scale_new) {
     UTILS::ComputeRelocation(P, opacity_old, scale_old, N, binoms, n_max, opacity_new, scale_new);
 }
+
+// Device pointers into the reference's own scratch buffers of the LAST forward (layouts from its fromChunk functions,
+// AR/cuda_rasterizer/rasterizer_impl.cu:249-305), for tests/gpu_diag_ar.py: out[0..] = ranges, point_list, n_contrib, max_contrib,
+// bucket_offsets, bucket_to_tile, sampled_T, means2D, conic_opacity, rgb, accum_alpha (final T), sampled_ar, pixel_colors, depths.
+REF_API void refar_internals(int P, int W, int H, int R, int B, void** out) {
+    char* c = g_geom.p;
+    auto geom = CudaRasterizer::GeometryState::fromChunk(c, P);
+    c = g_bin.p;
+    auto bin = CudaRasterizer::BinningState::fromChunk(c, R);
+    c = g_img.p;
+    auto img = CudaRasterizer::ImageState::fromChunk(c, (size_t)W * H);
+    c = g_sample.p;
+    auto smp = CudaRasterizer::SampleState::fromChunk(c, B);
+    out[0] = img.ranges; out[1] = bin.point_list; out[2] = img.n_contrib; out[3] = img.max_contrib; out[4] = img.bucket_offsets;
+    out[5] = smp.bucket_to_tile; out[6] = smp.T; out[7] = geom.means2D; out[8] = geom.conic_opacity; out[9] = geom.rgb;
+    out[10] = img.accum_alpha; out[11] = smp.ar; out[12] = img.pixel_colors; out[13] = geom.depths;
+}
+
+REF_API int refar_copy(void* dst, const void* src, size_t nbytes) { return (int)cudaMemcpy(dst, src, nbytes, cudaMemcpyDeviceToDevice); }
 
 REF_API void refar_free(void) {
     for (Buf* b : {&g_geom, &g_bin, &g_img, &g_sample}) {

@@ -1,88 +1,141 @@
-"""Diagnostic (not a test): per-gradient relative L2 of the alt-rasterizer surface against the reference AR kernels."""
-import sys, os
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
-import conftest  # noqa: F401  (sets sys.path)
-import torch
-import test_gpu_alt_rasterizer as T
-from oracle import refshim_ar
-from alt_gaussian_rasterization import _C
+"""Diagnostic (not a test): WHERE does the reference's per-Gaussian backward (AR/cuda_rasterizer/backward.cu:451-656) lose
+contributions? For every Gaussian whose colour gradient differs between the reference's backward and this library's, the
+script replays the reference's OWN sorted lists (its point_list / ranges / n_contrib / max_contrib / sampled_T, read from its scratch
+buffers through refar_internals) in torch, attributes dL_dcolor to the individual (tile, list position) instances and reports which
+instances the reference's result is missing and what state the reference kernel saw for them.
 
-for name in ("wide",):
-    for aa in (True,):
-        for zero_depth in (False, True):
+    python tests/gpu_diag_ar.py [case ...]        (GPU box)
+"""
+import ctypes as C
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+import conftest  # noqa: F401,E402  (sets sys.path)
+import torch  # noqa: E402
+
+import test_gpu_alt_rasterizer as T  # noqa: E402
+from alt_gaussian_rasterization import _C  # noqa: E402
+from oracle import refshim_ar  # noqa: E402
+
+
+def view(ptr, n, dtype):
+    """Copy of n elements of device memory at ptr (the reference's scratch buffers) as a torch tensor."""
+    t = torch.empty(n, dtype=dtype, device="cuda")
+    L = refshim_ar.lib()
+    L.refar_copy.restype = C.c_int
+    rc = L.refar_copy(C.c_void_p(t.data_ptr()), C.c_void_p(ptr), C.c_size_t(n * t.element_size()))
+    assert rc == 0, rc
+    return t
+
+
+def internals(rf, W, H):
+    out = (C.c_void_p * 16)()
+    L = refshim_ar.lib()
+    L.refar_internals.restype = None
+    L.refar_internals(C.c_int(rf["P"]), C.c_int(W), C.c_int(H), C.c_int(rf["R"]), C.c_int(rf["B"]), out)
+    ntiles = ((W + 15) // 16) * ((H + 15) // 16)
+    P, R, B = rf["P"], rf["R"], rf["B"]
+    return {"ranges": view(out[0], ntiles * 2, torch.int32).view(ntiles, 2), "point_list": view(out[1], R, torch.int32),
+            "n_contrib": view(out[2], W * H, torch.int32), "max_contrib": view(out[3], ntiles, torch.int32),
+            "bucket_offsets": view(out[4], ntiles, torch.int32), "bucket_to_tile": view(out[5], B, torch.int32),
+            "sampled_T": view(out[6], B * 256, torch.float32).view(B, 256), "means2D": view(out[7], P * 2, torch.float32).view(P, 2),
+            "conic_opacity": view(out[8], P * 4, torch.float32).view(P, 4), "rgb": view(out[9], P * 3, torch.float32).view(P, 3),
+            "final_T": view(out[10], W * H, torch.float32)}
+
+
+def replay_tile(st, t, W, H, dL):
+    """-> (ids [n], weight [n,256] = alpha*T of every (position, pixel) the forward blended, pixel validity [256], pix ids [256])."""
+    gx = (W + 15) // 16
+    ty, tx = divmod(t, gx)
+    lo, hi = (int(x) for x in st["ranges"][t])
+    ids = st["point_list"][lo:hi].long()
+    k = torch.arange(256, device="cuda")
+    px, py = tx * 16 + k % 16, ty * 16 + k // 16
+    valid = (px < W) & (py < H)
+    pid = (py * W + px).clamp(max=W * H - 1)
+    xy, co = st["means2D"][ids], st["conic_opacity"][ids]
+    dx = xy[:, 0:1] - px.float()[None]
+    dy = xy[:, 1:2] - py.float()[None]
+    power = -0.5 * (co[:, 0:1] * dx * dx + co[:, 2:3] * dy * dy) - co[:, 1:2] * dx * dy
+    alpha = torch.minimum(torch.tensor(0.99, device="cuda"), co[:, 3:4] * torch.exp(power))
+    ok = (power <= 0) & (alpha >= 1.0 / 255.0)
+    pos = torch.arange(hi - lo, device="cuda")[:, None]
+    blended = ok & (pos < st["n_contrib"][pid][None]) & valid[None]
+    a = torch.where(ok, alpha, torch.zeros_like(alpha))
+    Tb = torch.cumprod(torch.cat([torch.ones(1, 256, device="cuda"), 1 - a[:-1]], 0), 0)   # T before each position
+    w = torch.where(blended, a * Tb, torch.zeros_like(a))
+    return ids, w, Tb, valid, pid
+
+
+def main(names):
+    for name in names:
+        for aa in (True,):
             sc, cam, bg, dL, dLi = T._scene(name)
-            if zero_depth:
-                dLi = torch.zeros_like(dLi)
+            W, H = cam["W"], cam["H"]
             rf = refshim_ar.forward(sc, cam, bg, aa)
             rg = refshim_ar.backward(sc, cam, bg, rf, dL, dLi, aa)
+            st = internals(rf, W, H)
             e = torch.empty(0, device="cuda")
             out = _C.rasterize_gaussians(bg, sc["means3D"], e, sc["opacities"], sc["scales"], sc["rotations"], 1.0, e, cam["viewmatrix"],
-                                         cam["projmatrix"], cam["tanfovx"], cam["tanfovy"], cam["H"], cam["W"], sc["dc"], sc["shs_rest"],
-                                         sc["sh_degree"], cam["campos"], False, aa, False)
+                                         cam["projmatrix"], cam["tanfovx"], cam["tanfovy"], H, W, sc["dc"], sc["shs_rest"], sc["sh_degree"],
+                                         cam["campos"], False, aa, False)
             rendered, nb, color, invdepth, radii, geom, binning, img, sample = out
             grads = _C.rasterize_gaussians_backward(bg, sc["means3D"], radii, e, sc["opacities"], sc["scales"], sc["rotations"], 1.0, e,
                                                     cam["viewmatrix"], cam["projmatrix"], cam["tanfovx"], cam["tanfovy"], dL, sc["dc"],
                                                     sc["shs_rest"], dLi, sc["sh_degree"], cam["campos"], geom, rendered, binning, img, nb,
                                                     sample, aa, False)
-            names = ("dL_dmean2D", "dL_dcolor", "dL_dopacity", "dL_dmean3D", "dL_dcov3D", "dL_ddc", "dL_dsh", "dL_dscale", "dL_drot")
-            print("case", name, "aa", aa, "zero_depth", zero_depth, "R", rendered, rf["R"], "img err", float((color - rf["color"]).abs().max()))
-            for n, g in zip(names, grads):
-                print("   %-12s rel_l2 %.3e   |ref| %.3e |mine| %.3e" % (n, T.rel_l2(g, rg[n]), float(rg[n].norm()), float(g.norm())))
-            d = (grads[0] - rg["dL_dmean2D"])
-            i = int(d.abs().sum(1).argmax())
-            op = sc["opacities"].reshape(-1)
-            bad = (d.abs().sum(1) > 1e-3 * rg["dL_dmean2D"].abs().sum(1).max())
-            print("   bad rows", int(bad.sum()), "opacity of bad rows (min/mean/max)", float(op[bad].min()), float(op[bad].mean()), float(op[bad].max()),
-                  "radii", radii[bad][:10].tolist())
-            print("   worst row", i, grads[0][i].tolist(), rg["dL_dmean2D"][i].tolist(), "radius", int(radii[i]))
+            mine_c, ref_c = grads[1], rg["dL_dcolor"]
+            cdiff = (mine_c - ref_c).abs().sum(1)
+            dropped = cdiff > 1e-3 * ref_c.abs().sum(1) + 1e-12
+            rows = dropped.nonzero().reshape(-1).tolist()
+            print("case %s aa %s: visible %d, Gaussians whose dL_dcolor differs %d, R %d, B %d" % (name, aa, int((radii > 0).sum()), len(rows),
+                                                                                                    rf["R"], rf["B"]))
+            ntiles = st["ranges"].size(0)
+            lens = (st["ranges"][:, 1] - st["ranges"][:, 0])
+            print("   tile list lengths: max %d, tiles with > 256 entries %d of %d; max_contrib max %d" %
+                  (int(lens.max()), int((lens > 256).sum()), ntiles, int(st["max_contrib"].max())))
+            dLf = dL.reshape(3, -1)
+            cache = {}
+            summary = {"missing_instances": 0, "pos_lt_256": 0, "pos_ge_256": 0}
+            for r in rows[:40]:
+                # instances of r in the reference's lists
+                hits = (st["point_list"] == r).nonzero().reshape(-1)
+                inst = []
+                for h in hits.tolist():
+                    t = int(((st["ranges"][:, 0] <= h) & (h < st["ranges"][:, 1])).nonzero().reshape(-1)[0])
+                    if t not in cache:
+                        cache[t] = replay_tile(st, t, W, H, dL)
+                    ids, w, Tb, valid, pid = cache[t]
+                    pos = h - int(st["ranges"][t, 0])
+                    contrib = (w[pos][None] * dLf[:, pid]).sum(1)          # [3]
+                    inst.append((t, pos, contrib))
+                total = sum(c for _, _, c in inst) if inst else torch.zeros(3, device="cuda")
+                miss = []
+                for t, pos, c in inst:
+                    if float(c.abs().sum()) > 0 and float((total - c - ref_c[r]).abs().sum()) < 0.02 * float(c.abs().sum()):
+                        miss.append((t, pos))
+                print("   gaussian %d: mine %s | replay of the reference's lists %s | reference backward %s" %
+                      (r, ["%.3e" % x for x in mine_c[r].tolist()], ["%.3e" % x for x in total.tolist()], ["%.3e" % x for x in ref_c[r].tolist()]))
+                for t, pos, c in inst:
+                    lo, hi = (int(x) for x in st["ranges"][t])
+                    bbm = 0 if t == 0 else int(st["bucket_offsets"][t - 1])
+                    b = bbm + pos // 32
+                    ids, w, Tb, valid, pid = cache[t]
+                    # what the kernel read for the bucket: sampled_T of the pixels that blend this instance vs the replayed T at the bucket start
+                    pix = (w[pos] > 0).nonzero().reshape(-1)
+                    sT = st["sampled_T"][b][pix] if b < st["sampled_T"].size(0) else None
+                    rT = Tb[(pos // 32) * 32][pix]
+                    mism = int(((sT - rT).abs() > 1e-4 * rT.abs() + 1e-9).sum()) if sT is not None else -1
+                    print("      tile %d pos %d of %d (bucket %d, lane %d) max_contrib %d bucket_to_tile %s  contributes %s  blending pixels %d, "
+                          "sampled_T != replayed T at bucket start for %d of them%s" %
+                          (t, pos, hi - lo, pos // 32, pos % 32, int(st["max_contrib"][t]), int(st["bucket_to_tile"][b]) if b < st["bucket_to_tile"].numel() else None,
+                           ["%.3e" % x for x in c.tolist()], pix.numel(), mism, "   <-- MISSING in the reference backward" if (t, pos) in miss else ""))
+                    if (t, pos) in miss:
+                        summary["missing_instances"] += 1
+                        summary["pos_lt_256" if pos < 256 else "pos_ge_256"] += 1
+            print("   summary", summary)
 
-# ---- where do the rows the reference leaves at zero sit in their tile lists?
-import ctypes as C
-import lodgs
-sc, cam, bg, dL, dLi = T._scene("wide")
-rf = refshim_ar.forward(sc, cam, bg, True)
-rg1 = refshim_ar.backward(sc, cam, bg, rf, dL, dLi, True)
-rg2 = refshim_ar.backward(sc, cam, bg, rf, dL, dLi, True)
-print("reference deterministic:", all(torch.equal(rg1[k], rg2[k]) for k in rg1))
-e = torch.empty(0, device="cuda")
-out = _C.rasterize_gaussians(bg, sc["means3D"], e, sc["opacities"], sc["scales"], sc["rotations"], 1.0, e, cam["viewmatrix"],
-                             cam["projmatrix"], cam["tanfovx"], cam["tanfovy"], cam["H"], cam["W"], sc["dc"], sc["shs_rest"],
-                             sc["sh_degree"], cam["campos"], False, True, False)
-rendered, nb, color, invdepth, radii, geom, binning, img, sample = out
-grads = _C.rasterize_gaussians_backward(bg, sc["means3D"], radii, e, sc["opacities"], sc["scales"], sc["rotations"], 1.0, e,
-                                        cam["viewmatrix"], cam["projmatrix"], cam["tanfovx"], cam["tanfovy"], dL, sc["dc"],
-                                        sc["shs_rest"], dLi, sc["sh_degree"], cam["campos"], geom, rendered, binning, img, nb, sample, True, False)
-W, H = cam["W"], cam["H"]
-o = (C.c_size_t * 3)(); lodgs.lib.lodgs_image_layout(W, H, o)
-ntiles = ((W + 15) // 16) * ((H + 15) // 16)
-ranges = img[o[2]:o[2] + ntiles * 8].view(torch.int32).reshape(ntiles, 2).cpu()
-ncon = img[o[1]:o[1] + W * H * 4].view(torch.int32).reshape(H, W).cpu()
-b = (C.c_size_t * 5)(); lodgs.lib.lodgs_binning_layout(rendered, b)
-pl = binning[b[3]:b[3] + rendered * 4].view(torch.int32).cpu()
-zero_ref = (rg1["dL_dmean2D"].abs().sum(1) == 0) & (grads[0].abs().sum(1) > 0)
-rows = zero_ref.nonzero().reshape(-1).cpu().tolist()
-print("rows zero in the reference but not here:", len(rows))
-gx = (W + 15) // 16
-for r in rows[:12]:
-    info = []
-    for t in range(ntiles):
-        lo, hi = int(ranges[t, 0]), int(ranges[t, 1])
-        seg = pl[lo:hi]
-        pos = (seg == r).nonzero().reshape(-1)
-        if pos.numel():
-            ty, tx = divmod(t, gx)
-            mc = int(ncon[ty * 16:(ty + 1) * 16, tx * 16:(tx + 1) * 16].max())
-            info.append((t, int(pos[0]), hi - lo, mc))
-    print("  gaussian", r, "radius", int(radii[r]), "(tile, position in list, list length, max n_contrib of tile):", info)
 
-# ---- is the reference's zero right? finite difference THROUGH THE REFERENCE FORWARD on the DC colour (the loss is linear in it)
-for r in rows[:4]:
-    base = float((rf["color"].double() * dL.double()).sum() + (rf["invdepth"].double() * dLi.double()).sum())
-    sc2 = dict(sc)
-    dc2 = sc["dc"].clone()
-    dc2[r, 0, 0] += 1.0
-    sc2["dc"] = dc2
-    f2 = refshim_ar.forward(sc2, cam, bg, True)
-    pert = float((f2["color"].double() * dL.double()).sum() + (f2["invdepth"].double() * dLi.double()).sum())
-    print("  gaussian", r, "dL/d dc[0] by finite difference through the reference forward: %.6e   reference backward: %.6e   here: %.6e"
-          % (pert - base, float(rg1["dL_ddc"][r, 0, 0]), float(grads[5][r, 0, 0])))
+if __name__ == "__main__":
+    main(sys.argv[1:] or ["wide"])

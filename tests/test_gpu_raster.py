@@ -90,7 +90,9 @@ def test_against_cpu_oracle(name):
 
 
 @pytest.mark.skipif(not refshim.available(), reason="oracle/_ref not built")
-@pytest.mark.parametrize("P,W,H,lod", [(50000, 640, 360, False), (30000, 500, 300, True), (200000, 1280, 720, False)])
+@pytest.mark.parametrize("P,W,H,lod", [(50000, 640, 360, False), (30000, 500, 300, True), (200000, 1280, 720, False),
+                                       (1_000_000, 1920, 1080, False),    # BASELINE configs[1] at its full size
+                                       (1_000_000, 1920, 1080, True)])    # 1 M Gaussians, 500 k-entry index list with parents, t, kids
 def test_side_by_side_with_reference_build(P, W, H, lod):
     cam_np = synth.make_camera(W=W, H=H, fx=1200.0 * W / 1920, fy=1200.0 * W / 1920)
     sc = cu(synth.make_gaussians(P, seed=P % 97, tanfovx=cam_np["tanfovx"], tanfovy=cam_np["tanfovy"]))
