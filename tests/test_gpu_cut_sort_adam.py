@@ -127,12 +127,15 @@ def test_sort_structured_tile_depth_keys():
 
 
 def _check_against(res, want, rtol_p=2e-6):
+    from oracle.ouradam import LRS
     for k, (p, m, v) in res.items():
         wp, wm, wv = want[k]
         # rtol 1e-6 plus 2e-7 of the tensor's scale: 0.9 m + 0.1 g cancels for a few elements, and fused vs separate rounding shows there
         assert torch.allclose(m.cpu(), wm, rtol=1e-6, atol=2e-7 * float(wm.abs().max())), k
         assert torch.allclose(v.cpu(), wv, rtol=1e-6, atol=2e-7 * float(wv.abs().max())), k
-        assert torch.allclose(p.cpu(), wp, rtol=rtol_p, atol=1e-9), k
+        # a step moves a parameter by lr * O(1); its rounding (sqrt, divide, fused multiply-add) differs by ~1e-6 of the STEP, which for
+        # parameters near zero is more than 2e-6 of the value
+        assert torch.allclose(p.cpu(), wp, rtol=rtol_p, atol=1e-5 * LRS[k]), k
 
 
 @pytest.mark.parametrize("rows,eps,seed", [(257, 1e-15, 11), (257, 1e-8, 12)])

@@ -98,7 +98,7 @@ def test_gradcheck_against_finite_differences():
 
 
 def test_hierarchical_frame_in_kernel_lod_matches_python_interpolation():
-    """render_hierarchy.py:48-82: cut -> weights -> render_post; interp_python=False (kernel LOD) == interp_python=True."""
+    """render_hierarchy.py:48-82: cut -> weights -> render_post; interp_kernel=True (in-kernel LOD) == interp_python=True."""
     from gaussian_hierarchy import _C as gh
     from gaussian_renderer import render_post
     rng = np.random.default_rng(0)
@@ -131,10 +131,76 @@ def test_hierarchical_frame_in_kernel_lod_matches_python_interpolation():
         a = render_post(vc, pc, Pipe(), bg, render_indices=ri[:K], parent_indices=pi_safe, interpolation_weights=ts[:K],
                         num_node_siblings=kids[:K], interp_python=True)["render"]
         b = render_post(vc, pc, Pipe(), bg, render_indices=ri[:K], parent_indices=pi[:K], interpolation_weights=ts[:K],
+                        num_node_siblings=kids[:K], interp_kernel=True)["render"]
+        # interp_python=False is the reference's plain gather (GR:338-348): no interpolation, no LOD alpha. It equals rendering the
+        # gathered Gaussians directly.
+        c = render_post(vc, pc, Pipe(), bg, render_indices=ri[:K], parent_indices=pi[:K], interpolation_weights=ts[:K],
                         num_node_siblings=kids[:K], interp_python=False)["render"]
+        from gaussian_renderer import render_coarse
+        d = render_coarse(vc, pc, Pipe(), bg, indices=ri[:K].long())["render"].clamp(0, 1)
+    assert torch.equal(c, d)
+    assert float((c - a).abs().max()) > 1e-3     # un-interpolated differs from interpolated: the modes are really different
     assert float(a.max()) > 0.05
     # torch's lerp rounds differently from the in-kernel one: nearly coincident depths may swap order at isolated pixels
     assert float((a - b).abs().max()) <= 1e-2 and float((a - b).abs().mean()) <= 1e-4
+
+
+def test_render_post_gradients_follow_reference_semantics():
+    """interp_python=False: gradients flow to the gathered rows' own parameters (the reference gathers in torch, GR:338-345); nothing is
+    redirected to parents and opacity / scale / rotation gradients of the rendered rows are non-zero."""
+    from gaussian_renderer import render_post
+    sc, cam, bg, _, _, _ = cases.make_case("small")
+    pc, vc = FakeModel(sc), FakeCam(cam)
+    P = pc.get_xyz.size(0)
+    ri = torch.arange(0, P, 2, device="cuda", dtype=torch.int32)
+    par = torch.arange(1, P, 2, device="cuda", dtype=torch.int32)
+    ts = torch.full((ri.numel(),), 0.5, device="cuda")
+    kids = torch.full((ri.numel(),), 2, device="cuda", dtype=torch.int32)
+    out = render_post(vc, pc, Pipe(), torch.from_numpy(bg).cuda(), render_indices=ri, parent_indices=par, interpolation_weights=ts,
+                      num_node_siblings=kids, interp_python=False)
+    out["render"].sum().backward()
+    odd = torch.arange(1, P, 2, device="cuda")
+    for p in (pc._xyz, pc._opacity, pc._scaling, pc._rotation, pc._features):
+        assert float(p.grad[odd].abs().sum()) == 0.0          # parents untouched
+        assert float(p.grad[ri.long()].abs().sum()) > 0.0
+    assert out["visibility_filter"].dtype == torch.bool and out["visibility_filter"].numel() == ri.numel()
+
+
+def test_convert_shs_python_and_cov3d_python_paths():
+    """pipe.convert_SHs_python / pipe.compute_cov3D_python (GR:96-121): colours from the torch SH evaluation equal the in-kernel ones."""
+    from gaussian_renderer import render
+    sc, cam, bg, _, _, _ = cases.make_case("small")
+    pc, vc = FakeModel(sc), FakeCam(cam)
+
+    class P2(Pipe):
+        convert_SHs_python = True
+    with torch.no_grad():
+        a = render(vc, pc, Pipe(), torch.from_numpy(bg).cuda())["render"]
+        b = render(vc, pc, P2(), torch.from_numpy(bg).cuda())["render"]
+    assert float((a - b).abs().max()) <= 1e-4
+
+
+def test_render_on_disk_vanilla_and_occlusion_cull():
+    from gaussian_renderer import occlusion_cull, render_on_disk, render_vanilla
+    sc, cam, bg, _, _, _ = cases.make_case("small")
+    pc, vc = FakeModel(sc), FakeCam(cam)
+    bgt = torch.from_numpy(bg).cuda()
+    with torch.no_grad():
+        out = render_on_disk(vc, pc.get_xyz, pc.get_opacity, pc.get_scaling, pc.get_rotation, pc.get_features, Pipe(), bgt)
+        assert out["seen"].shape == (pc.get_xyz.size(0),) and 0 < int(out["seen"].sum()) <= pc.get_xyz.size(0)
+        f = pc.get_features
+        van = render_vanilla(vc, pc.get_xyz, pc.get_opacity, pc.get_scaling, pc.get_rotation, f[:, :1].contiguous(), f[:, 1:].contiguous(),
+                             Pipe(), bgt, anti_aliasing=True)
+        assert van["render"].shape == out["render"].shape and float((van["render"] - out["render"]).abs().max()) <= 2e-2
+    pc._opacity = torch.logit(pc.get_opacity.detach().clamp(1e-4, 1 - 1e-4))
+    pc._features_dc, pc._features_rest = f[:, :1].detach(), f[:, 1:].detach()
+    pc.opacity_activation, pc.scaling_activation = torch.sigmoid, torch.exp
+    pc.rotation_activation = torch.nn.functional.normalize
+    idx = torch.arange(0, 600, 3, device="cuda")
+    seen = occlusion_cull(idx, pc, vc, Pipe(), bgt)
+    assert seen.dtype == torch.bool and seen.device.type == "cpu" and seen.numel() == idx.numel()
+    full = out["seen"][idx].bool().cpu()
+    assert bool((seen | ~full).all())    # fewer occluders: whatever was seen among all Gaussians is still seen in the subset
 
 
 def test_smoke_entry():
