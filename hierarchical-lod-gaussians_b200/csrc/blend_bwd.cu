@@ -360,13 +360,14 @@ int launch_blend_bwd(bool lod, bool depth, const ImageState& img, const BinningS
                      const float* bg, float bg_mult, float null_thr, const int32_t* indices, const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic,
                      float* dL_dopacity, float* dL_dcolor, float* dL_dinvdepth, cudaStream_t s) {
     dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1), block(BWD_THREADS, 1, 1);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static std::atomic<bool> attr_set[MAX_DEVICES];
+    const int dslot = device_slot();
+    if (!attr_set[dslot].load(std::memory_order_acquire)) {
         LODGS_CUDA(cudaFuncSetAttribute(blend_bwd_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmem)));
         LODGS_CUDA(cudaFuncSetAttribute(blend_bwd_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmem)));
         LODGS_CUDA(cudaFuncSetAttribute(blend_bwd_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmem)));
         LODGS_CUDA(cudaFuncSetAttribute(blend_bwd_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmem)));
-        attr_set = true;
+        attr_set[dslot].store(true, std::memory_order_release);
     }
     const size_t smem = sizeof(BwdSmem);
     static const bool tile_id_order = getenv("LODGS_BLEND_TILE_ID_ORDER") != nullptr;  // A/B: CTAs in tile-id order

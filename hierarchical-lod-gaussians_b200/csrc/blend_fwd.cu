@@ -251,10 +251,11 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* _
 template <bool LOD, bool DEPTH, bool SEEN>
 static int launch_blend_one(dim3 grid, cudaStream_t s, const uint2* ranges, const uint32_t* order, const SplatRec* recs, const uint32_t* point_list, int W, int H,
                             const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_invdepth, int32_t* seen) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static std::atomic<bool> attr_set[MAX_DEVICES];
+    const int dslot = device_slot();
+    if (!attr_set[dslot].load(std::memory_order_acquire)) {
         LODGS_CUDA(cudaFuncSetAttribute(blend_fwd_kernel<LOD, DEPTH, SEEN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BlendSmem)));
-        attr_set = true;
+        attr_set[dslot].store(true, std::memory_order_release);
     }
     blend_fwd_kernel<LOD, DEPTH, SEEN><<<grid, BLEND_THREADS, sizeof(BlendSmem), s>>>(ranges, order, recs, point_list, W, H, bg, final_T, n_contrib,
                                                                                   out_color, out_invdepth, seen);

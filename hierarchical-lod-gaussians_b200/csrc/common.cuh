@@ -1,5 +1,6 @@
 // common.cuh — shared helpers for the lodgs kernels (sm_100a only).
 #pragma once
+#include <atomic>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -21,6 +22,15 @@ void prof_mark(const char* name);
 // in flight. publish_words enqueues a one-thread kernel copying n <= 8 ints from `src_dev` and records an event;
 // wait_words blocks the host on that event and returns the host copy (thread-local, valid until the next publish).
 int publish_words(const int32_t* src_dev, int n, cudaStream_t s);
+// One-time per-DEVICE setup (function attributes, occupancy queries and events belong to a device, and a process may drive several):
+// slot of the current device for the small per-device tables below; the tables are atomics, so concurrent host threads are safe
+// (setting an attribute twice is harmless).
+constexpr int MAX_DEVICES = 64;
+static inline int device_slot() {
+    int d = 0;
+    if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= MAX_DEVICES) d = 0;
+    return d;
+}
 const int32_t* wait_words();
 
 #define LODGS_CUDA(call)                                              \

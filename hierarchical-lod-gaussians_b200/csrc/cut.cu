@@ -352,6 +352,17 @@ __global__ void cut_check_monotone_kernel(const int32_t* __restrict__ nodes, con
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N) return;
     int parent = __ldg(nodes + (size_t)i * 7 + 1);
+    // child blocks must not overlap: every member of this node's block [start_children, +count_children) names THIS node as its
+    // parent (a node listed by two parents would enter the frontier twice and could overflow its N entries)
+    {
+        int cs = __ldg(nodes + (size_t)i * 7 + 5), cc = __ldg(nodes + (size_t)i * 7 + 6);
+        if (cc > 0) {
+            if (cs < 0 || (long long)cs + cc > N) hdr->monotone = 0;
+            else
+                for (int c = cs; c < cs + cc; c++)
+                    if (__ldg(nodes + (size_t)c * 7 + 1) != i) { hdr->monotone = 0; break; }
+        }
+    }
     if (parent < 0) {
         if (i != 0) hdr->monotone = 0;  // the traversal starts from node 0 as the single root
         return;
@@ -484,18 +495,22 @@ extern "C" int lodgs_expand_to_size(const int32_t* nodes, const float* boxes, in
     } else {
         LODGS_CUDA(cudaMemsetAsync(ws, 0, c.head_bytes, s));
         // One cooperative launch sweeps all levels (grid-wide sync between levels), sized to be co-resident.
-        static int blocks_per_sm = 0, num_sms = 0;
-        if (!blocks_per_sm) {
-            int dev = 0;
+        static std::atomic<int> grid_of[MAX_DEVICES];   // co-resident CTAs of the cooperative launch, per device
+        const int dslot = device_slot();
+        int coop_grid = grid_of[dslot].load(std::memory_order_acquire);
+        if (!coop_grid) {
+            int dev = 0, num_sms = 0, blocks_per_sm = 0;
             LODGS_CUDA(cudaGetDevice(&dev));
             LODGS_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
             LODGS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, cut_traverse_kernel, 256, 0));
             if (blocks_per_sm > 4) blocks_per_sm = 4;
+            coop_grid = num_sms * blocks_per_sm;
+            grid_of[dslot].store(coop_grid, std::memory_order_release);
         }
         const int32_t* a_nodes = nodes; const float* a_boxes = boxes; float a_tau = target_size; const float* a_vp = viewpoint_dev;
         int* fa = c.frontier[0]; int* fb = c.frontier[1]; CutHeader* hdr = c.hdr; unsigned* mk = c.mark; unsigned* ex = c.expanded;
         void* args[] = {&a_nodes, &a_boxes, &a_tau, &a_vp, &fa, &fb, &hdr, &mk, &ex};
-        LODGS_CUDA(cudaLaunchCooperativeKernel((void*)cut_traverse_kernel, dim3(num_sms * blocks_per_sm), dim3(256), args, 0, s));
+        LODGS_CUDA(cudaLaunchCooperativeKernel((void*)cut_traverse_kernel, dim3(coop_grid), dim3(256), args, 0, s));
         LODGS_LAUNCHED("cut_traverse_kernel");
         int nwords = (N + 31) / 32;
         int tiles = (nwords + CUT_BLOCK - 1) / CUT_BLOCK;

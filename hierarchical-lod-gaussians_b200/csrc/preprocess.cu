@@ -336,10 +336,11 @@ extern "C" int lodgs_forward_preprocess_lod(int P, int D, int M, int W, int H, c
     const size_t stage_bytes = (size_t)PRE_BLOCK * M * 12;
     p.staged = (shs && !indices && !parent_indices && p.sh_vec4 && (M * 12) % 16 == 0 && M <= 16) ? 1 : 0;
     if (p.staged) {
-        static size_t attr_smem = 0;
-        if (stage_bytes > attr_smem) {
+        static std::atomic<size_t> attr_smem[MAX_DEVICES];
+        const int dslot = device_slot();
+        if (stage_bytes > attr_smem[dslot].load(std::memory_order_acquire)) {
             LODGS_CUDA(cudaFuncSetAttribute(preprocess_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stage_bytes));
-            attr_smem = stage_bytes;
+            attr_smem[dslot].store(stage_bytes, std::memory_order_release);
         }
     }
     preprocess_fwd_kernel<<<tiles, PRE_BLOCK, p.staged ? stage_bytes : 0, s>>>(p, g);

@@ -387,10 +387,11 @@ int launch_preprocess_bwd(const PreBwdParams& p, cudaStream_t s) {
     const size_t smem = 256 * (size_t)p.M * 12;
     const bool staged = lodgs_backward_overwrites_dsh(p.M, p.indices != nullptr, p.parent_indices != nullptr, p.shs, p.dL_dsh) != 0;
     if (staged) {
-        static size_t attr_smem = 0;
-        if (smem > attr_smem) {
+        static std::atomic<size_t> attr_smem[MAX_DEVICES];
+        const int dslot = device_slot();
+        if (smem > attr_smem[dslot].load(std::memory_order_acquire)) {
             LODGS_CUDA(cudaFuncSetAttribute(preprocess_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            attr_smem = smem;
+            attr_smem[dslot].store(smem, std::memory_order_release);
         }
         preprocess_bwd_kernel<true><<<(p.P + 255) / 256, 256, smem, s>>>(p);
     } else {

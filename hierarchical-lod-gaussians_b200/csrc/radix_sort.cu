@@ -277,10 +277,11 @@ int sort_pairs_device_t(const KeyT* keys_in, const uint32_t* vals_in, KeyT* keys
     SortWs w = sort_from_chunk(ws, n);
     const size_t tiles = sort_tiles(n);
     LODGS_CUDA(cudaMemsetAsync(ws, 0, (size_t)((char*)(w.lookback + (size_t)passes * tiles * SORT_RADIX) - (char*)ws), s));
-    static bool attr_set = false;
-    if (!attr_set) {
+    static std::atomic<bool> attr_set[MAX_DEVICES];
+    const int dslot = device_slot();
+    if (!attr_set[dslot].load(std::memory_order_acquire)) {
         LODGS_CUDA(cudaFuncSetAttribute(sort_onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem<KeyT>)));
-        attr_set = true;
+        attr_set[dslot].store(true, std::memory_order_release);
     }
     int hist_blocks = (int)min((size_t)148 * 4, ((size_t)n + 2047) / 2048);
     sort_histogram_kernel<KeyT><<<hist_blocks, 256, 0, s>>>(keys_in, n, passes, begin_bit, w.hist);

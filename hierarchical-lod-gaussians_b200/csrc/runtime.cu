@@ -54,7 +54,8 @@ int check_cuda(cudaError_t e, const char* what) {
 constexpr int RESULT_WORDS = 8;
 static thread_local int32_t* t_words = nullptr;
 static thread_local int32_t* t_words_dev = nullptr;
-static thread_local cudaEvent_t t_words_ev = nullptr;
+static thread_local cudaEvent_t t_words_evs[MAX_DEVICES] = {};   // an event belongs to the device it was created on
+static thread_local cudaEvent_t t_words_ev = nullptr;             // the one recorded by the last publish
 
 __global__ void publish_words_kernel(const int32_t* __restrict__ src, int32_t* __restrict__ host_words, int n) {
     for (int i = 0; i < n; i++) reinterpret_cast<volatile int32_t*>(host_words)[i] = src[i];
@@ -63,10 +64,10 @@ __global__ void publish_words_kernel(const int32_t* __restrict__ src, int32_t* _
 
 int publish_words(const int32_t* src_dev, int n, cudaStream_t s) {
     if (n < 1 || n > RESULT_WORDS) { set_error("publish_words: bad word count %d", n); return LODGS_E_ARG; }
-    if (!t_words) {
-        LODGS_CUDA(cudaHostAlloc((void**)&t_words, RESULT_WORDS * sizeof(int32_t), cudaHostAllocMapped | cudaHostAllocPortable));
-        LODGS_CUDA(cudaEventCreateWithFlags(&t_words_ev, cudaEventDisableTiming));
-    }
+    if (!t_words) LODGS_CUDA(cudaHostAlloc((void**)&t_words, RESULT_WORDS * sizeof(int32_t), cudaHostAllocMapped | cudaHostAllocPortable));
+    const int dslot = device_slot();
+    if (!t_words_evs[dslot]) LODGS_CUDA(cudaEventCreateWithFlags(&t_words_evs[dslot], cudaEventDisableTiming));
+    t_words_ev = t_words_evs[dslot];
     LODGS_CUDA(cudaHostGetDevicePointer((void**)&t_words_dev, t_words, 0));  // per current device
     publish_words_kernel<<<1, 1, 0, s>>>(src_dev, t_words_dev, n);
     LODGS_LAUNCHED("publish_words_kernel");

@@ -11,11 +11,28 @@ import torch
 from lodgs import LodgsError, check, current_stream, lib, ptr
 
 _ws_cache = {}          # (device index) -> workspace tensor (grown on demand; the reference mallocs per call)
-_traversable = {}       # (nodes ptr, N) -> bool, from lodgs_cut_prepare
-_last_count = {}        # (nodes ptr, N) -> K of the previous cut of this hierarchy (the next frame's is close to it)
+_traversable = {}       # _hier_key -> bool, from lodgs_cut_prepare
+_last_count = {}        # _hier_key -> K of the previous cut of this hierarchy (the next frame's is close to it)
 TRAVERSAL_MIN_NODES = 16_000_000   # below this the single-pass flat kernel is faster than ~25 grid-synchronised levels
 TRAVERSAL_MAX_CUT_FRACTION = 0.10  # traversal time grows with the nodes it visits (about 2 K), the flat pass reads all N at
 #                                    ~3 TB/s: measured cross-over on 33.5 M nodes is K ~ 0.12 N (profiles/r1_cut_flat_ab_s15.json)
+
+
+def _hier_key(nodes, boxes):
+    """Identity of a hierarchy for the two caches: both tensors' storage AND their version counters, so an in-place edit of nodes or
+    boxes, or a new hierarchy that the caching allocator placed at a recycled address, never inherits a stale 'monotone' verdict (a new
+    tensor at an old address starts at version 0, so the entry is additionally dropped when its tensors die: see _remember)."""
+    return (nodes.data_ptr(), boxes.data_ptr(), nodes.size(0), nodes._version, boxes._version)
+
+
+def _remember(cache, key, value, nodes, boxes):
+    import weakref
+    cache[key] = value
+    for t in (nodes, boxes):   # drop the entry with the tensors it describes (address reuse after free)
+        try:
+            weakref.finalize(t, cache.pop, key, None)
+        except TypeError:
+            pass
 
 
 def _workspace(N, dev):
@@ -33,7 +50,7 @@ def prepare_hierarchy(nodes, boxes):
     ws = _workspace(N, nodes.device)
     ok = C.c_int32(0)
     check(lib.lodgs_cut_prepare(ptr(nodes), ptr(boxes), N, ws.data_ptr(), ws.numel(), C.addressof(ok), current_stream()))
-    _traversable[(nodes.data_ptr(), N)] = bool(ok.value)
+    _remember(_traversable, _hier_key(nodes, boxes), bool(ok.value), nodes, boxes)
     return bool(ok.value)
 
 
@@ -46,12 +63,12 @@ def expand_to_size(nodes, boxes, size, viewpoint, viewdir, render_indices, paren
     nodes, boxes = nodes.contiguous(), boxes.contiguous()
     N = nodes.size(0)
     vp = viewpoint.to(device=dev, dtype=torch.float32).contiguous()
-    key = (nodes.data_ptr(), N)
+    key = _hier_key(nodes, boxes)
     if mode is None:
         # traversal only pays on a big hierarchy cut shallowly; the previous frame's K is the predictor (first call: flat)
         mode = 1 if (N >= TRAVERSAL_MIN_NODES and _traversable.get(key, False)
                      and _last_count.get(key, N) < TRAVERSAL_MAX_CUT_FRACTION * N) else 0
-    if mode == 1 and not _traversable.get((nodes.data_ptr(), N), False):
+    if mode == 1 and not _traversable.get(key, False):
         if not prepare_hierarchy(nodes, boxes):
             mode = 0
     ws = _workspace(N, dev)
@@ -61,7 +78,10 @@ def expand_to_size(nodes, boxes, size, viewpoint, viewdir, render_indices, paren
     check(lib.lodgs_expand_to_size(ptr(nodes), ptr(boxes), N, float(size), ptr(vp), ptr(render_indices), ptr(parent_indices),
                                    ptr(nodes_for_render_indices), int(capacity), ws.data_ptr(), ws.numel(), int(mode),
                                    C.addressof(count), current_stream()))
-    _last_count[key] = int(count.value)
+    if key in _last_count:
+        _last_count[key] = int(count.value)
+    else:
+        _remember(_last_count, key, int(count.value), nodes, boxes)
     return int(count.value)
 
 

@@ -92,6 +92,22 @@ def test_cut_edge_cases():
     bad = boxes_np.copy()
     bad[5, 0, 3] = bad[5, 1, 3] = 1e6
     assert gh.prepare_hierarchy(n_t, torch.from_numpy(bad).to(DEV)) is False
+    # a 'monotone' verdict does not survive an in-place edit of the boxes (cache keyed on storage AND version): forced traversal mode
+    # re-checks, falls back to the flat rule and returns the flat rule's cut
+    b_edit = b_t.clone()
+    assert gh.prepare_hierarchy(n_t, b_edit) is True
+    b_edit[5, :, 3] = 1e6
+    v = views[1]
+    tau = np.float32(synth.tau_to_threshold(6, 0.8, 1920))
+    K1, ri1, pi1, ni1 = _cut(n_t, b_edit, tau, v, 1)
+    K0, ri0, pi0, ni0 = _cut(n_t, b_edit, tau, v, 0)
+    want = orc.expand_to_size(nodes_np, b_edit.cpu().numpy(), tau, v)
+    assert K1 == K0 == len(want[0]) and torch.equal(ri1[:K1], ri0[:K0]) and np.array_equal(ni1[:K1].cpu().numpy(), want[2])
+    # overlapping child blocks (a node listed by two parents) are refused too
+    n_bad = nodes_np.copy()
+    inner = np.nonzero(n_bad[:, 6] > 0)[0]
+    n_bad[inner[3], 5] = n_bad[inner[2], 5]           # node inner[3] now claims inner[2]'s children
+    assert gh.prepare_hierarchy(torch.from_numpy(n_bad).to(DEV), b_t.clone()) is False
 
 
 @pytest.mark.parametrize("n,end_bit", [(1, 45), (31, 8), (4096, 45), (4097, 45), (100003, 45), (1 << 20, 64), (777777, 33), (50000, 16)])
