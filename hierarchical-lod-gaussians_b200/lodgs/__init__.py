@@ -59,6 +59,8 @@ _SIGS = {
     "lodgs_dhier_probe": (_i, [C.c_char_p, _p, _p, _p]),
     "lodgs_dhier_load": (_i, [C.c_char_p, _p, _p, _p, _p, _p, _p]),
     "lodgs_dhier_write": (_i, [C.c_char_p, _i, _i, _i, _p, _p, _p, _p, _p, _p]),
+    "lodgs_hier_build_workspace_bytes": (_sz, [_i]),
+    "lodgs_hier_build": (_i, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "lodgs_geom_bytes": (_sz, [_i]),
     "lodgs_image_bytes": (_sz, [_i, _i]),
     "lodgs_binning_bytes": (_sz, [_i]),

@@ -128,6 +128,22 @@ int lodgs_hier_write(const char* filename, int P, int N, const float* pos, const
                      const float* scales, const float* rot, const int32_t* nodes, const float* boxes,
                      int compressed);
 
+/* GPU construction of the hierarchy. Replaces the reference's CPU creator pipeline (GH/mainHierarchyCreator.cpp:149-183):
+ * PointbasedKdTreeGenerator::generate (GH/PointbasedKdTreeGenerator.cpp:16-75), ClusterMerger::merge (GH/ClusterMerger.cpp:23-173),
+ * RotationAligner::align (GH/rotation_aligner.cpp:24-114) and the flattening of Writer::makeDynamicHierarchy (GH/writer.cpp:98-183) /
+ * Writer::makeHierarchy (GH/writer.cpp:21-96, upstream child emission). Inputs are the L leaf Gaussians as the creator holds them after
+ * loading and filtering (GH/loader.cpp:105-124): activated scales, normalised rotations (w,x,y,z), activated opacities, sh_floats SH
+ * coefficients per Gaussian (48 in the creator). Outputs, all on the device, for the N = 2L-1 nodes: one Gaussian per node in PRE-ORDER
+ * (out_pos[N,3], out_rot[N,4], out_scale[N,3] activated, out_opacity[N], out_shs[N,sh_floats]); dyn_nodes[N,6] (HierarchyNode,
+ * GH/types.h:60-67: node i owns Gaussian i; max_side_length = index of the input Gaussian for a leaf, -1 otherwise) and/or the static
+ * format nodes[N,7] + boxes[N,2,4] (GH/types.h:83-92,51-55: node.start = index of its Gaussian, box w = longest side for inner nodes,
+ * 0 for leaves). Any of dyn_nodes / nodes / boxes may be NULL. Equal coordinates at a split fall as a stable sort leaves them
+ * (std::nth_element leaves them unspecified); the eigen-decomposition is a float Jacobi iteration (the reference's is Eigen's). */
+size_t lodgs_hier_build_workspace_bytes(int L);
+int lodgs_hier_build(int L, int sh_floats, const float* pos, const float* scale, const float* rot, const float* opacity,
+                     const float* shs, float* out_pos, float* out_rot, float* out_scale, float* out_opacity, float* out_shs,
+                     int32_t* dyn_nodes, int32_t* nodes, float* boxes, void* ws, size_t ws_bytes, void* stream);
+
 /* Dynamic hierarchy files (host only). Replaces HierarchyLoader::loadDynamic (GH/hierarchy_loader.cpp:129-189) behind
  * gaussian_hierarchy._C.load_dynamic_hierarchy (torch_interface.cpp:43-75) and HierarchyWriter::writeDynamic
  * (GH/hierarchy_writer.cpp:122-168) behind write_dynamic_hierarchy (torch_interface.cpp:107-134). Layout: int P, int sh_degree,
