@@ -17,6 +17,11 @@ FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std
          "-Xcompiler", "-fvisibility=hidden"]
 
 
+# per-file additions: the hierarchy builder mirrors the reference creator's host arithmetic, which a default x86-64 build evaluates
+# without fused multiply-adds, so its kernels are compiled without FMA contraction
+EXTRA = {"hier_build.cu": ["-fmad=false"]}
+
+
 def _sources():
     return sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cpp")))
 
@@ -28,12 +33,13 @@ def _digest():
             h.update(f.encode())
             h.update(fh.read())
     h.update(" ".join(FLAGS).encode())
+    h.update(repr(sorted(EXTRA.items())).encode())
     return h.hexdigest()
 
 
 def _compile(src):
     obj = os.path.join(OBJDIR, os.path.splitext(src)[0] + ".o")
-    cmd = [NVCC] + FLAGS + ["-x", "cu", "-c", os.path.join(CSRC, src), "-o", obj]
+    cmd = [NVCC] + FLAGS + EXTRA.get(src, []) + ["-x", "cu", "-c", os.path.join(CSRC, src), "-o", obj]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed for %s:\n%s\n%s" % (src, r.stdout, r.stderr))

@@ -140,7 +140,8 @@ def skipped_instances(st, W, H):
     nc[:H, :W] = st["n_contrib"].view(H, W)
     true_max = nc.view((H + 15) // 16, 16, gx, 16).permute(0, 2, 1, 3).reshape(nt, 256).max(1).values.long()
     bucket_start = (pos // 32) * 32
-    lost = (bucket_start >= st["max_contrib"].long()[tile_of]) & (pos < true_max[tile_of])
+    mc = st["max_contrib"].long() & 0xffffffff   # uint32 in the reference; the uninitialised shared-memory slots often make it huge
+    lost = (bucket_start >= mc[tile_of]) & (pos < true_max[tile_of])
     return lost, tile_of, pos, true_max
 
 
