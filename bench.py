@@ -5,6 +5,9 @@ Workload (config.workload = "A"): 1 M synthetic Gaussians (SH degree 3), one 192
 backward through the reference-facing plugin surface (diff_gaussian_rasterization._C over the C ABI).
 A step = one forward + one backward of one view. With N GPUs every rank renders its own view of equal expected cost
 (see make_inputs; no data-path collective: the path shards by view), so scaling is weak and value = N * W*H * K / t.
+The same JSON line carries the other BASELINE configurations as sections (benchsections.py): `hier_step` (configs[2], 4 999 999
+nodes, N = 1), `eval_path` (configs[3], 49 999 999 nodes, 1000-pose camera path sharded over the ranks), `dp_train` (configs[4],
+gradient exchange over NCCL), `creator` (configs[0], GPU builder next to the reference's CPU creator + CPU cut tau sweep), `train`.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
@@ -35,7 +38,12 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--P", type=int, default=P, help="number of Gaussians (default: the 1 M of config A)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-cut", action="store_true", help="skip the LOD-cut ms/frame section")
+    ap.add_argument("--sections", default="hier_step,eval_path,dp_train,creator",
+                    help="comma list of the extra BASELINE configurations to run after the headline workload ('' = none)")
+    ap.add_argument("--eval-frames", type=int, default=1000, help="camera-path length of the eval_path section")
+    ap.add_argument("--eval-leaves", type=int, default=25_000_000, help="leaves of the eval_path hierarchy (N = 2L-1 nodes)")
+    ap.add_argument("--hier-leaves", type=int, default=2_500_000, help="leaves of the hier_step hierarchy")
+    ap.add_argument("--dp-mode", default="auto", choices=["auto", "factored", "allreduce"], help="gradient exchange of the dp_train section")
     return ap.parse_args()
 
 

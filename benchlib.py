@@ -136,6 +136,39 @@ class OursArm:
                                                     lodgs.current_stream()))
 
     def step_train(self):
+        """fwd + bwd + sparse Adam with the SH gradient kept in its factored form: the backward writes dL_drgb (12 B per Gaussian) instead
+        of dL_dsh (192 B), `lodgs_sh_adam_from_rgb` rebuilds the row in registers while it applies the update (csrc/sh_adam.cu)."""
+        import ctypes as C
+
+        import lodgs
+        from lodgs.optim import sh_adam_from_rgb
+        c, d = self.cam, self.tp
+        fa = (self.bg, self.ei, self.ei, self.ef, self.ei, d["means3D"], self.ef, d["opacities"], d["scales"], d["rotations"], 1.0,
+              self.ef, c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"], H, W, d["shs"], DEG, c["campos"], False, False, True)
+        R, color, radii, geom, binning, img, invdepth, seen = self._C.rasterize_gaussians(*fa)
+        dL = (color - self.target) * (2.0 / color.numel())
+        ba = (self.bg, self.ei, self.ei, self.ef, self.ei, d["means3D"], radii, self.ef, d["opacities"], d["scales"], d["rotations"],
+              1.0, self.ef, c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"], dL, torch.zeros_like(invdepth), d["shs"], DEG,
+              c["campos"], geom, R, binning, img, False)
+        grads = self._C.rasterize_gaussians_backward_rgb(*ba)
+        relevant = (radii > 0).nonzero().reshape(-1)
+        self.tstep += 1
+        sh_adam_from_rgb(grads[8], c["campos"], d["means3D"], d["shs"][:, :1], self.tm["shs"][:, :1], self.tv["shs"][:, :1], d["shs"][:, 1:],
+                         self.tm["shs"][:, 1:], self.tv["shs"][:, 1:], DEG, self.LR["shs"], self.LR["shs"], eps=1e-15, step=self.tstep,
+                         relevant=relevant)
+        keys = ("opacities", "scales", "rotations", "means3D")        # the means last: the SH update reads the ones the forward used
+        n = len(keys)
+        P4 = C.c_void_p * n
+        gs = [grads[self.GRAD_OF[k]] for k in keys]
+        rows = d["means3D"].size(0)
+        lodgs.check(lodgs.lib.lodgs_adam_step_multi(
+            n, P4(*[d[k].data_ptr() for k in keys]), P4(*[g.data_ptr() for g in gs]), P4(*[self.tm[k].data_ptr() for k in keys]),
+            P4(*[self.tv[k].data_ptr() for k in keys]), relevant.data_ptr(), relevant.numel(), None, (C.c_int64 * n)(*[rows] * n),
+            (C.c_int32 * n)(*[d[k].numel() // rows for k in keys]), (C.c_double * n)(*[self.LR[k] for k in keys]), (C.c_double * n)(*[0.9] * n),
+            (C.c_double * n)(*[0.999] * n), (C.c_double * n)(*[1e-15] * n), (C.c_int64 * n)(*[self.tstep] * n), 1, lodgs.current_stream()))
+
+    def step_train_materialised(self):
+        """The same iteration with dL_dsh written by the backward and read again by the optimizer (round-1 path; A/B and parity)."""
         color, grads = self.fwd_bwd(self.tp, self.target)
         relevant = (self.last[2] > 0).nonzero().reshape(-1)
         self.adam(relevant, grads)
@@ -209,13 +242,16 @@ class OursArm:
 
 
 class RefArm(OursArm):
-    """Same protocol over the reference CUDA build (oracle/_ref)."""
+    """Same protocol over the UNMODIFIED reference: its own torch extension (`_C.rasterize_gaussians` / `_backward` of
+    HR/rasterize_points.cu + HR/ext.cpp, oracle/_ref/ref_dgr/_C.so), i.e. the stock code path including its allocations, zero fills and the
+    mid-forward host synchronisation; the optimizer of the training section is scene/OurAdam.py's `Adam.step(relevant)` (the imported
+    class where /root/reference exists, else oracle/ouradam.RestatedAdam, pinned bit-identical to it by tests/test_ouradam_pin.py)."""
 
     def __init__(self, sc_host, cam_host, target_host, dev):
-        from oracle import refshim
-        if not refshim.available():
-            raise FileNotFoundError(refshim.REF_LIB)
-        self.ref = refshim
+        import benchsections
+        self.ext = benchsections._ref_ext()
+        if self.ext is None:
+            raise FileNotFoundError("oracle/_ref/ref_dgr/_C.so")
         self.dev = dev
         self.host = _pin(sc_host)
         self.target_host = torch.from_numpy(target_host).pin_memory()
@@ -223,39 +259,38 @@ class RefArm(OursArm):
         self.bg = torch.zeros(3, device=dev)
         self.d = {k: self.host[k].to(dev) for k in PARAM_KEYS}
         self.target = self.target_host.to(dev)
+        self.ei, self.ef = E(dev, torch.int32), E(dev)
         self.out_host = None
         self.last = None
         self.pipe = None
 
     def fwd_bwd(self, d, target):
-        L, ptr, c = self.ref.lib(), self.ref.ptr, self.cam
-        P = d["means3D"].size(0)
-        dev = self.dev
-        # allocations + zero fills exactly as RasterizeGaussiansCUDA / ...BackwardCUDA do (HR/rasterize_points.cu:73-92,178-187)
-        color = torch.zeros(3, H, W, device=dev)
-        invdepth = torch.zeros(1, H, W, device=dev)
-        radii = torch.zeros(P, dtype=torch.int32, device=dev)
-        rects = torch.zeros(P, 2, dtype=torch.int32, device=dev)
-        seen = torch.zeros(P, dtype=torch.int32, device=dev)
-        R = L.ref_forward(P, DEG, M, ptr(self.bg), W, H, None, None, None, None, ptr(d["means3D"]), ptr(d["shs"]), None,
-                          ptr(d["opacities"]), ptr(d["scales"]), 1.0, ptr(d["rotations"]), None, ptr(c["viewmatrix"]),
-                          ptr(c["projmatrix"]), ptr(c["campos"]), c["tanfovx"], c["tanfovy"], 0, ptr(color), ptr(invdepth), ptr(radii),
-                          ptr(rects), 0, ptr(seen))
+        c = self.cam
+        fa = (self.bg, self.ei, self.ei, self.ef, self.ei, d["means3D"], self.ef, d["opacities"], d["scales"], d["rotations"], 1.0,
+              self.ef, c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"], H, W, d["shs"], DEG, c["campos"], False, False, True)
+        R, color, radii, geom, binning, img, invdepth, seen = self.ext.rasterize_gaussians(*fa)
         dL = (color - target) * (2.0 / color.numel())
         dLi = torch.zeros_like(invdepth)
-        z = lambda *s: torch.zeros(*s, device=dev)  # noqa: E731
-        g2, gc, go, gcol, gi = z(P, 3), z(P, 2, 2), z(P, 1), z(P, 3), z(P, 1)
-        g3, gcov, gsh, gs, gr = z(P, 3), z(P, 6), z(P, M, 3), z(P, 3), z(P, 4)
-        L.ref_backward(P, DEG, M, R, ptr(self.bg), W, H, None, None, None, None, ptr(d["means3D"]), ptr(d["shs"]), None,
-                       ptr(d["opacities"]), ptr(d["scales"]), 1.0, ptr(d["rotations"]), None, ptr(c["viewmatrix"]), ptr(c["projmatrix"]),
-                       ptr(c["campos"]), c["tanfovx"], c["tanfovy"], ptr(radii), ptr(dL), ptr(dLi), ptr(g2), ptr(gc), ptr(go), ptr(gcol),
-                       ptr(gi), ptr(g3), ptr(gcov), ptr(gsh), ptr(gs), ptr(gr), 0)
-        grads = (g2, gcol, go, g3, gcov, gsh, gs, gr)
+        ba = (self.bg, self.ei, self.ei, self.ef, self.ei, d["means3D"], radii, self.ef, d["opacities"], d["scales"], d["rotations"],
+              1.0, self.ef, c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"], dL, dLi, d["shs"], DEG, c["campos"], geom, R,
+              binning, img, False)
+        grads = self.ext.rasterize_gaussians_backward(*ba)
         self.last = (R, color, radii, None, grads)
         return color, grads
 
-    def adam(self, relevant, grads):
-        _eager_index_adam(self, relevant, grads)
+    def train_init(self):
+        from oracle import ouradam
+        cls, self.opt_kind = ouradam.reference_or_restated()
+        self.tp = {k: torch.nn.Parameter(self.d[k].clone()) for k in PARAM_KEYS}
+        self.opt = cls([{"params": [self.tp[k]], "lr": self.LR[k]} for k in PARAM_KEYS], lr=0.0, eps=1e-15)
+
+    def step_train(self):
+        color, grads = self.fwd_bwd(self.tp, self.target)
+        relevant = (self.last[2] > 0).nonzero().reshape(-1)
+        for k in PARAM_KEYS:
+            self.tp[k].grad = grads[self.GRAD_OF[k]]
+        with torch.no_grad():
+            self.opt.step(relevant)
 
 
 # ------------------------------------------------------------------------------------------------ roofline
@@ -298,27 +333,6 @@ def _work_model(arm, n_gauss):
         "preprocess_bwd_kernel": ("hbm", p_vis * (115.0 + 68.0 + 24.0 * M)),
     }
     return work, {"num_rendered": R, "p_visible": p_vis, "n_test": n_test, "n_alpha": n_alpha, "n_blend": n_blend}
-
-
-def _eager_index_adam(arm, relevant, grads):
-    """The reference's optimizer step as it runs there: scene/OurAdam.py:251-354 `_single_tensor_adam` — gather the listed rows of
-    param / grad / moments, eager elementwise Adam with host-side bias correction, scatter the rows back."""
-    import math
-    arm.tstep += 1
-    b1, b2, eps = 0.9, 0.999, 1e-15
-    for k in PARAM_KEYS:
-        grad = grads[arm.GRAD_OF[k]][relevant]
-        exp_avg = arm.tm[k][relevant]
-        exp_avg_sq = arm.tv[k][relevant]
-        param = arm.tp[k][relevant]
-        exp_avg.mul_(b1).add_(grad, alpha=1 - b1)
-        exp_avg_sq.mul_(b2).addcmul_(grad, grad.conj(), value=1 - b2)
-        step_size = arm.LR[k] / (1 - b1 ** arm.tstep)
-        denom = (exp_avg_sq.sqrt() / math.sqrt(1 - b2 ** arm.tstep)).add_(eps)
-        param.addcdiv_(exp_avg, denom, value=-step_size)
-        arm.tm[k][relevant] = exp_avg
-        arm.tv[k][relevant] = exp_avg_sq
-        arm.tp[k][relevant] = param
 
 
 def _ncu_traffic():
@@ -391,8 +405,48 @@ def _train_section(arm, args, world, dev, what):
     terms outside the plugin); single GPU."""
     arm.train_init()
     ms = _timed(arm.step_train, args.steps, 3, world, dev)
-    return {"iters_per_s": round(args.steps / (ms * 1e-3), 2), "ms_per_iter": round(ms / args.steps, 4), "optimizer": what,
-            "updated_floats_per_gaussian": 59}
+    out = {"iters_per_s": round(args.steps / (ms * 1e-3), 2), "ms_per_iter": round(ms / args.steps, 4), "optimizer": what,
+           "updated_floats_per_gaussian": 59}
+    if isinstance(arm, OursArm) and not isinstance(arm, RefArm):
+        import lodgs
+        lodgs.profile(True)
+        for _ in range(5):
+            arm.step_train()
+        torch.cuda.synchronize()
+        prof = lodgs.profile_dump()
+        lodgs.profile(False)
+        out["per_kernel_ms"] = {name: round(t / 5, 4) for name, (t, n) in sorted(prof.items(), key=lambda kv: -kv[1][0])}
+    return out
+
+
+def _sections(impl, args, rank, world, dev):
+    """The other BASELINE configurations (benchsections.py), run by every rank (eval_path and dp_train are collective), reported by
+    rank 0. A section that cannot run reports why instead of aborting the headline line."""
+    import benchsections as bs
+    want = [x for x in (args.sections or "").split(",") if x]
+    out = {}
+
+    def guarded(name, fn):
+        if name not in want:
+            return
+        try:
+            torch.cuda.empty_cache()
+            t0 = time.perf_counter()
+            r = fn()
+            if isinstance(r, dict):
+                r["section_wall_s"] = round(time.perf_counter() - t0, 2)
+            out[name] = r
+        except Exception as e:  # noqa: BLE001
+            out[name] = {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:300])}
+            if world > 1:
+                raise
+    if world == 1:
+        guarded("hier_step", lambda: bs.hier_step(impl, dev, iters=max(3, args.steps // 2), leaves=args.hier_leaves))
+    guarded("eval_path", lambda: bs.eval_path(impl, rank, world, dev, frames=args.eval_frames, leaves=args.eval_leaves))
+    guarded("dp_train", lambda: bs.dp_train(impl, rank, world, dev, steps=args.steps, warmup=args.warmup, n_gauss=args.P, mode=args.dp_mode))
+    if world == 1 and impl == "ours" and not args.no_cpu_baseline:
+        guarded("creator", lambda: bs.creator_and_cpu_cut(dev))
+    return out
 
 
 def run_ours(args, rank, world, dev):
@@ -400,7 +454,6 @@ def run_ours(args, rank, world, dev):
     sc, cam, target = make_inputs(rank, args.P)
     arm = OursArm(sc, cam, target, dev)
     sampler = ClockSampler(dev.index) if rank == 0 else None
-    launches0 = lodgs.launch_count()
     for _ in range(args.warmup):
         arm.step_resident()
     torch.cuda.synchronize()
@@ -413,61 +466,87 @@ def run_ours(args, rank, world, dev):
     clocks = sampler.stop() if sampler else None
     ms_e2e = _timed(arm.step_e2e, args.steps, max(3, args.warmup // 2), world, dev, finish_fn=arm.finish_e2e)
     h2d, d2h = arm.io_bytes()
+    floor_ms = _copy_floor(arm, args.steps, world, dev)
     mpix = W * H / 1e6
     value = world * mpix * args.steps / (ms * 1e-3)
     e2e = world * mpix * args.steps / (ms_e2e * 1e-3)
+    extra = {}
+    if rank == 0:
+        sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
+        work, counters = _work_model(arm, args.P)
+        roof, per_kernel = _roofline(prof, args.steps, work, sm_count)
+        extra = {"impl": "ours", "e2e": {"value": round(e2e, 2), "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                                         "ms_per_step": round(ms_e2e / args.steps, 4), "copy_floor_ms": round(floor_ms, 4),
+                                         "frac_of_copy_floor": round(floor_ms / (ms_e2e / args.steps), 4)},
+                 "gpu_launches": int(launches), "roofline": roof, "per_kernel": per_kernel, "workload_counters": counters,
+                 "cpu_baseline": _cpu_baseline(args.no_cpu_baseline)}
+    if world == 1:
+        extra["train"] = _train_section(arm, args, world, dev, "sparse Adam on the rows with radii > 0: lodgs_sh_adam_from_rgb (SH rows rebuilt from "
+                                                               "dL_drgb, no dL_dsh in HBM) + lodgs_adam_step_multi")
+        arm.train_init()
+        ms_mat = _timed(arm.step_train_materialised, args.steps, 3, world, dev)
+        extra["train"]["ms_per_iter_with_materialised_dL_dsh"] = round(ms_mat / args.steps, 4)
+    del arm
+    extra.update(_sections("ours", args, rank, world, dev))
     if rank != 0:
         return None
-    sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
-    work, counters = _work_model(arm, args.P)
-    roof, per_kernel = _roofline(prof, args.steps, work, sm_count)
-    extra = {"impl": "ours", "e2e": {"value": round(e2e, 2), "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                                     "ms_per_step": round(ms_e2e / args.steps, 4)},
-             "gpu_launches": int(launches), "roofline": roof, "per_kernel": per_kernel, "workload_counters": counters,
-             "cpu_baseline": _cpu_baseline(args.no_cpu_baseline)}
-    if world == 1:
-        extra["train"] = _train_section(arm, args, world, dev, "lodgs_adam_step on the rows with radii > 0 (one fused kernel per tensor)")
-    if not getattr(args, "no_cut", False) and world == 1:
-        extra["lod_cut"] = _lod_cut(dev, not args.no_cpu_baseline)
     return _line(args, world, value, ms / args.steps, clocks, extra)
 
 
-def _lod_cut(dev, with_cpu):
-    """Second half of BASELINE.json's metric: LOD-cut ms/frame (expand_to_size [+ get_interpolation_weights]) on a synthetic
-    4.19 M-node hierarchy, tau in {0,3,6,15} px, next to the reference CUDA cut and the CPU port (tools/bench_cut.py)."""
-    try:
-        import importlib.util
-        spec = importlib.util.spec_from_file_location("bench_cut", os.path.join(ROOT, "tools", "bench_cut.py"))
-        mod = importlib.util.module_from_spec(spec)
-        spec.loader.exec_module(mod)
-        return mod.run(k=21, frames=30, dev=dev, with_ref=True, with_cpu=with_cpu)
-    except Exception as e:  # noqa: BLE001
-        return {"unavailable": str(e)[:200]}
+def _copy_floor(arm, steps, world, dev):
+    """The host-link floor of the end-to-end step: the SAME per-step transfers (all inputs host->device, all results device->host, pinned
+    memory, both directions concurrently on two streams) with no kernel in between; ms per step, max over ranks."""
+    if arm.pipe is None or arm.out_host is None:
+        return 0.0
+    pp = arm.pipe
+    d, target = pp["in"][0]
+    outs = pp["keep"][0]
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    _barrier(world)
+    ev0.record()
+    for _ in range(steps):
+        with torch.cuda.stream(pp["h2d"]):
+            for k in PARAM_KEYS:
+                d[k].copy_(arm.host[k], non_blocking=True)
+            target.copy_(arm.target_host, non_blocking=True)
+        with torch.cuda.stream(pp["d2h"]):
+            for h, o in zip(arm.out_host, outs):
+                h.copy_(o, non_blocking=True)
+    for st in (pp["h2d"], pp["d2h"]):
+        torch.cuda.current_stream().wait_stream(st)
+    ev1.record()
+    _barrier(world)
+    return _max_over_ranks(ev0.elapsed_time(ev1) / steps, world, dev)
 
 
 def run_reference(args, rank, world, dev):
     sc, cam, target = make_inputs(rank, args.P)
     try:
         arm = RefArm(sc, cam, target, dev)
-    except (FileNotFoundError, OSError) as e:
-        return {"impl": "reference", "unavailable": "oracle/_ref/libref_lodgs.so missing or not loadable (%s)" % str(e)[:80]}
+    except (FileNotFoundError, OSError, ImportError) as e:
+        return {"impl": "reference", "unavailable": "oracle/_ref/ref_dgr/_C.so (the reference's torch extension) missing or not loadable (%s)" % str(e)[:80]}
     sampler = ClockSampler(dev.index) if rank == 0 else None
     ms = _timed(arm.step_resident, args.steps, args.warmup, world, dev, sampler)
     clocks = sampler.stop() if sampler else None
     ms_e2e = _timed(arm.step_e2e, args.steps, max(3, args.warmup // 2), world, dev, finish_fn=arm.finish_e2e)
     h2d, d2h = arm.io_bytes()
+    floor_ms = _copy_floor(arm, args.steps, world, dev)
     mpix = W * H / 1e6
     value = world * mpix * args.steps / (ms * 1e-3)
     e2e = world * mpix * args.steps / (ms_e2e * 1e-3)
-    if rank != 0:
-        return None
     extra = {"impl": "reference",
              "e2e": {"value": round(e2e, 2), "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                     "ms_per_step": round(ms_e2e / args.steps, 4)},
+                     "ms_per_step": round(ms_e2e / args.steps, 4), "copy_floor_ms": round(floor_ms, 4),
+                     "frac_of_copy_floor": round(floor_ms / (ms_e2e / args.steps), 4)},
              "cpu_baseline": {"value": round(e2e, 2), "unit": "Mpix/s", "cores": 0, "kind": "reference",
-                              "sample": "full workload; the reference has no CPU implementation of this path, so this arm runs its "
-                                        "unmodified CUDA kernels (oracle/_ref, sm_100a rebuild) on the same B200"}}
+                              "sample": "full workload; the reference has no CPU implementation of the rasterizer, so this arm runs its "
+                                        "unmodified CUDA code through its own torch extension (oracle/_ref/ref_dgr, sm_100a rebuild) on the same "
+                                        "B200; its CPU code (hierarchy creator) and the CPU cut are timed in the `creator` section of the other arm"}}
     if world == 1:
-        extra["train"] = _train_section(arm, args, world, dev, "eager torch restatement of scene/OurAdam.py _single_tensor_adam "
-                                                               "(row gather, elementwise ops, row scatter) on the rows with radii > 0")
+        extra["train"] = _train_section(arm, args, world, dev, "scene/OurAdam.py Adam.step(relevant) on the rows with radii > 0")
+        extra["train"]["optimizer_class"] = getattr(arm, "opt_kind", None)
+    del arm
+    extra.update(_sections("reference", args, rank, world, dev))
+    if rank != 0:
+        return None
     return _line(args, world, value, ms / args.steps, clocks, extra)

@@ -21,6 +21,9 @@ What differs from diff_gaussian_rasterization and how it is mapped:
 import torch
 
 import lodgs
+
+import lodgs as _lodgs
+_lodgs.load()   # the plugin cannot work without the native library: fail at import, loudly
 from diff_gaussian_rasterization import _C as _hr
 from lodgs.optim import adam_update
 

@@ -254,3 +254,50 @@ extern "C" int lodgs_expand_to_target(const int32_t* nodes, int N, int target, i
     if (out && n > capacity) { lodgs::set_error("lodgs_expand_to_target: %lld entries, capacity %lld", (long long)n, (long long)capacity); return LODGS_E_WORKSPACE; }
     return LODGS_OK;
 }
+
+
+// ---- host side of the hierarchy creator around lodgs_hier_build: what the reference does with a PLY record before and after the
+// tree stages, with the same libm calls, so that a .dhier written from the GPU build carries the creator's bits.
+#include <cmath>
+
+// Loader::loadPly<LessRichPoint> (GH/loader.cpp:105-124; record GH/common.h:39-47 = position 3, normal 3, shs 12, opacity 1, scale 3,
+// rotation 4) followed by the validity filter of GH/mainHierarchyCreator.cpp:87-149. keep[i] = 1 for the Gaussians the creator keeps.
+extern "C" int lodgs_creator_activate(const float* records, int64_t count, float* pos, float* scale, float* rot, float* opacity, float* shs48,
+                                      uint8_t* keep) {
+    if (count < 0 || (count > 0 && (!records || !pos || !scale || !rot || !opacity || !shs48 || !keep))) {
+        lodgs::set_error("lodgs_creator_activate: bad argument");
+        return LODGS_E_ARG;
+    }
+    for (int64_t i = 0; i < count; i++) {
+        const float* r = records + i * 26;
+        const float o = 1.0f / (1.0f + expf(-r[18]));                       // common.h:20-23 sigmoid
+        opacity[i] = o;
+        bool ok = !std::isinf(o) && !std::isnan(o) && o != 0.f;
+        for (int c = 0; c < 3; c++) {
+            pos[3 * i + c] = r[c];
+            const float sc = expf(r[19 + c]);
+            scale[3 * i + c] = sc;
+            ok = ok && !(sc > 10.f) && !std::isnan(sc) && !std::isnan(r[c]);
+        }
+        float n2 = r[22] * r[22];
+        for (int c = 1; c < 4; c++) n2 += r[22 + c] * r[22 + c];
+        const float n = sqrtf(n2);
+        for (int c = 0; c < 4; c++) {
+            const float q = n > 0.f ? r[22 + c] / n : r[22 + c];            // Eigen normalized(): unchanged when the norm is 0
+            rot[4 * i + c] = q;
+            ok = ok && !std::isnan(q);
+        }
+        float* sh = shs48 + i * 48;
+        for (int c = 0; c < 48; c++) sh[c] = 0.f;
+        for (int c = 0; c < 3; c++) { sh[c] = r[6 + c]; ok = ok && !std::isnan(r[6 + c]); }   // a LessRichPoint only carries its DC over
+        keep[i] = ok ? 1 : 0;
+    }
+    return LODGS_OK;
+}
+
+// log of the scales as the writer stores them (GH/writer.cpp:119,130 `g.scale.array().log()`): libm logf on the host.
+extern "C" int lodgs_logf_host(const float* in, int64_t n, float* out) {
+    if (n < 0 || (n > 0 && (!in || !out))) { lodgs::set_error("lodgs_logf_host: bad argument"); return LODGS_E_ARG; }
+    for (int64_t i = 0; i < n; i++) out[i] = logf(in[i]);
+    return LODGS_OK;
+}

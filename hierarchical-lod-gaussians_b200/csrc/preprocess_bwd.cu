@@ -38,7 +38,8 @@ struct PreBwdParams {
     float* dL_dopacity;
     float* dL_dmean3D;
     float* dL_dcov3D;
-    float* dL_dsh;
+    float* dL_dsh;   // may be null when dL_drgb is given: the SH gradient is then not materialised (lodgs_sh_adam_from_rgb rebuilds it)
+    float* dL_drgb;  // optional [fullP,3]: colour gradient after the clamp mask, the factor dL_dsh[k] = basis_k(dir) * dL_drgb is built from
     float* dL_dscale;
     float* dL_drot;
     int sh_vec4;
@@ -86,19 +87,23 @@ __global__ void __launch_bounds__(256, 3) preprocess_bwd_kernel(const PreBwdPara
             sc[0] = sc[1] = sc[2] = 0.f;
             reinterpret_cast<float4*>(p.dL_drot)[t_idx] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
+        if (p.dL_drgb) {
+            float* c3 = p.dL_drgb + 3 * (size_t)t_idx;
+            c3[0] = c3[1] = c3[2] = 0.f;
+        }
     }
     if (STAGED) {
         if (!active) {
             // culled rows still travel with the block store: they carry the zeros the caller's zero-fill put there
             mbar_wait(&s_bar, 0);
-            if (t_idx < p.P)
+            if (t_idx < p.P && p.dL_dsh)
                 for (int k = 0; k < row4; k++) sh_stage[threadIdx.x * row4 + k] = make_float4(0.f, 0.f, 0.f, 0.f);
         } else {
             preprocess_bwd_one<STAGED>(p, t_idx, s_view, s_proj, sh_stage + threadIdx.x * row4, &s_bar);
         }
         fence_async_smem();
         __syncthreads();
-        if (threadIdx.x == 0) {
+        if (threadIdx.x == 0 && p.dL_dsh) {
             bulk_s2g(p.dL_dsh + (size_t)tile_base * p.M * 3, sh_stage, (unsigned)tile_cnt * (unsigned)row4 * 16u);
             bulk_commit_wait_all();
         }
@@ -232,6 +237,10 @@ __device__ __forceinline__ void preprocess_bwd_one(const PreBwdParams& p, int t_
         dRGB.x *= (cl & 1) ? 0 : 1;
         dRGB.y *= (cl & 2) ? 0 : 1;
         dRGB.z *= (cl & 4) ? 0 : 1;
+        if (p.dL_drgb && !is_child) {
+            float* c3 = p.dL_drgb + 3 * (size_t)idx;
+            c3[0] = dRGB.x; c3[1] = dRGB.y; c3[2] = dRGB.z;
+        }
         const int deg = p.D;
         const int ncoef = (deg + 1) * (deg + 1);
         v3 sh[16];
@@ -289,7 +298,9 @@ __device__ __forceinline__ void preprocess_bwd_one(const PreBwdParams& p, int t_
             }
         }
         // dL_dsh: LOD children's own SH gradient is discarded by the reference (backward.cu:489-493)
-        if (STAGED) {
+        if (!p.dL_dsh) {
+            // not materialised: the consumer rebuilds w[k] * dRGB from dL_drgb (csrc/sh_adam.cu)
+        } else if (STAGED) {
             // the row is rebuilt in place (this thread is its only reader and writer); coefficients above the active degree are 0
             float o[48];
 #pragma unroll
@@ -385,7 +396,9 @@ __device__ __forceinline__ void preprocess_bwd_one(const PreBwdParams& p, int t_
 
 int launch_preprocess_bwd(const PreBwdParams& p, cudaStream_t s) {
     const size_t smem = 256 * (size_t)p.M * 12;
-    const bool staged = lodgs_backward_overwrites_dsh(p.M, p.indices != nullptr, p.parent_indices != nullptr, p.shs, p.dL_dsh) != 0;
+    // staged SH rows (one bulk load per CTA, and one bulk store of dL_dsh when that gradient is materialised)
+    const bool staged = p.dL_dsh ? lodgs_backward_overwrites_dsh(p.M, p.indices != nullptr, p.parent_indices != nullptr, p.shs, p.dL_dsh) != 0
+                                 : lodgs_backward_overwrites_dsh(p.M, p.indices != nullptr, p.parent_indices != nullptr, p.shs, p.shs) != 0;
     if (staged) {
         static std::atomic<size_t> attr_smem[MAX_DEVICES];
         const int dslot = device_slot();
@@ -410,8 +423,9 @@ int run_preprocess_bwd(int P, int D, int M, const int32_t* indices, const int32_
                        const float* projmatrix, const float* campos, float focal_x, float focal_y, float tan_fovx, float tan_fovy,
                        const float* dL_dmean2D, const float* dL_dconic, const float* dL_dinvdepth, const float* dL_dcolor,
                        float* dL_dopacity, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
-                       unsigned flags, cudaStream_t s) {
+                       float* dL_drgb, unsigned flags, cudaStream_t s) {
     PreBwdParams p;
+    p.dL_drgb = dL_drgb;
     p.flags = flags;
     p.P = P; p.D = D; p.M = M; p.indices = indices; p.parent_indices = parent_indices; p.ts = ts; p.means3D = means3D; p.radii = radii;
     p.shs = shs; p.clamped = clamped; p.opacities = opacities; p.scales = scales; p.rotations = rotations; p.scale_modifier = scale_modifier;

@@ -124,7 +124,7 @@ int run_preprocess_bwd(int P, int D, int M, const int32_t* indices, const int32_
                        const float* projmatrix, const float* campos, float focal_x, float focal_y, float tan_fovx, float tan_fovy,
                        const float* dL_dmean2D, const float* dL_dconic, const float* dL_dinvdepth, const float* dL_dcolor,
                        float* dL_dopacity, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
-                       unsigned flags, cudaStream_t s);
+                       float* dL_drgb, unsigned flags, cudaStream_t s);
 }  // namespace lodgs
 
 extern "C" int lodgs_backward(int P, int fullP, int D, int M, int R, int W, int H, const float* background, const int32_t* indices,
@@ -151,6 +151,21 @@ extern "C" int lodgs_backward_ex(int P, int fullP, int D, int M, int R, int W, i
                                  const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
                                  float* dL_dinvdepth, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
                                  unsigned flags, void* stream) {
+    return lodgs_backward_rgb(P, fullP, D, M, R, W, H, background, indices, parent_indices, ts, kids, means3D, shs, colors_precomp, opacities,
+                              scales, scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, radii,
+                              geom_buffer, binning_buffer, image_buffer, dL_dpix, dL_dinvdepth_pix, dL_dmean2D, dL_dconic, dL_dopacity,
+                              dL_dcolor, dL_dinvdepth, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, nullptr, flags, stream);
+}
+
+extern "C" int lodgs_backward_rgb(int P, int fullP, int D, int M, int R, int W, int H, const float* background, const int32_t* indices,
+                                  const int32_t* parent_indices, const float* ts, const int32_t* kids, const float* means3D,
+                                  const float* shs, const float* colors_precomp, const float* opacities, const float* scales,
+                                  float scale_modifier, const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                                  const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy, const int32_t* radii,
+                                  void* geom_buffer, void* binning_buffer, void* image_buffer, const float* dL_dpix,
+                                  const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                                  float* dL_dinvdepth, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                                  float* dL_drgb, unsigned flags, void* stream) {
     (void)colors_precomp;
     if (P < 0 || fullP < 0 || W <= 0 || H <= 0 || R < 0 || D < 0 || D > 3) { set_error("lodgs_backward: bad size argument"); return LODGS_E_ARG; }
     if (P == 0) return LODGS_OK;
@@ -160,7 +175,7 @@ extern "C" int lodgs_backward_ex(int P, int fullP, int D, int M, int R, int W, i
         return LODGS_E_ARG;
     }
     if ((dL_dinvdepth_pix == nullptr) != (dL_dinvdepth == nullptr)) { set_error("lodgs_backward: dL_dinvdepth_pix and dL_dinvdepth go together"); return LODGS_E_ARG; }
-    if (shs && !dL_dsh) { set_error("lodgs_backward: dL_dsh missing"); return LODGS_E_ARG; }
+    if (shs && !dL_dsh && !dL_drgb) { set_error("lodgs_backward: dL_dsh missing"); return LODGS_E_ARG; }
     if (scales && (!rotations || !dL_dscale || !dL_drot)) { set_error("lodgs_backward: scale/rotation gradient buffers missing"); return LODGS_E_ARG; }
     cudaStream_t s = (cudaStream_t)stream;
     prof_stage_begin(s);
@@ -182,7 +197,7 @@ extern "C" int lodgs_backward_ex(int P, int fullP, int D, int M, int R, int W, i
     return run_preprocess_bwd(P, D, M, indices, parent_indices, ts, means3D, radii, shs, g.clamped, opacities, scales, rotations,
                               scale_modifier, cov3Ds, cov3D_precomp ? 1 : 0, viewmatrix, projmatrix, campos, focal_x, focal_y, tan_fovx,
                               tan_fovy, dL_dmean2D, dL_dconic, dL_dinvdepth, dL_dcolor, dL_dopacity, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale,
-                              dL_drot, flags, s);
+                              dL_drot, dL_drgb, flags, s);
 }
 
 namespace lodgs {

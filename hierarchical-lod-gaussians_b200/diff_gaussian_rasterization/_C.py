@@ -6,6 +6,9 @@ import ctypes as C
 import torch
 
 import lodgs
+
+import lodgs as _lodgs
+_lodgs.load()   # the plugin cannot work without the native library: fail at import, loudly
 from lodgs import check, current_stream, lib, ptr
 
 NUM_CHANNELS = 3
@@ -99,9 +102,20 @@ def rasterize_gaussians_backward(background, indices, parent_indices, ts, kids, 
                          degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug, 0)
 
 
+def rasterize_gaussians_backward_rgb(background, indices, parent_indices, ts, kids, means3D, radii, colors, opacities, scales,
+                                     rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
+                                     dL_dout_color, dL_dout_invdepth, sh, degree, campos, geomBuffer, R, binningBuffer,
+                                     imageBuffer, debug):
+    """rasterize_gaussians_backward without the SH gradient: the sixth result is None and a ninth, dL_drgb [fullP,3] (colour gradient
+    after the clamp mask), is appended — the input of lodgs.optim.sh_adam_from_rgb (not in the reference: lodgs_backward_rgb)."""
+    return backward_impl(background, indices, parent_indices, ts, kids, means3D, radii, colors, opacities, scales, rotations,
+                         scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_invdepth, sh,
+                         degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug, 0, want_rgb=True)
+
+
 def backward_impl(background, indices, parent_indices, ts, kids, means3D, radii, colors, opacities, scales, rotations, scale_modifier,
                   cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_invdepth, sh, degree, campos,
-                  geomBuffer, R, binningBuffer, imageBuffer, debug, _flags):
+                  geomBuffer, R, binningBuffer, imageBuffer, debug, _flags, want_rgb=False):
     dev = means3D.device
     fullP = means3D.size(0)
     P = fullP if indices.numel() == 0 else indices.size(0)
@@ -134,10 +148,15 @@ def backward_impl(background, indices, parent_indices, ts, kids, means3D, radii,
     has_scales = scales.numel() != 0
     dL_dscales = alloc(fullP, 3) if has_scales else z(fullP, 3)
     dL_drotations = alloc(fullP, 4) if has_scales else z(fullP, 4)
-    dL_dsh = torch.empty((fullP, M, 3), dtype=torch.float32, device=dev)
-    if not (P != 0 and sh.numel() and sh.device == dev and sh.is_contiguous() and
-            lib.lodgs_backward_overwrites_dsh(M, int(indices.numel() != 0), int(parent_indices.numel() != 0), ptr(sh), ptr(dL_dsh))):
-        dL_dsh.zero_()
+    dL_drgb = None
+    if want_rgb:
+        dL_dsh = None
+        dL_drgb = alloc(fullP, NUM_CHANNELS)
+    else:
+        dL_dsh = torch.empty((fullP, M, 3), dtype=torch.float32, device=dev)
+        if not (P != 0 and sh.numel() and sh.device == dev and sh.is_contiguous() and
+                lib.lodgs_backward_overwrites_dsh(M, int(indices.numel() != 0), int(parent_indices.numel() != 0), ptr(sh), ptr(dL_dsh))):
+            dL_dsh.zero_()
     if P != 0:
         t = [_f(x.to(dev)) if x.numel() and x.device != dev else _f(x) for x in
              (background, indices, parent_indices, ts, kids, means3D, colors, opacities, scales, rotations, cov3D_precomp,
@@ -147,16 +166,18 @@ def backward_impl(background, indices, parent_indices, ts, kids, means3D, radii,
         dL_dout_color = dL_dout_color.contiguous()
         if has_depth:
             dL_dout_invdepth = dL_dout_invdepth.contiguous()
-        check(lib.lodgs_backward_ex(P, fullP, int(degree), M, int(R), W, H, ptr(background), ptr(indices), ptr(parent_indices),
+        check(lib.lodgs_backward_rgb(P, fullP, int(degree), M, int(R), W, H, ptr(background), ptr(indices), ptr(parent_indices),
                                  ptr(ts), ptr(kids), ptr(means3D), ptr(sh), ptr(colors), ptr(opacities), ptr(scales),
                                  float(scale_modifier), ptr(rotations), ptr(cov3D_precomp), ptr(viewmatrix), ptr(projmatrix),
                                  ptr(campos), float(tan_fovx), float(tan_fovy), ptr(radii), ptr(geomBuffer), ptr(binningBuffer),
                                  ptr(imageBuffer), ptr(dL_dout_color), ptr(dL_dout_invdepth) if has_depth else None,
                                  ptr(dL_dmeans2D), ptr(dL_dconic), ptr(dL_dopacity), ptr(dL_dcolors),
                                  ptr(dL_dinvdepths) if has_depth else None, ptr(dL_dmeans3D), ptr(dL_dcov3D), ptr(dL_dsh),
-                                 ptr(dL_dscales), ptr(dL_drotations), int(_flags), current_stream()))
+                                 ptr(dL_dscales), ptr(dL_drotations), ptr(dL_drgb), int(_flags), current_stream()))
         if debug:
             torch.cuda.synchronize()
+    if want_rgb:
+        return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, None, dL_dscales, dL_drotations, dL_drgb
     return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations
 
 

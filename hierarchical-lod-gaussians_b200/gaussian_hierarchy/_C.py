@@ -10,6 +10,9 @@ import torch
 
 from lodgs import LodgsError, check, current_stream, lib, ptr
 
+import lodgs as _lodgs
+_lodgs.load()   # the plugin cannot work without the native library: fail at import, loudly
+
 _ws_cache = {}          # (device index) -> workspace tensor (grown on demand; the reference mallocs per call)
 _traversable = {}       # _hier_key -> bool, from lodgs_cut_prepare
 _last_count = {}        # _hier_key -> K of the previous cut of this hierarchy (the next frame's is close to it)

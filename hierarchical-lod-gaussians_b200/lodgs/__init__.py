@@ -1,7 +1,9 @@
 """ctypes binding of liblodgs.so (include/lodgs.h). PyTorch is used only for device memory and streams.
 
-The library is mandatory: importing this module fails loudly when liblodgs.so is missing or does not export
-every symbol of the header; there is no CPU or PyTorch fallback anywhere in the product path.
+The library is mandatory: `lodgs.load()` — called by the first use of `lodgs.lib` and by every plugin module at import — fails loudly
+when liblodgs.so is missing or does not export every symbol of the header; there is no CPU or PyTorch fallback anywhere in the product
+path. Importing the bare package (for `lodgs.synth`, the seeded input generators) does not map the library, so a process that only
+runs the reference's code never has it loaded.
 """
 import ctypes as C
 import os
@@ -35,7 +37,15 @@ def _load():
     return C.CDLL(LIB_PATH)
 
 
-lib = _load()
+class _Lib:
+    """`lodgs.lib`: binds liblodgs.so on first attribute access."""
+    _cdll = None
+
+    def __getattr__(self, name):
+        return getattr(load(), name)
+
+
+lib = _Lib()
 
 _p, _i, _f, _sz, _i64, _d = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_int64, C.c_double
 
@@ -60,6 +70,8 @@ _SIGS = {
     "lodgs_dhier_load": (_i, [C.c_char_p, _p, _p, _p, _p, _p, _p]),
     "lodgs_dhier_write": (_i, [C.c_char_p, _i, _i, _i, _p, _p, _p, _p, _p, _p]),
     "lodgs_hier_build_workspace_bytes": (_sz, [_i]),
+    "lodgs_creator_activate": (_i, [_p, _i64, _p, _p, _p, _p, _p, _p]),
+    "lodgs_logf_host": (_i, [_p, _i64, _p]),
     "lodgs_hier_build": (_i, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "lodgs_geom_bytes": (_sz, [_i]),
     "lodgs_image_bytes": (_sz, [_i, _i]),
@@ -75,6 +87,10 @@ _SIGS = {
                             _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "lodgs_backward_ex": (_i, [_i, _i, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _f, _f, _p,
                                _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, C.c_uint, _p]),
+    "lodgs_backward_rgb": (_i, [_i, _i, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _f, _f, _p,
+                                _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, C.c_uint, _p]),
+    "lodgs_sh_adam_from_rgb": (_i, [_i64, _i, _i, _p, _i64, _p, _p, _p, _i64, _p, _p, _p, _p, _i, _p, _p, _p, _i, _i, _d, _d, _d, _d, _d,
+                                    _i64, _i, _p]),
     "lodgs_mark_visible": (_i, [_i, _p, _p, _p, _p, _p]),
     "lodgs_spt_cut_workspace_bytes": (_sz, [_i]),
     "lodgs_spt_cut_count": (_i, [_i, _p, _i, _p, _p, _p, _p, _p, _p, _p, _sz, _p, _p]),
@@ -103,11 +119,11 @@ def header_symbols():
     return sorted(set(re.findall(r"\b(lodgs_[a-z0-9_]+)\s*\(", text)))
 
 
-def _bind():
+def _bind(cdll):
     missing = []
     for name, (res, args) in _SIGS.items():
         try:
-            fn = getattr(lib, name)
+            fn = getattr(cdll, name)
         except AttributeError:
             missing.append(name)
             continue
@@ -117,7 +133,17 @@ def _bind():
         raise ImportError("liblodgs.so does not export: %s" % ", ".join(missing))
 
 
-_bind()
+def load():
+    """Map liblodgs.so and bind every entry point of include/lodgs.h (idempotent). Raises ImportError when that is not possible."""
+    if _Lib._cdll is None:
+        cdll = _load()
+        _bind(cdll)
+        _Lib._cdll = cdll
+    return _Lib._cdll
+
+
+def loaded():
+    return _Lib._cdll is not None
 
 
 def last_error():

@@ -50,19 +50,25 @@ def read_less_rich_ply(path):
 
 def activate_and_filter(records, device, skyboxpoints=0):
     """records[count,26] (position 3, normal 3, shs 12, opacity logit 1, log-scale 3, rotation 4) -> (pos, scales, rotations, opacities,
-    shs[.,48]) of the Gaussians the creator keeps: loader activation (GH/loader.cpp:105-124: sigmoid, exp, normalise; a LessRichPoint
-    only carries its three DC coefficients over) and the validity filter of mainHierarchyCreator.cpp:87-149."""
-    r = torch.as_tensor(records[skyboxpoints:], dtype=torch.float32, device=device)
-    pos = r[:, 0:3]
-    opacity = 1.0 / (1.0 + torch.exp(-r[:, 18]))
-    scales = torch.exp(r[:, 19:22])
-    rot = r[:, 22:26]
-    rot = rot / rot.norm(dim=1, keepdim=True)
-    shs = torch.zeros(r.size(0), 48, device=device)
-    shs[:, 0:3] = r[:, 6:9]
-    ok = torch.isfinite(opacity) & ~(scales > 10).any(1) & ~torch.isnan(scales).any(1) & ~torch.isnan(rot).any(1) & \
-        ~torch.isnan(pos).any(1) & ~torch.isnan(shs).any(1) & (opacity != 0)
-    return pos[ok].contiguous(), scales[ok].contiguous(), rot[ok].contiguous(), opacity[ok].contiguous(), shs[ok].contiguous()
+    shs[.,48]) on `device` of the Gaussians the creator keeps: loader activation (GH/loader.cpp:105-124: sigmoid, exp, normalise; a
+    LessRichPoint only carries its three DC coefficients over) and the validity filter of mainHierarchyCreator.cpp:87-149, evaluated
+    on the host by `lodgs_creator_activate` with the creator's libm calls, so the build starts from the creator's bits."""
+    r = np.ascontiguousarray(records[skyboxpoints:], dtype=np.float32)
+    n = r.shape[0]
+    pos, scales, rot = np.empty((n, 3), np.float32), np.empty((n, 3), np.float32), np.empty((n, 4), np.float32)
+    opac, shs, keep = np.empty(n, np.float32), np.empty((n, 48), np.float32), np.empty(n, np.uint8)
+    P = lambda a: a.ctypes.data  # noqa: E731
+    check(lib.lodgs_creator_activate(P(r), n, P(pos), P(scales), P(rot), P(opac), P(shs), P(keep)))
+    k = keep.astype(bool)
+    return tuple(torch.from_numpy(a[k]).to(device) for a in (pos, scales, rot, opac, shs))
+
+
+def log_scales_like_writer(scales):
+    """log(scale) as GH/writer.cpp:119,130 stores it (libm logf on the host) -> CPU tensor."""
+    s = np.ascontiguousarray(scales.detach().cpu().numpy(), dtype=np.float32)
+    out = np.empty_like(s)
+    check(lib.lodgs_logf_host(s.ctypes.data, s.size, out.ctypes.data))
+    return torch.from_numpy(out)
 
 
 def create_dynamic_hierarchy(ply_path, out_prefix, device="cuda"):
@@ -70,6 +76,6 @@ def create_dynamic_hierarchy(ply_path, out_prefix, device="cuda"):
     <out_prefix>hierarchy.dhier with the reference's layout (log-scales, activated opacities, SH degree 3) and returns the build."""
     from gaussian_hierarchy import _C as gh
     h = build_hierarchy(*activate_and_filter(read_less_rich_ply(ply_path), device), dynamic=True, static=False)
-    gh.write_dynamic_hierarchy(out_prefix + "hierarchy.dhier", h["pos"], h["shs"], h["opacities"], torch.log(h["scales"]), h["rotations"],
-                               h["dyn_nodes"], 3)
+    gh.write_dynamic_hierarchy(out_prefix + "hierarchy.dhier", h["pos"], h["shs"], h["opacities"], log_scales_like_writer(h["scales"]),
+                               h["rotations"], h["dyn_nodes"], 3)
     return h

@@ -72,6 +72,46 @@ class Adam(torch.optim.Adam):
         return loss
 
 
+def sh_adam_from_rgb(dL_drgb, campos, means3D, dc, dc_m, dc_v, rest, rest_m, rest_v, degree, lr_dc, lr_rest, betas=(0.9, 0.999), eps=1e-15,
+                     step=1, relevant=None, visible=None, bias_correction=True):
+    """Sparse Adam on the SH coefficients straight from the colour gradient of `_C.rasterize_gaussians_backward_rgb` (`lodgs_sh_adam_from_rgb`,
+    csrc/sh_adam.cu): dL_drgb [V,P,3] or [P,3], campos [V,3] or [3] (CUDA), means3D [P,3] as the forward saw them; dc [P,1,3] / rest [P,K,3]
+    and their moments may be strided row views of one fused [P,1+K,3] tensor (inner dimensions contiguous). Rows: `relevant` (i64 list,
+    OurAdam) or all, optionally masked by `visible` (bool [P], AR). No dL_dsh is ever materialised."""
+    P = means3D.size(0)
+    g = dL_drgb.reshape(-1, P, 3)
+    if not g.is_contiguous():
+        g = g.contiguous()
+    cp = campos.reshape(-1, 3).to(device=means3D.device, dtype=torch.float32).contiguous()
+    if cp.size(0) != g.size(0):
+        raise RuntimeError("sh_adam_from_rgb: one camera centre per view")
+    for t in (dc, dc_m, dc_v):
+        if t.stride(-1) != 1 or t[0].numel() != 3 or t.dtype != torch.float32 or not t.is_cuda:
+            raise RuntimeError("sh_adam_from_rgb: dc tensors must be float32 CUDA rows of 3 contiguous floats")
+    rest_floats = rest[0].numel() if rest is not None and rest.numel() else 0
+    if rest_floats:
+        for t in (rest, rest_m, rest_v):
+            if not t[0].is_contiguous() or t.dtype != torch.float32 or not t.is_cuda:
+                raise RuntimeError("sh_adam_from_rgb: rest tensors must be float32 CUDA rows of contiguous floats")
+    if relevant is not None and relevant.size(0) == 0:
+        relevant = None
+    if relevant is not None:
+        relevant = relevant.to(torch.int64).contiguous()
+    if visible is not None:
+        visible = visible.contiguous()
+        if visible.dtype not in (torch.bool, torch.uint8):
+            visible = visible != 0
+    same = lambda a, b: a.stride(0) == b.stride(0)  # noqa: E731
+    if not (same(dc, dc_m) and same(dc, dc_v)) or (rest_floats and not (same(rest, rest_m) and same(rest, rest_v))):
+        raise RuntimeError("sh_adam_from_rgb: moments must share the layout of their parameter")
+    check(lib.lodgs_sh_adam_from_rgb(P, int(degree), g.size(0), g.data_ptr(), g.stride(0), cp.data_ptr(), means3D.contiguous().data_ptr(),
+                                     ptr(relevant), relevant.numel() if relevant is not None else 0, ptr(visible), dc.data_ptr(), dc_m.data_ptr(),
+                                     dc_v.data_ptr(), dc.stride(0), rest.data_ptr() if rest_floats else None,
+                                     rest_m.data_ptr() if rest_floats else None, rest_v.data_ptr() if rest_floats else None,
+                                     rest.stride(0) if rest_floats else 0, rest_floats, float(lr_dc), float(lr_rest), float(betas[0]),
+                                     float(betas[1]), float(eps), int(step), 1 if bias_correction else 0, current_stream()))
+
+
 def adam_update(param, grad, exp_avg, exp_avg_sq, visible, lr, b1, b2, eps, N, M):
     """AR `_C.adamUpdate(param, grad, exp_avg, exp_avg_sq, visible bool[N], lr, b1, b2, eps, N, M)` (AR/rasterize_points.cu adamUpdate)."""
     _require(param, "param")

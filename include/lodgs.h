@@ -140,6 +140,13 @@ int lodgs_hier_write(const char* filename, int P, int N, const float* pos, const
  * 0 for leaves). Any of dyn_nodes / nodes / boxes may be NULL. Equal coordinates at a split fall as a stable sort leaves them
  * (std::nth_element leaves them unspecified); the eigen-decomposition is a float Jacobi iteration (the reference's is Eigen's). */
 size_t lodgs_hier_build_workspace_bytes(int L);
+/* Host side of the creator around lodgs_hier_build, with the libm calls of the reference so that a .dhier written from the GPU build is
+ * byte-identical to the creator's: lodgs_creator_activate = Loader::loadPly<LessRichPoint> (GH/loader.cpp:105-124: sigmoid, exp,
+ * normalise, DC only) + the validity filter of GH/mainHierarchyCreator.cpp:87-149 on `count` 26-float PLY records (keep[i] = 1 for the
+ * Gaussians the creator keeps); lodgs_logf_host = the `scale.array().log()` of GH/writer.cpp:119,130. Host pointers, no stream. */
+int lodgs_creator_activate(const float* records, int64_t count, float* pos, float* scale, float* rot, float* opacity, float* shs48,
+                           uint8_t* keep);
+int lodgs_logf_host(const float* in, int64_t n, float* out);
 int lodgs_hier_build(int L, int sh_floats, const float* pos, const float* scale, const float* rot, const float* opacity,
                      const float* shs, float* out_pos, float* out_rot, float* out_scale, float* out_opacity, float* out_shs,
                      int32_t* dyn_nodes, int32_t* nodes, float* boxes, void* ws, size_t ws_bytes, void* stream);
@@ -280,6 +287,26 @@ int lodgs_backward_ex(int P, int fullP, int D, int M, int R, int W, int H, const
                       float* dL_dinvdepth, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
                       float* dL_dscale, float* dL_drot, unsigned flags, void* stream);
 
+/* lodgs_backward_ex with the colour gradient exposed in its factored form: dL_drgb [fullP,3] receives, per Gaussian, the gradient of
+ * the loss with respect to its view-dependent colour AFTER the clamp mask (HR/cuda_rasterizer/backward.cu:45-50), i.e. the factor
+ * from which computeColorFromSH's backward forms dL_dsh[k] = basis_k(direction) * dL_drgb (backward.cu:60-131). With dL_drgb given,
+ * dL_dsh may be NULL: the 12*M-byte SH gradient row is then neither written nor re-read, and lodgs_sh_adam_from_rgb applies the
+ * optimizer step to the SH coefficients directly from dL_drgb (of one view, or of the views of several GPUs: multi-view training
+ * exchanges 12 bytes per Gaussian and view instead of an all-reduce over 12*M). Rows of culled Gaussians are set to zero when the
+ * call has no index list and no parents (as lodgs_backward_overwrites_geometry reports); otherwise the caller zero-fills dL_drgb.
+ * Children with parents (LOD redirect) leave their row untouched, like their dL_dsh row (backward.cu:489-493). */
+int lodgs_backward_rgb(int P, int fullP, int D, int M, int R, int W, int H, const float* background,
+                       const int32_t* indices, const int32_t* parent_indices, const float* ts, const int32_t* kids,
+                       const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
+                       const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                       const float* viewmatrix, const float* projmatrix, const float* campos,
+                       float tan_fovx, float tan_fovy, const int32_t* radii,
+                       void* geom_buffer, void* binning_buffer, void* image_buffer,
+                       const float* dL_dpix, const float* dL_dinvdepth_pix,
+                       float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                       float* dL_dinvdepth, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
+                       float* dL_dscale, float* dL_drot, float* dL_drgb, unsigned flags, void* stream);
+
 /* 1 when lodgs_backward will write every row of dL_dsh[0..P) itself (no index list, SH rows a multiple of 16 bytes, 16-byte
  * aligned pointers): the caller may then pass an uninitialised dL_dsh instead of the zero-filled one the reference
  * allocates (rasterize_points.cu:183). */
@@ -352,6 +379,24 @@ int lodgs_adam_step_multi(int n_tensors, float* const* params, const float* cons
                           float* const* exp_avg_sqs, const int64_t* relevant, int64_t n_relevant, const uint8_t* visible,
                           const int64_t* rows, const int32_t* widths, const double* lrs, const double* betas1, const double* betas2,
                           const double* epss, const int64_t* steps, int bias_correction, void* stream);
+
+/* Sparse Adam on the SH coefficients straight from the colour gradient(s) of lodgs_backward_rgb: the fusion of the preprocess
+ * backward's SH part (HR/cuda_rasterizer/backward.cu:23-142) with the optimizer step (scene/OurAdam.py:251-354; AR adamUpdateCUDA,
+ * AR/cuda_rasterizer/adam.cu:9-38) — the gradient row dL_dsh[row] = sum over views of basis(normalize(mean - campos_v)) (x)
+ * dL_drgb[v][row] is rebuilt in registers and never touches HBM.
+ *   dL_drgb [n_views] blocks of [P,3], view_stride floats apart (3*P when packed; an all-gather of every rank's block in multi-view
+ *   training), campos [n_views,3] (device), means3D [P,3] = the means the forward used.
+ *   dc / rest: the two SH parameter tensors of a Gaussian model (scene/gaussian_model.py _features_dc [P,1,3], _features_rest
+ *   [P,15,3]) with their first and second moments in the same layout; *_stride = floats between consecutive rows, so one fused
+ *   [P,16,3] tensor is dc = shs, rest = shs + 3, both strides 48. rest_floats = 3 * (coefficients in rest), 0 allowed.
+ *   Rows: `relevant` index list (OurAdam) or all `rows`, optionally masked by `visible` u8[P] (AR). Coefficients above degree D get
+ *   a zero gradient (their moments still decay), as the zero-filled dL_dsh of the reference does.
+ * Arithmetic, bias_correction and step as lodgs_adam_step. Views are added in index order on every rank: replicas stay bit-identical. */
+int lodgs_sh_adam_from_rgb(int64_t rows, int D, int n_views, const float* dL_drgb, int64_t view_stride, const float* campos,
+                           const float* means3D, const int64_t* relevant, int64_t n_relevant, const uint8_t* visible,
+                           float* dc, float* dc_m, float* dc_v, int dc_stride, float* rest, float* rest_m, float* rest_v,
+                           int rest_stride, int rest_floats, double lr_dc, double lr_rest, double beta1, double beta2, double eps,
+                           int64_t step, int bias_correction, void* stream);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

@@ -55,6 +55,73 @@ int orc_expand_to_size(const int32_t* nodes, const float* boxes, int N, float ta
     return off;
 }
 
+/* The same cut with the reference's three-stage structure spread over the host cores (markNodesForSize :495-529 -> inclusive scan
+ * :1021-1023 -> putRenderIndices :68-93): counts in parallel, a two-level scan over contiguous node chunks, scatter in parallel.
+ * Identical output to orc_expand_to_size; `counts` is caller scratch of N ints. Returns K; *threads_used reports the team size. */
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+int orc_expand_to_size_omp(const int32_t* nodes, const float* boxes, int N, float tau, const float* viewpoint, int32_t* render_indices,
+                           int32_t* parent_indices, int32_t* node_ids, int32_t* counts, int* threads_used) {
+    int T = 1;
+#ifdef _OPENMP
+    T = omp_get_max_threads();
+#endif
+    if (T > 256) T = 256;
+    long chunk_sum[257];
+    int total = 0;
+#pragma omp parallel num_threads(T)
+    {
+        int t = 0, nt = 1;
+#ifdef _OPENMP
+        t = omp_get_thread_num();
+        nt = omp_get_num_threads();
+#endif
+        const long lo = (long)N * t / nt, hi = (long)N * (t + 1) / nt;
+        long sum = 0;
+        for (long i = lo; i < hi; i++) {
+            const int32_t* n = nodes + i * 7;
+            float size = box_size(boxes + i * 8, viewpoint);
+            int count = 0;
+            if (size >= tau) {
+                count = n[3];
+            } else if (n[1] != -1) {
+                float psize = box_size(boxes + (long)n[1] * 8, viewpoint);
+                if (psize >= tau) {
+                    count = n[3];
+                    if (n[0] != 0) count += n[4];
+                }
+            }
+            counts[i] = count;
+            sum += count;
+        }
+        chunk_sum[t + 1] = sum;
+#pragma omp barrier
+#pragma omp single
+        {
+            chunk_sum[0] = 0;
+            for (int k = 0; k < nt; k++) chunk_sum[k + 1] += chunk_sum[k];
+            total = (int)chunk_sum[nt];
+            if (threads_used) *threads_used = nt;
+        }
+        long off = chunk_sum[t];
+        for (long i = lo; i < hi; i++) {
+            const int32_t* n = nodes + i * 7;
+            const int count = counts[i];
+            if (!count) continue;
+            int parentgaussian = -1;
+            if (n[1] != -1) parentgaussian = nodes[(long)n[1] * 7 + 2];
+            for (int k = 0; k < count; k++) {
+                render_indices[off] = n[2] + k;
+                if (parent_indices) parent_indices[off] = parentgaussian;
+                if (node_ids) node_ids[off] = (int32_t)i;
+                off++;
+            }
+        }
+    }
+    return total;
+}
+
 void orc_get_interpolation_weights(const int32_t* indices, int K, float tau, const int32_t* nodes, const float* boxes, const float* viewpoint,
                                    float* ts, int32_t* kids) {
     for (int idx = 0; idx < K; idx++) {

@@ -77,6 +77,23 @@ def expand_to_size(nodes, boxes, tau, viewpoint):
     return ri[:K].copy(), pi[:K].copy(), ni[:K].copy()
 
 
+def expand_to_size_omp(nodes, boxes, tau, viewpoint, bufs=None):
+    """orc_expand_to_size_omp (all host cores) -> (render_indices[K], parent_indices[K], node_ids[K], threads used). `bufs` = reusable
+    (ri, pi, ni, counts) arrays of length >= N (one Gaussian per node) for timing loops."""
+    import ctypes as C
+    nodes, boxes, vp = _c(nodes, np.int32), _c(boxes, np.float32), _c(viewpoint, np.float32)
+    N = nodes.shape[0]
+    if bufs is None:
+        cap = int(np.maximum(nodes[:, 3] + nodes[:, 4], 1).sum())
+        bufs = tuple(np.zeros(max(cap, N), np.int32) for _ in range(4))
+    ri, pi, ni, counts = bufs
+    used = C.c_int(0)
+    fn = lib().orc_expand_to_size_omp
+    fn.restype = C.c_int
+    K = fn(_i(nodes), _f(boxes), N, C.c_float(float(tau)), _f(vp), _i(ri), _i(pi), _i(ni), _i(counts), C.byref(used))
+    return ri[:K], pi[:K], ni[:K], used.value
+
+
 def get_interpolation_weights(node_ids, tau, nodes, boxes, viewpoint):
     idx, nodes, boxes, vp = _c(node_ids, np.int32), _c(nodes, np.int32), _c(boxes, np.float32), _c(viewpoint, np.float32)
     K = idx.shape[0]

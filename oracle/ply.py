@@ -4,9 +4,22 @@ input.ply of BASELINE.json configs[0] is not in the reference tree (.MISSING_LAR
 import numpy as np
 
 
-def synth_points(n, seed=0, extent=(40.0, 40.0, 4.0), scale_mean=0.05):
+def synth_points(n, seed=0, extent=(40.0, 40.0, 4.0), scale_mean=0.05, distinct=True):
+    """Seeded Gaussians. `distinct`: no two points share a coordinate on any axis (duplicates are nudged to the next float): the kd-tree
+    split then selects a unique SET at every node — std::nth_element leaves the order of equal keys unspecified, so with ties the
+    reference creator's own result is one of several valid ones."""
     rng = np.random.default_rng(seed)
     pos = (rng.random((n, 3), dtype=np.float32) - 0.5) * np.asarray(extent, np.float32)
+    if distinct:
+        for a in range(3):
+            order = np.argsort(pos[:, a], kind="stable")
+            s = pos[order, a].copy()
+            while True:
+                dup = np.nonzero(s[1:] <= s[:-1])[0]
+                if dup.size == 0:
+                    break
+                s[dup + 1] = np.nextafter(s[dup], np.float32(np.inf))
+            pos[order, a] = s
     shs = np.concatenate([rng.normal(0.5, 0.5, (n, 3)) / 0.2821, rng.normal(0, 0.1, (n, 9))], 1).astype(np.float32)
     opacity = rng.normal(0.0, 2.0, (n, 1)).astype(np.float32)
     log_scale = rng.normal(np.log(scale_mean), 0.6, (n, 3)).astype(np.float32)

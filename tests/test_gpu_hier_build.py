@@ -70,26 +70,17 @@ def test_build_matches_reference_creator(tmp_path, n, seed):
 
 
 @pytest.mark.skipif(not rh.creator_available(), reason="oracle/_ref/GaussianHierarchyCreator not built")
-def test_create_dynamic_hierarchy_from_ply_end_to_end(tmp_path):
-    """The product path from a PLY (torch activation on the device, 1 ulp off the creator's libm) against the creator binary: same
-    node table unless a split decision sits on a rounding edge; Gaussians to tolerance; and the written file loads back."""
-    n = 3000
+@pytest.mark.parametrize("n,seed", [(3000, 9), (100000, 10)])
+def test_create_dynamic_hierarchy_writes_the_creators_file(tmp_path, n, seed):
+    """The product path from a PLY (tools/create_hierarchy.py: host activation with the creator's libm calls, GPU build, .dhier writer)
+    against the creator binary run on the same PLY: the two hierarchy.dhier files are byte-identical."""
+    import filecmp
     plyf = str(tmp_path / "in.ply")
-    oply.write_less_rich_ply(plyf, *oply.synth_points(n, seed=9))
+    oply.write_less_rich_ply(plyf, *oply.synth_points(n, seed=seed))
     rh.run_creator(plyf, str(tmp_path) + "/ref_")
-    r_pos, r_shs, r_op, r_ls, r_rot, r_nodes = gh.load_dynamic_hierarchy(str(tmp_path) + "/ref_hierarchy.dhier")
-    h = hier_build.create_dynamic_hierarchy(plyf, str(tmp_path) + "/ours_")
+    hier_build.create_dynamic_hierarchy(plyf, str(tmp_path) + "/ours_")
     torch.cuda.synchronize()
-    o_pos, o_shs, o_op, o_ls, o_rot, o_nodes = gh.load_dynamic_hierarchy(str(tmp_path) + "/ours_hierarchy.dhier")
-    assert torch.equal(o_nodes, h["dyn_nodes"].cpu()) and torch.equal(o_pos, h["pos"].cpu())
-    assert torch.equal(o_nodes[:, :5], r_nodes[:, :5])                 # the shape of the tree depends on the leaf count alone
-    if torch.equal(o_nodes, r_nodes):
-        N = 2 * n - 1
-        assert float((o_pos - r_pos).abs().max()) <= 1e-5 * float(r_pos.abs().max())
-        assert torch.allclose(o_op, r_op, rtol=2e-4, atol=1e-7)
-        ca, cb = _cov(torch.exp(o_ls), o_rot), _cov(torch.exp(r_ls), r_rot)
-        assert float(((ca - cb).flatten(1).norm(dim=1) / cb.flatten(1).norm(dim=1)).max()) <= 2e-3
-        assert float((o_shs - r_shs).abs().max()) <= 1e-5 * max(1.0, float(r_shs.abs().max()))
+    assert filecmp.cmp(str(tmp_path) + "/ours_hierarchy.dhier", str(tmp_path) + "/ref_hierarchy.dhier", shallow=False)
 
 
 def _upstream_populate(dyn):
