@@ -95,6 +95,8 @@ _SIGS = {
     "lodgs_spt_cut_workspace_bytes": (_sz, [_i]),
     "lodgs_spt_cut_count": (_i, [_i, _p, _i, _p, _p, _p, _p, _p, _p, _p, _sz, _p, _p]),
     "lodgs_spt_cut_write": (_i, [_i, _p, _i, _p, _p, _p, _p, _p, _p, _i, _p]),
+    "lodgs_upper_cut_workspace_bytes": (_sz, [_i]),
+    "lodgs_upper_tree_cut": (_i, [_p, _i, _i, _p, _p, _p, _i, _p, _p, _f, _p, _i, _p, _p, _p, _p, _p, _sz, _p, _p]),
     "lodgs_get_morton_codes": (_i, [_p, _p, _p, _p, _i, _p]),
     "lodgs_compute_relocation": (_i, [_i, _p, _p, _p, _p, _i, _p, _p, _p]),
     "lodgs_geom_layout": (_i, [_i, _p]),

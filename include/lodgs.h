@@ -109,6 +109,24 @@ int lodgs_spt_cut_write(int S, const int32_t* gaussian_indices, int n_entries, c
                         const int32_t* SPT_indices, const float* SPT_distances, const void* ws, int32_t* cut_out, int capacity,
                         void* stream);
 
+/* Cut of the "upper tree" that precedes the SPT cut — one level-synchronous kernel. Replaces the per-frame torch code
+ * GaussianModel.cut_hierarchy_on_condition (scene/gaussian_model.py:354-394) with its cull GaussianModel.frustum_cull_spheres (:80-103)
+ * and LOD condition `min_distance_squared[i] > |campos - xyz[i]|^2 * distance_multiplier` (train_post.py:336-339), plus the split of
+ * the result that feeds get_spt_cut_cuda (train_post.py:349-356). nodes [N,6] i32 = upper_tree_nodes {depth, parent, child_count,
+ * first_child (leaves: SPT index, or <= 0 for none), next_sibling, gaussian index}; xyz [N,3]; bounds [N] bounding-sphere radii or NULL
+ * (no culling); planes [n_planes,4] normalised (nx,ny,nz,d) as extract_frustum_planes builds them (:55-78), 16-byte aligned;
+ * min_dist_sq [N]; campos [3]; all on the device. Outputs in the reference's order (per level: leaves of the culled stack, then the
+ * nodes failing the condition; next stack = first children then their next siblings): cut [capacity] node ids; for the cut's leaves,
+ * in cut order: spt_indices / spt_nodes / spt_distances (leaves with first_child >= 0: SPT id, node id, |xyz - campos| *
+ * distance_multiplier) and direct (gaussian index of leaves with first_child <= 0) — each [capacity] or NULL. counts_host (3 ints:
+ * cut, SPT slots, direct leaves) is filled through a mapped pinned word when non-NULL (NULL: nothing is read back, the counts
+ * stay in the first 12 bytes of ws). */
+size_t lodgs_upper_cut_workspace_bytes(int N);
+int lodgs_upper_tree_cut(const int32_t* nodes, int N, int root, const float* xyz, const float* bounds, const float* planes, int n_planes,
+                         const float* min_dist_sq, const float* campos, float distance_multiplier, int32_t* cut, int capacity,
+                         int32_t* spt_indices, int32_t* spt_nodes, float* spt_distances, int32_t* direct, void* ws, size_t ws_bytes,
+                         int32_t* counts_host, void* stream);
+
 /* Morton codes. Replaces MORTON::getMortonCode (GH/morton.cu:9-60) as bound by gaussian_hierarchy._C.get_morton_indices
  * (torch_interface.cpp GetMortonCode; scene/gaussian_model.py:574). xyz f32[P,3]; min3/max3 = 3 floats each ON THE DEVICE;
  * codes i64[P]: bits 0..20 of trunc((c - min) / (max - min) * 2^21) per axis, interleaved x, y, z from bit 0. */
