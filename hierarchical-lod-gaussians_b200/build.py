@@ -19,7 +19,7 @@ FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std
 
 # per-file additions: the hierarchy builder mirrors the reference creator's host arithmetic, which a default x86-64 build evaluates
 # without fused multiply-adds, so its kernels are compiled without FMA contraction
-EXTRA = {"hier_build.cu": ["-fmad=false"]}
+EXTRA = {"hier_build.cu": ["-fmad=false"], "page.cu": ["-Xcompiler", "-fopenmp"]}   # page.cu: host row gather / scatter over the cores
 
 
 def _sources():
@@ -56,7 +56,7 @@ def build(force=False, verbose=True):
         raise RuntimeError("nvcc not found at %s and no prebuilt %s matches the sources" % (NVCC, LIB))
     with cf.ThreadPoolExecutor(max_workers=8) as ex:
         objs = list(ex.map(_compile, _sources()))
-    cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"]
+    cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-Xcompiler", "-fopenmp"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n%s\n%s" % (r.stdout, r.stderr))

@@ -97,6 +97,13 @@ _SIGS = {
     "lodgs_spt_cut_write": (_i, [_i, _p, _i, _p, _p, _p, _p, _p, _p, _i, _p]),
     "lodgs_upper_cut_workspace_bytes": (_sz, [_i]),
     "lodgs_upper_tree_cut": (_i, [_p, _i, _i, _p, _p, _p, _i, _p, _p, _f, _p, _i, _p, _p, _p, _p, _p, _sz, _p, _p]),
+    "lodgs_page_workspace_bytes": (_sz, [_i64]),
+    "lodgs_page_plan": (_i, [_p, _i64, _p, _p, _sz, _p, _p]),
+    "lodgs_page_apply": (_i, [_p, _i64, _i, _p, _p, _p, _p, _i64, _i64, _p]),
+    "lodgs_host_scatter_rows": (_i, [_p, _i64, _i64, _p, _i64, _p]),
+    "lodgs_host_gather_rows": (_i, [_p, _i64, _i64, _p, _i64, _p]),
+    "lodgs_l1_ssim_workspace_bytes": (_sz, [_i, _i, _i]),
+    "lodgs_l1_ssim_loss": (_i, [_p, _p, _i, _i, _i, _f, _f, _f, _p, _p, _p, _sz, _p]),
     "lodgs_get_morton_codes": (_i, [_p, _p, _p, _p, _i, _p]),
     "lodgs_compute_relocation": (_i, [_i, _p, _p, _p, _p, _i, _p, _p, _p]),
     "lodgs_geom_layout": (_i, [_i, _p]),

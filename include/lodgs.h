@@ -127,6 +127,33 @@ int lodgs_upper_tree_cut(const int32_t* nodes, int N, int root, const float* xyz
                          int32_t* spt_indices, int32_t* spt_nodes, float* spt_distances, int32_t* direct, void* ws, size_t ws_bytes,
                          int32_t* counts_host, void* stream);
 
+/* CPU <-> GPU paging of parameter and Adam-moment rows between training iterations. Replaces train_post.py:440-479 (write-back of the
+ * rows leaving the render set into host storage, `tensor[keep_mask]`, `cat(kept, storage[load_indices].cuda())`, for 6 parameter and 12
+ * moment tensors). lodgs_page_plan scans the keep mask ONCE: dst[i] = slot of resident row i among the kept rows (>= 0), or -1 - slot
+ * among the evicted rows, both in the original order (what boolean-mask indexing yields); counts_host[0..1] = kept, evicted (through a
+ * mapped pinned word; NULL = not read back, they stay in the first 8 bytes of ws). lodgs_page_apply, per tensor of `width` floats per
+ * row: out[dst] = kept rows, out[n_keep + j] = loaded[j] (the rows just copied up from host storage, device staging [n_load,width]),
+ * evict[-1 - dst] = evicted rows (device staging [evicted,width], NULL to drop them). The transfers between device staging and pinned
+ * host staging are one cudaMemcpyAsync each (the caller's); lodgs_host_scatter_rows / lodgs_host_gather_rows move whole rows between
+ * pinned staging and the big host storage tensors with memcpy over the host cores (storage[indices[i]] = staging[i] and the reverse). */
+size_t lodgs_page_workspace_bytes(int64_t n);
+int lodgs_page_plan(const uint8_t* keep_mask, int64_t n, int32_t* dst, void* ws, size_t ws_bytes, int32_t* counts_host, void* stream);
+int lodgs_page_apply(const float* src, int64_t n, int width, const int32_t* dst, float* out, float* evict, const float* loaded,
+                     int64_t n_load, int64_t n_keep, void* stream);
+int lodgs_host_scatter_rows(void* storage, int64_t storage_rows, int64_t row_bytes, const int64_t* indices, int64_t n, const void* staging);
+int lodgs_host_gather_rows(const void* storage, int64_t storage_rows, int64_t row_bytes, const int64_t* indices, int64_t n, void* staging);
+
+/* Fused L1 + SSIM image loss, forward and backward. Replaces the loss of the training loops, train_post.py:558-559 / train_single.py:
+ * 106-110: `(1 - lambda) * l1_loss(image, gt) + lambda * (1 - fused_ssim(image[None], gt[None]))` with l1_loss / ssim of utils/loss_utils.py:
+ * 17-18,33-63 (11x11 Gaussian window, sigma 1.5, zero padding, C1 = 0.01^2, C2 = 0.03^2; `fused_ssim` is an external package computing
+ * the same SSIM). img, gt [C,H,W] on the device. out3 (device, 3 floats) = { a_l1 * mean|img - gt| + a_ssim * mean(ssim) + bias, mean|img - gt|,
+ * mean(ssim) }; dL_dimg [C,H,W] (optional) = gradient of out3[0] with respect to img. The training loss is a_l1 = 1 - lambda,
+ * a_ssim = -lambda, bias = lambda; fused_ssim alone is a_l1 = 0, a_ssim = 1, bias = 0. ws: lodgs_l1_ssim_workspace_bytes (3 derivative
+ * maps + block partial sums). Sums are reduced in a fixed order in double: the result is deterministic. */
+size_t lodgs_l1_ssim_workspace_bytes(int C, int H, int W);
+int lodgs_l1_ssim_loss(const float* img, const float* gt, int C, int H, int W, float a_l1, float a_ssim, float bias, float* out3,
+                       float* dL_dimg, void* ws, size_t ws_bytes, void* stream);
+
 /* Morton codes. Replaces MORTON::getMortonCode (GH/morton.cu:9-60) as bound by gaussian_hierarchy._C.get_morton_indices
  * (torch_interface.cpp GetMortonCode; scene/gaussian_model.py:574). xyz f32[P,3]; min3/max3 = 3 floats each ON THE DEVICE;
  * codes i64[P]: bits 0..20 of trunc((c - min) / (max - min) * 2^21) per axis, interleaved x, y, z from bit 0. */
