@@ -9,10 +9,10 @@ What differs from diff_gaussian_rasterization and how it is mapped:
   gradient split again (one extra copy each way; the kernels want the coefficients of a Gaussian contiguous);
 * per-Gaussian backward over 32-splat buckets with a `sampleBuffer` of per-bucket pixel states (AR/cuda_rasterizer/
   rasterizer_impl.cu:288-295, backward.cu:451-656): the tile-reduced backward of csrc/blend_bwd.cu computes the same
-  gradients without that state, so `sampleBuffer` is empty and `num_buckets` (which only sizes that state) is counted over
-  the un-culled tile lists: the reference drops (Gaussian, tile) instances that cannot reach alpha 1/255 anywhere inside the
-  tile before counting (rasterizer_impl.cu:143-187) — pairs the blend kernels here skip per pixel with the same result —
-  so the value returned here is an upper bound of the reference's;
+  gradients without that state, so `sampleBuffer` is empty; `num_buckets` (which only sizes that state) is still the reference's
+  value: the reference drops (Gaussian, tile) instances that cannot reach alpha 1/255 anywhere inside the tile before counting
+  (rasterizer_impl.cu:143-187) — pairs the blend kernels here skip per pixel with the same result — and csrc/ar_buckets.cu
+  evaluates that tile test on the sorted instance list just to report the same count;
 * two quirks of AR's backward are reproduced on request of this module (LODGS_RASTER_BACKGROUND_TWICE,
   LODGS_RASTER_CLAMPED_ALPHA_GRAD, see include/lodgs.h): the background term of dL/dalpha counted twice, and no gradient
   cut for alphas clamped at 0.99;
@@ -54,13 +54,14 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         tan_fovx, tan_fovy, image_height, image_width, shs, degree, campos, prefiltered, debug, True, _flags(antialiasing))
     num_buckets = 0
     if rendered > 0:
-        # sum over tiles of ceil(range length / 32) (AR/cuda_rasterizer/rasterizer_impl.cu:223-232, :464-469)
+        # the reference's value: per-tile lists after ITS tile-level opacity cull, ceil(length / 32) summed (csrc/ar_buckets.cu)
         import ctypes as C
-        o = (C.c_size_t * 3)()
-        lodgs.lib.lodgs_image_layout(int(image_width), int(image_height), o)
         ntiles = ((int(image_width) + 15) // 16) * ((int(image_height) + 15) // 16)
-        ranges = img[o[2]:o[2] + ntiles * 8].view(torch.int32).reshape(ntiles, 2)
-        num_buckets = int((((ranges[:, 1] - ranges[:, 0]).clamp_min(0) + 31) // 32).sum().item())
+        ws = torch.empty(ntiles * 4 + 512, dtype=torch.uint8, device=dev)
+        out2 = (C.c_int32 * 2)()
+        lodgs.check(lodgs.lib.lodgs_ar_bucket_count(radii.numel(), int(image_width), int(image_height), int(rendered), geom.data_ptr(),
+                                                    binning.data_ptr(), ws.data_ptr(), ws.numel(), out2, lodgs.current_stream()))
+        num_buckets = int(out2[0])
     sample = torch.empty(0, dtype=torch.uint8, device=dev)
     return rendered, num_buckets, color, invdepth, radii, geom, binning, img, sample
 

@@ -91,6 +91,7 @@ _SIGS = {
                                 _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, C.c_uint, _p]),
     "lodgs_sh_adam_from_rgb": (_i, [_i64, _i, _i, _p, _i64, _p, _p, _p, _i64, _p, _p, _p, _p, _i, _p, _p, _p, _i, _i, _d, _d, _d, _d, _d,
                                     _i64, _i, _p]),
+    "lodgs_ar_bucket_count": (_i, [_i, _i, _i, _i, _p, _p, _p, _sz, _p, _p]),
     "lodgs_mark_visible": (_i, [_i, _p, _p, _p, _p, _p]),
     "lodgs_spt_cut_workspace_bytes": (_sz, [_i]),
     "lodgs_spt_cut_count": (_i, [_i, _p, _i, _p, _p, _p, _p, _p, _p, _p, _sz, _p, _p]),

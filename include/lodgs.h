@@ -352,6 +352,13 @@ int lodgs_backward_rgb(int P, int fullP, int D, int M, int R, int W, int H, cons
                        float* dL_dinvdepth, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
                        float* dL_dscale, float* dL_drot, float* dL_drgb, unsigned flags, void* stream);
 
+/* The alt-rasterizer's bucket count, exactly (second value of AR's rasterize_gaussians 9-tuple, AR/rasterize_points.cu:116): after
+ * lodgs_forward_render of a LODGS_RASTER_SQUARE_RECT forward, out2_host[0] = sum over tiles of ceil(n_t / 32) and out2_host[1] = sum of n_t,
+ * n_t = instances of tile t that survive the reference's per-tile opacity test (AR/cuda_rasterizer/rasterizer_impl.cu:56-100,143-187,
+ * 223-232). ws: device scratch of at least 4 * tiles + 256 bytes. */
+int lodgs_ar_bucket_count(int P, int W, int H, int R, void* geom_buffer, void* binning_buffer, void* ws, size_t ws_bytes,
+                          int32_t* out2_host, void* stream);
+
 /* 1 when lodgs_backward will write every row of dL_dsh[0..P) itself (no index list, SH rows a multiple of 16 bytes, 16-byte
  * aligned pointers): the caller may then pass an uninitialised dL_dsh instead of the zero-filled one the reference
  * allocates (rasterize_points.cu:183). */
