@@ -25,15 +25,24 @@ static int set_lod_cut() {
 }
 
 
-constexpr int BWD_BATCH = 128;
-constexpr int BWD_THREADS = 128;  // 16 x 8 threads, two vertically adjacent pixels each (a warp covers a 16x4 block)
 constexpr int NV = 10;  // dmean.x dmean.y dconic.xx dconic.xy dconic.yy dopacity dcol.r dcol.g dcol.b dinvdepth
 
-struct BwdSmem {
-    SplatRec recs[2][BWD_BATCH];
-    float acc[2][BWD_BATCH * NV];
+// Q = vertically adjacent pixel PAIRS per thread. A CTA is one 16x16 tile, so it has 128 / Q threads: Q = 1 is 16 x 8 threads with two pixels
+// each (a warp covers 16x4 pixels), Q = 2 is 16 x 4 threads with a column of four pixels each (a warp covers 16x8). Everything that is paid once
+// per (warp, splat) — the three record loads, the loop, the two votes, the 12-shuffle reduction and the shared atomics — is shared by twice
+// the pixels with Q = 2. The batch (splats gathered per round, one per thread) shrinks with the CTA.
+template <int Q>
+struct BwdCfg {
+    static constexpr int THREADS = 128 / Q;
+    static constexpr int BATCH = THREADS;
+};
+
+template <int Q>
+struct BwdSmemT {
+    SplatRec recs[2][BwdCfg<Q>::BATCH];
+    float acc[2][BwdCfg<Q>::BATCH * NV];
     uint64_t bar[2];
-    unsigned warp_max[BWD_THREADS / 32];
+    unsigned warp_max[BwdCfg<Q>::THREADS / 32];
 };
 
 __device__ __forceinline__ float ex2_ftz(float x) {
@@ -90,102 +99,124 @@ __device__ __forceinline__ float warp_reduce10(const float (&v)[NV], unsigned la
 // Splat constants enter as broadcast operands (mov.b64 {x,x} folds into the instruction). ptxas contracts mul+add pairs of
 // packed operations even with .rn; harmless here (gradients are held to 1e-3, not bit-exact) — the FORWARD kernel, whose
 // rounding is pinned, restricts itself to the packed forms ptxas cannot re-contract (see blend_fwd.cu).
-// Replay state of the thread's two pixels (lo = upper pixel, hi = the one below it).
-struct BwdPix2 {
-    f2 npy, T, T_final, last_alpha, ar0, ar1, ar2, ar_invd, g0, g1, g2, gd, nbg_dot;
-    float px, lc0, lc1, lc2, last_invd;  // the colour / inverse depth of the previously processed splat is the same for both pixels
-    unsigned last0, last1;
+// Replay state of the thread's Q pixel pairs (pair h: lo = row 2h of the thread's column, hi = the one below it).
+template <int Q>
+struct BwdPix {
+    f2 T[Q], Tfn[Q], last_alpha[Q], ar0[Q], ar1[Q], ar2[Q], ar_invd[Q], g0[Q], g1[Q], g2[Q], gd[Q];  // Tfn = T_final * (-bg_mult * bg . dL_dpixel)
+    f2 npy;  // -(y) of pair 0; pair h lies 2h rows further down
+    float px, lc0, lc1, lc2, last_invd;  // the colour / inverse depth of the previously processed splat is the same for all pixels of the warp
+    unsigned last[2 * Q];
 };
 
-// One splat against both pixels (backward.cu:600-716). A pixel the splat does not contribute to (behind its last contributor,
+// One splat against the thread's 2Q pixels (backward.cu:600-716). A pixel the splat does not contribute to (behind its last contributor,
 // power > 0, below the cut-off or alpha < 1/255) takes part as a ZERO-ALPHA splat: T / (1 - 0) = T, the running colour
 // recurrence ar' = last_alpha*lc + (1-last_alpha)*ar passes through it unchanged (the next splat sees last_alpha = 0), and
 // its k is forced to 0 — so no per-pixel branches and no per-pixel copies of the previous colour are needed. The same holds
-// for a whole LANE: the two early-outs are warp votes (the return value is warp-uniform), a lane whose pixels both skip the
+// for a whole LANE: the two early-outs are warp votes (the return value is warp-uniform), a lane whose pixels all skip the
 // splat produces ten exact zeros, so there is no divergence inside the loop and nothing to clear before the reduction.
-template <bool LOD, bool DEPTH>
-__device__ __forceinline__ bool bwd_pair2(BwdPix2& p, const unsigned pos, const float4 q0, const float4 q1, const float4 q2,
+template <bool LOD, bool DEPTH, int Q>
+__device__ __forceinline__ bool bwd_splat(BwdPix<Q>& p, const unsigned pos, const float4 q0, const float4 q1, const float4 q2,
                                           const float null_thr, float (&v)[NV]) {
     const float dx = q0.x - p.px;
-    const f2 dy = add2(bc(q0.y), p.npy);
-    const f2 quad = fma2(dy, mul2(dy, bc(q1.x)), bc(dx * (dx * q0.z)));
-    const f2 power = fma2(dy, bc(-(dx * q0.w)), mul2(quad, bc(-0.5f)));
-    const float pw0 = lo(power), pw1 = hi(power);
-    bool ok0 = pos < p.last0 && !(pw0 > 0.0f), ok1 = pos < p.last1 && !(pw1 > 0.0f);
-    if (!LOD) {  // certainly below the 1/255 cut (cut-off stored by the preprocess kernel)
-        ok0 = ok0 && !(pw0 < q2.z);
-        ok1 = ok1 && !(pw1 < q2.z);
-    } else {     // the same cut rebuilt per splat (LOD alpha <= opacity*exp(power) for t in [0,1], kids >= 1; see blend_fwd.cu)
-        const float cut = (c_lod_cut && q2.z >= 0.0f && q2.z <= 1.0f && q2.w > 0.0f && q2.w <= 1.0f) ? -__logf(255.0f * q1.y) - 0.02f : -__builtin_huge_valf();
-        ok0 = ok0 && !(pw0 < cut);
-        ok1 = ok1 && !(pw1 < cut);
+    const float dxx = dx * (dx * q0.z), ndxy = -(dx * q0.w);
+    float cut;
+    if (!LOD) cut = q2.z;  // certainly below the 1/255 cut (cut-off stored by the preprocess kernel)
+    else      // the same cut rebuilt per splat (LOD alpha <= opacity*exp(power) for t in [0,1], kids >= 1; see blend_fwd.cu)
+        cut = (c_lod_cut && q2.z >= 0.0f && q2.z <= 1.0f && q2.w > 0.0f && q2.w <= 1.0f) ? -__logf(255.0f * q1.y) - 0.02f : -__builtin_huge_valf();
+    f2 dy[Q], power[Q];
+    bool ok[2 * Q];
+    bool any = false;
+#pragma unroll
+    for (int h = 0; h < Q; h++) {
+        dy[h] = add2(bc(q0.y - 2.0f * h), p.npy);
+        const f2 quad = fma2(dy[h], mul2(dy[h], bc(q1.x)), bc(dxx));
+        power[h] = fma2(dy[h], bc(ndxy), mul2(quad, bc(-0.5f)));
+        const float pw0 = lo(power[h]), pw1 = hi(power[h]);
+        ok[2 * h] = pos < p.last[2 * h] && !(pw0 > 0.0f) && !(pw0 < cut);
+        ok[2 * h + 1] = pos < p.last[2 * h + 1] && !(pw1 > 0.0f) && !(pw1 < cut);
+        any = any || ok[2 * h] || ok[2 * h + 1];
     }
-    if (!__any_sync(0xffffffffu, ok0 || ok1)) return false;  // warp-uniform: lanes without a contribution ride along with alpha 0
+    if (!__any_sync(0xffffffffu, any)) return false;  // warp-uniform: lanes without a contribution ride along with alpha 0
     // ex2.approx.ftz on power * log2(e) instead of the forward's full-range expf: alpha moves by ~1e-7 relative, far inside the
-    // gradient budget; flushing results below 2^-126 is immaterial (alpha < 1/255 is skipped two lines further down)
-    const f2 pl = mul2(power, bc(1.4426950408889634f));
-    const f2 G = pk(ex2_ftz(lo(pl)), ex2_ftz(hi(pl)));
-    const f2 ta = mul2(bc(q1.y), G);
-    const float ta0 = lo(ta), ta1 = hi(ta);
-    const float ma0 = fminf(0.99f, ta0), ma1 = fminf(0.99f, ta1);
-    float a0 = ma0, a1 = ma1, t = 1.f, frac = 1.f;
-    if (LOD) {
-        t = q2.z;
-        frac = q2.w;
-        a0 = fmaf(ma0, t, (1.0f - t) * (1.0f - __powf(1.0f - ma0, frac)));
-        a1 = fmaf(ma1, t, (1.0f - t) * (1.0f - __powf(1.0f - ma1, frac)));
+    // gradient budget; flushing results below 2^-126 is immaterial (alpha < 1/255 is skipped a few lines further down)
+    f2 G[Q];
+    float ta[2 * Q], ma[2 * Q], al[2 * Q];
+    float t = 1.f, frac = 1.f;
+    if (LOD) { t = q2.z; frac = q2.w; }
+    any = false;
+#pragma unroll
+    for (int h = 0; h < Q; h++) {
+        const f2 pl = mul2(power[h], bc(1.4426950408889634f));
+        G[h] = pk(ex2_ftz(lo(pl)), ex2_ftz(hi(pl)));
+        const f2 ta2 = mul2(bc(q1.y), G[h]);
+        ta[2 * h] = lo(ta2);
+        ta[2 * h + 1] = hi(ta2);
+#pragma unroll
+        for (int e = 2 * h; e < 2 * h + 2; e++) {
+            ma[e] = fminf(0.99f, ta[e]);
+            al[e] = ma[e];
+            if (LOD) al[e] = fmaf(ma[e], t, (1.0f - t) * (1.0f - __powf(1.0f - ma[e], frac)));
+            ok[e] = ok[e] && !(al[e] < 1.0f / 255.0f);
+            any = any || ok[e];
+        }
     }
-    ok0 = ok0 && !(a0 < 1.0f / 255.0f);
-    ok1 = ok1 && !(a1 < 1.0f / 255.0f);
-    if (!__any_sync(0xffffffffu, ok0 || ok1)) return false;
-    const f2 alpha = pk(ok0 ? a0 : 0.f, ok1 ? a1 : 0.f);
-    const f2 oma = fma2(alpha, bc(-1.0f), bc(1.0f));
-    const f2 rcp1ma = pk(rcp_approx(lo(oma)), rcp_approx(hi(oma)));  // 1-alpha in [0.01,1]; rcp.approx(1) == 1 exactly
-    p.T = mul2(p.T, rcp1ma);
-    const f2 weight = mul2(alpha, p.T);
-    const f2 oml = fma2(p.last_alpha, bc(-1.0f), bc(1.0f));
-    p.ar0 = fma2(p.last_alpha, bc(p.lc0), mul2(oml, p.ar0));
-    p.ar1 = fma2(p.last_alpha, bc(p.lc1), mul2(oml, p.ar1));
-    p.ar2 = fma2(p.last_alpha, bc(p.lc2), mul2(oml, p.ar2));
+    if (!__any_sync(0xffffffffu, any)) return false;
+    f2 A[NV];
+#pragma unroll
+    for (int h = 0; h < Q; h++) {
+        const bool ok0 = ok[2 * h], ok1 = ok[2 * h + 1];
+        const f2 alpha = pk(ok0 ? al[2 * h] : 0.f, ok1 ? al[2 * h + 1] : 0.f);
+        const f2 oma = fma2(alpha, bc(-1.0f), bc(1.0f));
+        const f2 rcp1ma = pk(rcp_approx(lo(oma)), rcp_approx(hi(oma)));  // 1-alpha in [0.01,1]; rcp.approx(1) == 1 exactly
+        p.T[h] = mul2(p.T[h], rcp1ma);
+        const f2 weight = mul2(alpha, p.T[h]);
+        const f2 oml = fma2(p.last_alpha[h], bc(-1.0f), bc(1.0f));
+        p.ar0[h] = fma2(p.last_alpha[h], bc(p.lc0), mul2(oml, p.ar0[h]));
+        p.ar1[h] = fma2(p.last_alpha[h], bc(p.lc1), mul2(oml, p.ar1[h]));
+        p.ar2[h] = fma2(p.last_alpha[h], bc(p.lc2), mul2(oml, p.ar2[h]));
+        f2 dL_dalpha = mul2(fma2(p.ar0[h], bc(-1.0f), bc(q1.z)), p.g0[h]);
+        dL_dalpha = fma2(fma2(p.ar1[h], bc(-1.0f), bc(q1.w)), p.g1[h], dL_dalpha);
+        dL_dalpha = fma2(fma2(p.ar2[h], bc(-1.0f), bc(q2.x)), p.g2[h], dL_dalpha);
+        A[6] = h ? fma2(weight, p.g0[h], A[6]) : mul2(weight, p.g0[h]);
+        A[7] = h ? fma2(weight, p.g1[h], A[7]) : mul2(weight, p.g1[h]);
+        A[8] = h ? fma2(weight, p.g2[h], A[8]) : mul2(weight, p.g2[h]);
+        if (DEPTH) {
+            p.ar_invd[h] = fma2(p.last_alpha[h], bc(p.last_invd), mul2(oml, p.ar_invd[h]));
+            dL_dalpha = fma2(fma2(p.ar_invd[h], bc(-1.0f), bc(q2.y)), p.gd[h], dL_dalpha);
+            A[9] = h ? fma2(weight, p.gd[h], A[9]) : mul2(weight, p.gd[h]);
+        }
+        p.last_alpha[h] = alpha;
+        dL_dalpha = fma2(p.Tfn[h], rcp1ma, mul2(dL_dalpha, p.T[h]));
+        f2 k = mul2(G[h], dL_dalpha);
+        const float k0 = (ok0 && !(ta[2 * h] > null_thr)) ? lo(k) : 0.f;  // 0.99 clamp (backward.cu:620,687); +inf threshold with AR's convention
+        const float k1 = (ok1 && !(ta[2 * h + 1] > null_thr)) ? hi(k) : 0.f;
+        k = pk(k0, k1);
+        // Per pair only the moments of k = G * dL_dalpha over (dx, dy) are accumulated; the splat-constant factors (conic,
+        // opacity, 0.5*W, 0.5*H, -0.5) of backward.cu:676-702 are applied once per (tile, splat) when the sums are flushed.
+        const f2 kdx = mul2(k, bc(dx)), kdy = mul2(k, dy[h]);
+        A[0] = h ? add2(A[0], kdx) : kdx;
+        A[1] = h ? add2(A[1], kdy) : kdy;
+        A[2] = h ? fma2(kdx, bc(dx), A[2]) : mul2(kdx, bc(dx));
+        A[3] = h ? fma2(kdx, dy[h], A[3]) : mul2(kdx, dy[h]);
+        A[4] = h ? fma2(kdy, dy[h], A[4]) : mul2(kdy, dy[h]);
+        if (LOD) {
+            const float w0 = t - __powf(1.0f - ma[2 * h], frac - 1.0f) * (t - 1.0f) * frac;
+            const float w1 = t - __powf(1.0f - ma[2 * h + 1], frac - 1.0f) * (t - 1.0f) * frac;
+            A[5] = h ? fma2(pk(w0, w1), k, A[5]) : mul2(pk(w0, w1), k);
+        } else {
+            A[5] = h ? add2(A[5], k) : k;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < (DEPTH ? NV : NV - 1); i++) v[i] = hsum(A[i]);  // the pairs are added lane-wise first: one horizontal add per value
+    if (!DEPTH) v[9] = 0.f;
     p.lc0 = q1.z; p.lc1 = q1.w; p.lc2 = q2.x;
-    f2 dL_dalpha = mul2(fma2(p.ar0, bc(-1.0f), bc(q1.z)), p.g0);
-    dL_dalpha = fma2(fma2(p.ar1, bc(-1.0f), bc(q1.w)), p.g1, dL_dalpha);
-    dL_dalpha = fma2(fma2(p.ar2, bc(-1.0f), bc(q2.x)), p.g2, dL_dalpha);
-    v[6] = hsum(mul2(weight, p.g0));
-    v[7] = hsum(mul2(weight, p.g1));
-    v[8] = hsum(mul2(weight, p.g2));
-    if (DEPTH) {
-        p.ar_invd = fma2(p.last_alpha, bc(p.last_invd), mul2(oml, p.ar_invd));
-        p.last_invd = q2.y;
-        dL_dalpha = fma2(fma2(p.ar_invd, bc(-1.0f), bc(q2.y)), p.gd, dL_dalpha);
-        v[9] = hsum(mul2(weight, p.gd));
-    }
-    p.last_alpha = alpha;
-    dL_dalpha = fma2(mul2(p.T_final, rcp1ma), p.nbg_dot, mul2(dL_dalpha, p.T));
-    f2 k = mul2(G, dL_dalpha);
-    const float k0 = (ok0 && !(ta0 > null_thr)) ? lo(k) : 0.f;  // 0.99 clamp (backward.cu:620,687); +inf threshold with AR's convention
-    const float k1 = (ok1 && !(ta1 > null_thr)) ? hi(k) : 0.f;
-    k = pk(k0, k1);
-    // Per pair only the moments of k = G * dL_dalpha over (dx, dy) are accumulated; the splat-constant factors (conic,
-    // opacity, 0.5*W, 0.5*H, -0.5) of backward.cu:676-702 are applied once per (tile, splat) when the sums are flushed.
-    const f2 kdx = mul2(k, bc(dx)), kdy = mul2(k, dy);
-    v[0] = hsum(kdx);
-    v[1] = hsum(kdy);
-    v[2] = hsum(mul2(kdx, bc(dx)));
-    v[3] = hsum(mul2(kdx, dy));
-    v[4] = hsum(mul2(kdy, dy));
-    if (LOD) {
-        const float m0 = t - __powf(1.0f - ma0, frac - 1.0f) * (t - 1.0f) * frac;
-        const float m1 = t - __powf(1.0f - ma1, frac - 1.0f) * (t - 1.0f) * frac;
-        v[5] = fmaf(m0, k0, m1 * k1);
-    } else {
-        v[5] = k0 + k1;
-    }
+    if (DEPTH) p.last_invd = q2.y;
     return true;
 }
 
-template <bool LOD, bool DEPTH>
-__global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const SplatRec* __restrict__ recs,
+template <bool LOD, bool DEPTH, int Q>
+__global__ void __launch_bounds__(BwdCfg<Q>::THREADS) blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const SplatRec* __restrict__ recs,
                                                                const uint32_t* __restrict__ point_list, int W, int H,
                                                                const float* __restrict__ bg_color, const float bg_mult,
                                                                const float null_thr, const int32_t* __restrict__ indices,
@@ -194,6 +225,8 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
                                                                float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic2D,
                                                                float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolors,
                                                                float* __restrict__ dL_dinvdepths) {
+    constexpr int BWD_THREADS = BwdCfg<Q>::THREADS, BWD_BATCH = BwdCfg<Q>::BATCH;
+    using BwdSmem = BwdSmemT<Q>;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, tx = tid & 15u, ty = tid >> 4;
@@ -201,44 +234,45 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
     const unsigned cta = blockIdx.y * horizontal_blocks + blockIdx.x;
     const unsigned tile = tile_order ? __ldg(tile_order + cta) : cta;   // longest lists first (binning.cu)
     const unsigned tile_x = tile % horizontal_blocks, tile_y = tile / horizontal_blocks;
-    const unsigned pix_x = tile_x * TILE_X + tx, pix_y0 = tile_y * TILE_Y + 2u * ty;
+    const unsigned pix_x = tile_x * TILE_X + tx, pix_y0 = tile_y * TILE_Y + 2u * Q * ty;
     const uint2 range = ranges[tile];
     const size_t HW = (size_t)H * W;
     const float bg0 = bg_color[0], bg1 = bg_color[1], bg2 = bg_color[2];
 
-    BwdPix2 p2;
+    BwdPix<Q> p2;
+    unsigned tmax = 0;
     {
-        float Tf[2], g0[2], g1[2], g2[2], gd[2];
-        unsigned last[2];
-#pragma unroll
-        for (int h = 0; h < 2; h++) {
-            const unsigned y = pix_y0 + h;
-            const bool inside = pix_x < (unsigned)W && y < (unsigned)H;
-            const uint32_t pix_id = W * y + pix_x;
-            Tf[h] = inside ? final_Ts[pix_id] : 0.f;
-            last[h] = inside ? n_contrib[pix_id] : 0u;
-            g0[h] = inside ? dL_dpixels[0 * HW + pix_id] : 0.f;
-            g1[h] = inside ? dL_dpixels[1 * HW + pix_id] : 0.f;
-            g2[h] = inside ? dL_dpixels[2 * HW + pix_id] : 0.f;
-            gd[h] = (DEPTH && inside) ? dL_invdepths[pix_id] : 0.f;
-        }
         p2.px = (float)pix_x;
         p2.npy = pk(-(float)pix_y0, -(float)(pix_y0 + 1u));
-        p2.T_final = pk(Tf[0], Tf[1]);
-        p2.T = p2.T_final;
-        p2.last0 = last[0];
-        p2.last1 = last[1];
-        p2.last_alpha = p2.ar0 = p2.ar1 = p2.ar2 = p2.ar_invd = bc(0.f);
         p2.lc0 = p2.lc1 = p2.lc2 = p2.last_invd = 0.f;
-        p2.g0 = pk(g0[0], g0[1]);
-        p2.g1 = pk(g1[0], g1[1]);
-        p2.g2 = pk(g2[0], g2[1]);
-        p2.gd = pk(gd[0], gd[1]);
-        p2.nbg_dot = pk(-bg_mult * (bg0 * g0[0] + bg1 * g1[0] + bg2 * g2[0]), -bg_mult * (bg0 * g0[1] + bg1 * g1[1] + bg2 * g2[1]));
+#pragma unroll
+        for (int q = 0; q < Q; q++) {
+            float Tf[2], g0[2], g1[2], g2[2], gd[2];
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const unsigned y = pix_y0 + 2u * q + h;
+                const bool inside = pix_x < (unsigned)W && y < (unsigned)H;
+                const uint32_t pix_id = W * y + pix_x;
+                Tf[h] = inside ? final_Ts[pix_id] : 0.f;
+                p2.last[2 * q + h] = inside ? n_contrib[pix_id] : 0u;
+                tmax = max(tmax, p2.last[2 * q + h]);
+                g0[h] = inside ? dL_dpixels[0 * HW + pix_id] : 0.f;
+                g1[h] = inside ? dL_dpixels[1 * HW + pix_id] : 0.f;
+                g2[h] = inside ? dL_dpixels[2 * HW + pix_id] : 0.f;
+                gd[h] = (DEPTH && inside) ? dL_invdepths[pix_id] : 0.f;
+            }
+            p2.T[q] = pk(Tf[0], Tf[1]);
+            p2.last_alpha[q] = p2.ar0[q] = p2.ar1[q] = p2.ar2[q] = p2.ar_invd[q] = bc(0.f);
+            p2.g0[q] = pk(g0[0], g0[1]);
+            p2.g1[q] = pk(g1[0], g1[1]);
+            p2.g2[q] = pk(g2[0], g2[1]);
+            p2.gd[q] = pk(gd[0], gd[1]);
+            p2.Tfn[q] = pk(Tf[0] * (-bg_mult * (bg0 * g0[0] + bg1 * g1[0] + bg2 * g2[0])), Tf[1] * (-bg_mult * (bg0 * g0[1] + bg1 * g1[1] + bg2 * g2[1])));
+        }
     }
 
     // the replay only has to cover splats up to the tile's deepest contributor
-    const unsigned wmax = __reduce_max_sync(0xffffffffu, max(p2.last0, p2.last1));
+    const unsigned wmax = __reduce_max_sync(0xffffffffu, tmax);
     if (lane == 0) sm.warp_max[warp] = wmax;
     if (tid == 0) {
         mbar_init(&sm.bar[0], BWD_THREADS);
@@ -346,7 +380,7 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
         _Pragma("unroll 2") for (int j = jtop; j >= 0; j--, rp -= 3, accp -= NV, pos--) {
             float v[NV];
             const float4 q0 = rp[0], q1 = rp[1], q2 = rp[2];
-            if (!bwd_pair2<LOD, DEPTH>(p2, pos, q0, q1, q2, null_thr, v)) continue;  // the same answer in every lane
+            if (!bwd_splat<LOD, DEPTH, Q>(p2, pos, q0, q1, q2, null_thr, v)) continue;  // the same answer in every lane
             int slot;
             const float total = warp_reduce10(v, lane, slot);
             if (slot >= 0 && (DEPTH || slot < 9) && total != 0.f) atomicAdd(accp + slot, total);
@@ -356,31 +390,43 @@ __global__ void __launch_bounds__(BWD_THREADS) blend_bwd_kernel(const uint2* __r
     flush();
 }
 
-int launch_blend_bwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, const SplatRec* recs, int W, int H,
-                     const float* bg, float bg_mult, float null_thr, const int32_t* indices, const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic,
-                     float* dL_dopacity, float* dL_dcolor, float* dL_dinvdepth, cudaStream_t s) {
-    dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1), block(BWD_THREADS, 1, 1);
+template <bool LOD, bool DEPTH, int Q, typename... Args>
+static int launch_bwd_variant(dim3 grid, cudaStream_t s, Args... args) {
     static std::atomic<bool> attr_set[MAX_DEVICES];
     const int dslot = device_slot();
     if (!attr_set[dslot].load(std::memory_order_acquire)) {
-        LODGS_CUDA(cudaFuncSetAttribute(blend_bwd_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmem)));
-        LODGS_CUDA(cudaFuncSetAttribute(blend_bwd_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmem)));
-        LODGS_CUDA(cudaFuncSetAttribute(blend_bwd_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmem)));
-        LODGS_CUDA(cudaFuncSetAttribute(blend_bwd_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmem)));
+        LODGS_CUDA(cudaFuncSetAttribute(blend_bwd_kernel<LOD, DEPTH, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemT<Q>)));
         attr_set[dslot].store(true, std::memory_order_release);
     }
-    const size_t smem = sizeof(BwdSmem);
+    blend_bwd_kernel<LOD, DEPTH, Q><<<grid, dim3(BwdCfg<Q>::THREADS, 1, 1), sizeof(BwdSmemT<Q>), s>>>(args...);
+    return LODGS_OK;
+}
+
+int launch_blend_bwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, const SplatRec* recs, int W, int H,
+                     const float* bg, float bg_mult, float null_thr, const int32_t* indices, const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic,
+                     float* dL_dopacity, float* dL_dcolor, float* dL_dinvdepth, cudaStream_t s) {
+    dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1);
     static const bool tile_id_order = getenv("LODGS_BLEND_TILE_ID_ORDER") != nullptr;  // A/B: CTAs in tile-id order
+    static const int px = getenv("LODGS_BWD_PX") ? atoi(getenv("LODGS_BWD_PX")) : 4;   // A/B: pixels per thread (2 or 4)
     static const int lod_cut_rc = set_lod_cut();
     if (lod_cut_rc) { set_error("blend: setting the LOD cut-off switch failed"); return LODGS_E_CUDA; }
     const uint32_t* order = tile_id_order ? nullptr : img.tile_order;
-#define LODGS_BWD_ARGS img.ranges, order, recs, bin.point_list, W, H, bg, bg_mult, null_thr, indices, img.final_T, img.n_contrib, dL_dpix, dL_dinvdepth_pix, \
-                       dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dinvdepth
-    if (lod && depth) blend_bwd_kernel<true, true><<<grid, block, smem, s>>>(LODGS_BWD_ARGS);
-    else if (lod) blend_bwd_kernel<true, false><<<grid, block, smem, s>>>(LODGS_BWD_ARGS);
-    else if (depth) blend_bwd_kernel<false, true><<<grid, block, smem, s>>>(LODGS_BWD_ARGS);
-    else blend_bwd_kernel<false, false><<<grid, block, smem, s>>>(LODGS_BWD_ARGS);
+#define LODGS_BWD_ARGS grid, s, (const uint2*)img.ranges, order, recs, (const uint32_t*)bin.point_list, W, H, bg, bg_mult, null_thr, indices, (const float*)img.final_T, \
+                       (const uint32_t*)img.n_contrib, dL_dpix, dL_dinvdepth_pix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dinvdepth
+    int rc;
+    if (px == 2) {
+        if (lod && depth) rc = launch_bwd_variant<true, true, 1>(LODGS_BWD_ARGS);
+        else if (lod) rc = launch_bwd_variant<true, false, 1>(LODGS_BWD_ARGS);
+        else if (depth) rc = launch_bwd_variant<false, true, 1>(LODGS_BWD_ARGS);
+        else rc = launch_bwd_variant<false, false, 1>(LODGS_BWD_ARGS);
+    } else {
+        if (lod && depth) rc = launch_bwd_variant<true, true, 2>(LODGS_BWD_ARGS);
+        else if (lod) rc = launch_bwd_variant<true, false, 2>(LODGS_BWD_ARGS);
+        else if (depth) rc = launch_bwd_variant<false, true, 2>(LODGS_BWD_ARGS);
+        else rc = launch_bwd_variant<false, false, 2>(LODGS_BWD_ARGS);
+    }
 #undef LODGS_BWD_ARGS
+    if (rc) return rc;
     LODGS_LAUNCHED("blend_bwd_kernel");
     return LODGS_OK;
 }
