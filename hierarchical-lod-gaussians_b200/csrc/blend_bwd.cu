@@ -35,6 +35,7 @@ template <int Q>
 struct BwdCfg {
     static constexpr int THREADS = 128 / Q;
     static constexpr int BATCH = THREADS;
+    static constexpr int MIN_CTAS = Q == 1 ? 7 : Q == 2 ? 10 : 12;  // register budget asked of ptxas: 72 / 96 / 168 per thread
 };
 
 template <int Q>
@@ -102,9 +103,13 @@ __device__ __forceinline__ float warp_reduce10(const float (&v)[NV], unsigned la
 // Replay state of the thread's Q pixel pairs (pair h: lo = row 2h of the thread's column, hi = the one below it).
 template <int Q>
 struct BwdPix {
-    f2 T[Q], Tfn[Q], last_alpha[Q], ar0[Q], ar1[Q], ar2[Q], ar_invd[Q], g0[Q], g1[Q], g2[Q], gd[Q];  // Tfn = T_final * (-bg_mult * bg . dL_dpixel)
+    // Tfn = T_final * (-bg_mult * bg . dL_dpixel).  S = dL_dpixel . (colour accumulated behind the current splat, inverse depth included
+    // with DEPTH), lcg = dL_dpixel . (colour of the previously processed splat): backward.cu:640-668 keeps the accumulated colour per
+    // channel and forms sum_c (c_c - accum_c) * dL_dpixel_c; the recurrence accum' = la * last_c + (1 - la) * accum is linear, so its dot
+    // product with the (per-pixel constant) dL_dpixel obeys the same recurrence and one value per pixel replaces four.
+    f2 T[Q], Tfn[Q], last_alpha[Q], S[Q], lcg[Q], g0[Q], g1[Q], g2[Q], gd[Q];
     f2 npy;  // -(y) of pair 0; pair h lies 2h rows further down
-    float px, lc0, lc1, lc2, last_invd;  // the colour / inverse depth of the previously processed splat is the same for all pixels of the warp
+    float px;
     unsigned last[2 * Q];
 };
 
@@ -117,27 +122,29 @@ struct BwdPix {
 template <bool LOD, bool DEPTH, int Q>
 __device__ __forceinline__ bool bwd_splat(BwdPix<Q>& p, const unsigned pos, const float4 q0, const float4 q1, const float4 q2,
                                           const float null_thr, float (&v)[NV]) {
+    // log2(e) * power = dy * (dy * A + B) + C with A = -0.5*l2e*con.yy, B = -l2e*con.xy*dx, C = -0.5*l2e*con.xx*dx*dx: two packed FMAs per
+    // pixel pair; the exponential is ex2 of it, the cut-offs are compared in the same units
+    constexpr float L2E = 1.4426950408889634f;
     const float dx = q0.x - p.px;
-    const float dxx = dx * (dx * q0.z), ndxy = -(dx * q0.w);
+    const float cA = (-0.5f * L2E) * q1.x, cB = (-L2E * q0.w) * dx, cC = ((-0.5f * L2E) * q0.z * dx) * dx;
     float cut;
-    if (!LOD) cut = q2.z;  // certainly below the 1/255 cut (cut-off stored by the preprocess kernel)
+    if (!LOD) cut = q2.z * L2E;  // certainly below the 1/255 cut (cut-off stored by the preprocess kernel)
     else      // the same cut rebuilt per splat (LOD alpha <= opacity*exp(power) for t in [0,1], kids >= 1; see blend_fwd.cu)
-        cut = (c_lod_cut && q2.z >= 0.0f && q2.z <= 1.0f && q2.w > 0.0f && q2.w <= 1.0f) ? -__logf(255.0f * q1.y) - 0.02f : -__builtin_huge_valf();
+        cut = (c_lod_cut && q2.z >= 0.0f && q2.z <= 1.0f && q2.w > 0.0f && q2.w <= 1.0f) ? -__log2f(255.0f * q1.y) - 0.03f : -__builtin_huge_valf();
     f2 dy[Q], power[Q];
     bool ok[2 * Q];
     bool any = false;
 #pragma unroll
     for (int h = 0; h < Q; h++) {
         dy[h] = add2(bc(q0.y - 2.0f * h), p.npy);
-        const f2 quad = fma2(dy[h], mul2(dy[h], bc(q1.x)), bc(dxx));
-        power[h] = fma2(dy[h], bc(ndxy), mul2(quad, bc(-0.5f)));
+        power[h] = fma2(dy[h], fma2(dy[h], bc(cA), bc(cB)), bc(cC));
         const float pw0 = lo(power[h]), pw1 = hi(power[h]);
         ok[2 * h] = pos < p.last[2 * h] && !(pw0 > 0.0f) && !(pw0 < cut);
         ok[2 * h + 1] = pos < p.last[2 * h + 1] && !(pw1 > 0.0f) && !(pw1 < cut);
         any = any || ok[2 * h] || ok[2 * h + 1];
     }
     if (!__any_sync(0xffffffffu, any)) return false;  // warp-uniform: lanes without a contribution ride along with alpha 0
-    // ex2.approx.ftz on power * log2(e) instead of the forward's full-range expf: alpha moves by ~1e-7 relative, far inside the
+    // ex2.approx.ftz on log2(e) * power instead of the forward's full-range expf: alpha moves by ~1e-7 relative, far inside the
     // gradient budget; flushing results below 2^-126 is immaterial (alpha < 1/255 is skipped a few lines further down)
     f2 G[Q];
     float ta[2 * Q], ma[2 * Q], al[2 * Q];
@@ -146,8 +153,7 @@ __device__ __forceinline__ bool bwd_splat(BwdPix<Q>& p, const unsigned pos, cons
     any = false;
 #pragma unroll
     for (int h = 0; h < Q; h++) {
-        const f2 pl = mul2(power[h], bc(1.4426950408889634f));
-        G[h] = pk(ex2_ftz(lo(pl)), ex2_ftz(hi(pl)));
+        G[h] = pk(ex2_ftz(lo(power[h])), ex2_ftz(hi(power[h])));
         const f2 ta2 = mul2(bc(q1.y), G[h]);
         ta[2 * h] = lo(ta2);
         ta[2 * h + 1] = hi(ta2);
@@ -161,7 +167,7 @@ __device__ __forceinline__ bool bwd_splat(BwdPix<Q>& p, const unsigned pos, cons
         }
     }
     if (!__any_sync(0xffffffffu, any)) return false;
-    f2 A[NV];
+    f2 A[NV], M[3];
 #pragma unroll
     for (int h = 0; h < Q; h++) {
         const bool ok0 = ok[2 * h], ok1 = ok[2 * h + 1];
@@ -170,21 +176,19 @@ __device__ __forceinline__ bool bwd_splat(BwdPix<Q>& p, const unsigned pos, cons
         const f2 rcp1ma = pk(rcp_approx(lo(oma)), rcp_approx(hi(oma)));  // 1-alpha in [0.01,1]; rcp.approx(1) == 1 exactly
         p.T[h] = mul2(p.T[h], rcp1ma);
         const f2 weight = mul2(alpha, p.T[h]);
-        const f2 oml = fma2(p.last_alpha[h], bc(-1.0f), bc(1.0f));
-        p.ar0[h] = fma2(p.last_alpha[h], bc(p.lc0), mul2(oml, p.ar0[h]));
-        p.ar1[h] = fma2(p.last_alpha[h], bc(p.lc1), mul2(oml, p.ar1[h]));
-        p.ar2[h] = fma2(p.last_alpha[h], bc(p.lc2), mul2(oml, p.ar2[h]));
-        f2 dL_dalpha = mul2(fma2(p.ar0[h], bc(-1.0f), bc(q1.z)), p.g0[h]);
-        dL_dalpha = fma2(fma2(p.ar1[h], bc(-1.0f), bc(q1.w)), p.g1[h], dL_dalpha);
-        dL_dalpha = fma2(fma2(p.ar2[h], bc(-1.0f), bc(q2.x)), p.g2[h], dL_dalpha);
+        f2 cg = mul2(p.g0[h], bc(q1.z));
+        cg = fma2(p.g1[h], bc(q1.w), cg);
+        cg = fma2(p.g2[h], bc(q2.x), cg);
         A[6] = h ? fma2(weight, p.g0[h], A[6]) : mul2(weight, p.g0[h]);
         A[7] = h ? fma2(weight, p.g1[h], A[7]) : mul2(weight, p.g1[h]);
         A[8] = h ? fma2(weight, p.g2[h], A[8]) : mul2(weight, p.g2[h]);
         if (DEPTH) {
-            p.ar_invd[h] = fma2(p.last_alpha[h], bc(p.last_invd), mul2(oml, p.ar_invd[h]));
-            dL_dalpha = fma2(fma2(p.ar_invd[h], bc(-1.0f), bc(q2.y)), p.gd[h], dL_dalpha);
+            cg = fma2(p.gd[h], bc(q2.y), cg);
             A[9] = h ? fma2(weight, p.gd[h], A[9]) : mul2(weight, p.gd[h]);
         }
+        p.S[h] = fma2(p.last_alpha[h], fma2(p.S[h], bc(-1.0f), p.lcg[h]), p.S[h]);
+        p.lcg[h] = cg;
+        f2 dL_dalpha = fma2(p.S[h], bc(-1.0f), cg);
         p.last_alpha[h] = alpha;
         dL_dalpha = fma2(p.Tfn[h], rcp1ma, mul2(dL_dalpha, p.T[h]));
         f2 k = mul2(G[h], dL_dalpha);
@@ -193,30 +197,34 @@ __device__ __forceinline__ bool bwd_splat(BwdPix<Q>& p, const unsigned pos, cons
         k = pk(k0, k1);
         // Per pair only the moments of k = G * dL_dalpha over (dx, dy) are accumulated; the splat-constant factors (conic,
         // opacity, 0.5*W, 0.5*H, -0.5) of backward.cu:676-702 are applied once per (tile, splat) when the sums are flushed.
-        const f2 kdx = mul2(k, bc(dx)), kdy = mul2(k, dy[h]);
-        A[0] = h ? add2(A[0], kdx) : kdx;
-        A[1] = h ? add2(A[1], kdy) : kdy;
-        A[2] = h ? fma2(kdx, bc(dx), A[2]) : mul2(kdx, bc(dx));
-        A[3] = h ? fma2(kdx, dy[h], A[3]) : mul2(kdx, dy[h]);
-        A[4] = h ? fma2(kdy, dy[h], A[4]) : mul2(kdy, dy[h]);
+        // dx is the same for all pixels of the thread (one column): only sum k, sum k*dy and sum k*dy*dy are accumulated per pixel
+        const f2 kdy = mul2(k, dy[h]);
+        M[0] = h ? add2(M[0], k) : k;
+        M[1] = h ? add2(M[1], kdy) : kdy;
+        M[2] = h ? fma2(kdy, dy[h], M[2]) : mul2(kdy, dy[h]);
         if (LOD) {
             const float w0 = t - __powf(1.0f - ma[2 * h], frac - 1.0f) * (t - 1.0f) * frac;
             const float w1 = t - __powf(1.0f - ma[2 * h + 1], frac - 1.0f) * (t - 1.0f) * frac;
             A[5] = h ? fma2(pk(w0, w1), k, A[5]) : mul2(pk(w0, w1), k);
-        } else {
-            A[5] = h ? add2(A[5], k) : k;
         }
     }
-#pragma unroll
-    for (int i = 0; i < (DEPTH ? NV : NV - 1); i++) v[i] = hsum(A[i]);  // the pairs are added lane-wise first: one horizontal add per value
-    if (!DEPTH) v[9] = 0.f;
-    p.lc0 = q1.z; p.lc1 = q1.w; p.lc2 = q2.x;
-    if (DEPTH) p.last_invd = q2.y;
+    // the pairs were added lane-wise first: one horizontal add per value
+    const float s0 = hsum(M[0]), s1 = hsum(M[1]);
+    v[0] = dx * s0;
+    v[1] = s1;
+    v[2] = dx * v[0];
+    v[3] = dx * s1;
+    v[4] = hsum(M[2]);
+    v[5] = LOD ? hsum(A[5]) : s0;
+    v[6] = hsum(A[6]);
+    v[7] = hsum(A[7]);
+    v[8] = hsum(A[8]);
+    v[9] = DEPTH ? hsum(A[9]) : 0.f;
     return true;
 }
 
 template <bool LOD, bool DEPTH, int Q>
-__global__ void __launch_bounds__(BwdCfg<Q>::THREADS) blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const SplatRec* __restrict__ recs,
+__global__ void __launch_bounds__(BwdCfg<Q>::THREADS, BwdCfg<Q>::MIN_CTAS) blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const SplatRec* __restrict__ recs,
                                                                const uint32_t* __restrict__ point_list, int W, int H,
                                                                const float* __restrict__ bg_color, const float bg_mult,
                                                                const float null_thr, const int32_t* __restrict__ indices,
@@ -244,7 +252,6 @@ __global__ void __launch_bounds__(BwdCfg<Q>::THREADS) blend_bwd_kernel(const uin
     {
         p2.px = (float)pix_x;
         p2.npy = pk(-(float)pix_y0, -(float)(pix_y0 + 1u));
-        p2.lc0 = p2.lc1 = p2.lc2 = p2.last_invd = 0.f;
 #pragma unroll
         for (int q = 0; q < Q; q++) {
             float Tf[2], g0[2], g1[2], g2[2], gd[2];
@@ -262,7 +269,7 @@ __global__ void __launch_bounds__(BwdCfg<Q>::THREADS) blend_bwd_kernel(const uin
                 gd[h] = (DEPTH && inside) ? dL_invdepths[pix_id] : 0.f;
             }
             p2.T[q] = pk(Tf[0], Tf[1]);
-            p2.last_alpha[q] = p2.ar0[q] = p2.ar1[q] = p2.ar2[q] = p2.ar_invd[q] = bc(0.f);
+            p2.last_alpha[q] = p2.S[q] = p2.lcg[q] = bc(0.f);
             p2.g0[q] = pk(g0[0], g0[1]);
             p2.g1[q] = pk(g1[0], g1[1]);
             p2.g2[q] = pk(g2[0], g2[1]);
@@ -419,6 +426,11 @@ int launch_blend_bwd(bool lod, bool depth, const ImageState& img, const BinningS
         else if (lod) rc = launch_bwd_variant<true, false, 1>(LODGS_BWD_ARGS);
         else if (depth) rc = launch_bwd_variant<false, true, 1>(LODGS_BWD_ARGS);
         else rc = launch_bwd_variant<false, false, 1>(LODGS_BWD_ARGS);
+    } else if (px == 8) {
+        if (lod && depth) rc = launch_bwd_variant<true, true, 4>(LODGS_BWD_ARGS);
+        else if (lod) rc = launch_bwd_variant<true, false, 4>(LODGS_BWD_ARGS);
+        else if (depth) rc = launch_bwd_variant<false, true, 4>(LODGS_BWD_ARGS);
+        else rc = launch_bwd_variant<false, false, 4>(LODGS_BWD_ARGS);
     } else {
         if (lod && depth) rc = launch_bwd_variant<true, true, 2>(LODGS_BWD_ARGS);
         else if (lod) rc = launch_bwd_variant<true, false, 2>(LODGS_BWD_ARGS);
