@@ -26,23 +26,32 @@ static int set_lod_cut() {
 }
 
 
-constexpr int BLEND_BATCH = 256;
-constexpr int BLEND_THREADS = 128;  // 16 x 8 threads, two vertically adjacent pixels each: a warp covers a 16x4 pixel block
+// Q = vertically adjacent pixel PAIRS per thread: a CTA is one 16x16 tile with 128 / Q threads (Q = 1: 16 x 8 threads with two pixels each, a warp
+// covers 16x4 pixels; Q = 2: 16 x 4 threads with a column of four pixels each, a warp covers 16x8). What is paid per (warp, splat) — three
+// record loads, the loop with its exit vote, the column-constant dx terms — is shared by twice the pixels with Q = 2. Every thread gathers
+// two records per batch, so the batch shrinks with the CTA.
+template <int Q>
+struct BlendCfg {
+    static constexpr int THREADS = 128 / Q;
+    static constexpr int BATCH = 2 * THREADS;
+};
 
-struct BlendSmem {
-    SplatRec recs[2][BLEND_BATCH];
-    uint8_t flag[2][BLEND_BATCH];
+template <int Q>
+struct BlendSmemT {
+    SplatRec recs[2][BlendCfg<Q>::BATCH];
+    uint8_t flag[2][BlendCfg<Q>::BATCH];
     uint64_t bar[2];
 };
 
-// Blend state of the thread's two pixels in packed FP32 pairs (lo = upper pixel, hi = the one below it).
-struct PixState2 {
-    f2 npy, T, C0, C1, C2, D;
+// Blend state of the thread's 2Q pixels in packed FP32 pairs (pair h: lo = row 2h of the thread's column, hi = the one below it).
+template <int Q>
+struct PixState {
+    f2 npy[Q], T[Q], C0[Q], C1[Q], C2[Q], D[Q];
     float px;
-    uint32_t last0, last1;
+    uint32_t last[2 * Q];
 };
 
-// One splat against the thread's two pixels, rounding pinned to the reference build's SASS for renderCUDA (forward.cu:529-585):
+// One splat against the thread's pixels, rounding pinned to the reference build's SASS for renderCUDA (forward.cu:529-585):
 //   power = (dx*(dx*con.x) + dy*(dy*con.z)) * -0.5 - dy*(dx*con.y),   C += T * (alpha * c),   T *= (1 - alpha)
 // evaluated on packed pairs: every half performs exactly the IEEE operations of the scalar code —
 //   dy = y + (-py);  quad = fma(dx, dx*con.x, dy*(dy*con.z));  power = fma(quad, -0.5, dy*(-(dx*con.y)))  [quad * -0.5 is exact,
@@ -50,62 +59,86 @@ struct PixState2 {
 //   C = fma(T, alpha*c, C) — and only sequences ptxas cannot re-contract are used (see common.cuh).
 // A pixel that does not take the splat (saturated, power > 0, below the cut-off, alpha < 1/255, or saturating on this splat)
 // rides along with alpha 0: fma(T, 0*c, C) == C and its T is kept by a select, so its results are untouched bit for bit.
-template <bool LOD, bool DEPTH, bool SEEN>
-__device__ __forceinline__ void blend_pair2(PixState2& p, unsigned& done0, unsigned& done1, const float4 q0, const float4 q1,
+template <bool LOD, bool DEPTH, bool SEEN, int Q>
+__device__ __forceinline__ void blend_splat(PixState<Q>& p, unsigned (&done)[2 * Q], const float4 q0, const float4 q1,
                                             const float4 q2, uint32_t contributor, uint8_t* flagp) {
     const float dx = __fsub_rn(q0.x, p.px), dxa = __fmul_rn(dx, q0.z), ndxb = -__fmul_rn(dx, q0.w);
-    const f2 dy = add2(bc(q0.y), p.npy);
-    const f2 quad = fma2(bc(dx), bc(dxa), mul2(dy, mul2(dy, bc(q1.x))));
-    const f2 power = fma2(quad, bc(-0.5f), mul2(dy, bc(ndxb)));
-    const float pw0 = lo(power), pw1 = hi(power);
-    bool ok0 = !done0 && !(pw0 > 0.0f), ok1 = !done1 && !(pw1 > 0.0f);
+    float cut;
     if (!LOD) {  // alpha is certainly below 1/255 (cut-off precomputed per splat, see preprocess_one)
-        ok0 = ok0 && !(pw0 < q2.z);
-        ok1 = ok1 && !(pw1 < q2.z);
+        cut = q2.z;
     } else {
         // Both spare record slots carry t and 1/kids here, so the cut-off is rebuilt per splat: the LOD alpha
         // t*a + (1-t)*(1 - (1-a)^(1/kids)) never exceeds a = opacity*exp(power) for t in [0,1] and kids >= 1, and
         // power < -log(255*opacity) - 0.02 puts a 2 % below 1/255 (the approximations of __logf/__powf move it by ~1e-6), so
         // exactly pairs the alpha test below would drop are dropped here — before two exponentials and two powers.
-        const float cut = (c_lod_cut && q2.z >= 0.0f && q2.z <= 1.0f && q2.w > 0.0f && q2.w <= 1.0f) ? -__logf(255.0f * q1.y) - 0.02f : -__builtin_huge_valf();
-        ok0 = ok0 && !(pw0 < cut);
-        ok1 = ok1 && !(pw1 < cut);
+        cut = (c_lod_cut && q2.z >= 0.0f && q2.z <= 1.0f && q2.w > 0.0f && q2.w <= 1.0f) ? -__logf(255.0f * q1.y) - 0.02f : -__builtin_huge_valf();
     }
-    if (!ok0 && !ok1) return;
-    const f2 al = mul2(bc(q1.y), pk(expf(pw0), expf(pw1)));
-    float a0 = fminf(0.99f, lo(al)), a1 = fminf(0.99f, hi(al));
-    if (LOD) {
-        const float k0 = __fsub_rn(1.0f, __powf(__fsub_rn(1.0f, a0), q2.w)), k1 = __fsub_rn(1.0f, __powf(__fsub_rn(1.0f, a1), q2.w));
-        const float omt = __fsub_rn(1.0f, q2.z);
-        a0 = __fmaf_rn(a0, q2.z, __fmul_rn(omt, k0));
-        a1 = __fmaf_rn(a1, q2.z, __fmul_rn(omt, k1));
+    float pw[2 * Q];
+    bool ok[2 * Q];
+    bool any = false;
+#pragma unroll
+    for (int h = 0; h < Q; h++) {
+        const f2 dy = add2(bc(q0.y), p.npy[h]);
+        const f2 quad = fma2(bc(dx), bc(dxa), mul2(dy, mul2(dy, bc(q1.x))));
+        const f2 power = fma2(quad, bc(-0.5f), mul2(dy, bc(ndxb)));
+        pw[2 * h] = lo(power);
+        pw[2 * h + 1] = hi(power);
+#pragma unroll
+        for (int e = 2 * h; e < 2 * h + 2; e++) {
+            ok[e] = !done[e] && !(pw[e] > 0.0f) && !(pw[e] < cut);
+            any = any || ok[e];
+        }
     }
-    ok0 = ok0 && !(a0 < 1.0f / 255.0f);
-    ok1 = ok1 && !(a1 < 1.0f / 255.0f);
-    if (!ok0 && !ok1) return;
-    const f2 test_T = mul2(p.T, fma2(pk(a0, a1), bc(-1.0f), bc(1.0f)));
-    const float t0 = lo(test_T), t1 = hi(test_T);
-    const bool sat0 = ok0 && t0 < 0.0001f, sat1 = ok1 && t1 < 0.0001f;
-    if (sat0) done0 = 1u;
-    if (sat1) done1 = 1u;
-    const bool bl0 = ok0 && !sat0, bl1 = ok1 && !sat1;
-    if (SEEN && (bl0 || bl1)) *flagp = 1;
-    const f2 ae = pk(bl0 ? a0 : 0.f, bl1 ? a1 : 0.f);
-    fma2_acc(p.C0, p.T, mul2(ae, bc(q1.z)));
-    fma2_acc(p.C1, p.T, mul2(ae, bc(q1.w)));
-    fma2_acc(p.C2, p.T, mul2(ae, bc(q2.x)));
-    if (DEPTH) fma2_acc(p.D, p.T, mul2(ae, bc(q2.y)));  // q2.y = rcp.rn(depth), precomputed per Gaussian
-    p.T = pk(bl0 ? t0 : lo(p.T), bl1 ? t1 : hi(p.T));
-    if (bl0) p.last0 = contributor;
-    if (bl1) p.last1 = contributor;
+    if (!any) return;
+    float a[2 * Q];
+    any = false;
+#pragma unroll
+    for (int h = 0; h < Q; h++) {
+        const f2 al = mul2(bc(q1.y), pk(expf(pw[2 * h]), expf(pw[2 * h + 1])));
+        a[2 * h] = fminf(0.99f, lo(al));
+        a[2 * h + 1] = fminf(0.99f, hi(al));
+#pragma unroll
+        for (int e = 2 * h; e < 2 * h + 2; e++) {
+            if (LOD) {
+                const float k = __fsub_rn(1.0f, __powf(__fsub_rn(1.0f, a[e]), q2.w));
+                const float omt = __fsub_rn(1.0f, q2.z);
+                a[e] = __fmaf_rn(a[e], q2.z, __fmul_rn(omt, k));
+            }
+            ok[e] = ok[e] && !(a[e] < 1.0f / 255.0f);
+            any = any || ok[e];
+        }
+    }
+    if (!any) return;
+    bool blended = false;
+#pragma unroll
+    for (int h = 0; h < Q; h++) {
+        const f2 test_T = mul2(p.T[h], fma2(pk(a[2 * h], a[2 * h + 1]), bc(-1.0f), bc(1.0f)));
+        const float t0 = lo(test_T), t1 = hi(test_T);
+        const bool sat0 = ok[2 * h] && t0 < 0.0001f, sat1 = ok[2 * h + 1] && t1 < 0.0001f;
+        if (sat0) done[2 * h] = 1u;
+        if (sat1) done[2 * h + 1] = 1u;
+        const bool bl0 = ok[2 * h] && !sat0, bl1 = ok[2 * h + 1] && !sat1;
+        blended = blended || bl0 || bl1;
+        const f2 ae = pk(bl0 ? a[2 * h] : 0.f, bl1 ? a[2 * h + 1] : 0.f);
+        fma2_acc(p.C0[h], p.T[h], mul2(ae, bc(q1.z)));
+        fma2_acc(p.C1[h], p.T[h], mul2(ae, bc(q1.w)));
+        fma2_acc(p.C2[h], p.T[h], mul2(ae, bc(q2.x)));
+        if (DEPTH) fma2_acc(p.D[h], p.T[h], mul2(ae, bc(q2.y)));  // q2.y = rcp.rn(depth), precomputed per Gaussian
+        p.T[h] = pk(bl0 ? t0 : lo(p.T[h]), bl1 ? t1 : hi(p.T[h]));
+        if (bl0) p.last[2 * h] = contributor;
+        if (bl1) p.last[2 * h + 1] = contributor;
+    }
+    if (SEEN && blended) *flagp = 1;
 }
 
-template <bool LOD, bool DEPTH, bool SEEN>
-__global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const SplatRec* __restrict__ recs,
+template <bool LOD, bool DEPTH, bool SEEN, int Q>
+__global__ void __launch_bounds__(BlendCfg<Q>::THREADS) blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const SplatRec* __restrict__ recs,
                                                                  const uint32_t* __restrict__ point_list, int W, int H,
                                                                  const float* __restrict__ bg_color, float* __restrict__ final_T,
                                                                  uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
                                                                  float* __restrict__ out_invdepth, int32_t* __restrict__ seen) {
+    constexpr int BLEND_THREADS = BlendCfg<Q>::THREADS, BLEND_BATCH = BlendCfg<Q>::BATCH;
+    using BlendSmem = BlendSmemT<Q>;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     BlendSmem& sm = *reinterpret_cast<BlendSmem*>(smem_raw);
     const unsigned tid = threadIdx.x, tx = tid & 15u, ty = tid >> 4;
@@ -113,16 +146,23 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* _
     const unsigned cta = blockIdx.y * horizontal_blocks + blockIdx.x;
     const unsigned tile = tile_order ? __ldg(tile_order + cta) : cta;   // longest lists first (binning.cu)
     const unsigned tile_x = tile % horizontal_blocks, tile_y = tile / horizontal_blocks;
-    const unsigned pix_x = tile_x * TILE_X + tx, pix_y0 = tile_y * TILE_Y + 2u * ty;
-    const bool inside0 = pix_x < (unsigned)W && pix_y0 < (unsigned)H;
-    const bool inside1 = pix_x < (unsigned)W && pix_y0 + 1u < (unsigned)H;
-    unsigned done0 = inside0 ? 0u : 1u, done1 = inside1 ? 0u : 1u;
-    PixState2 p;
+    const unsigned pix_x = tile_x * TILE_X + tx, pix_y0 = tile_y * TILE_Y + 2u * Q * ty;
+    unsigned done[2 * Q];
+    PixState<Q> p;
     p.px = (float)pix_x;
-    p.npy = pk(-(float)pix_y0, -(float)(pix_y0 + 1u));
-    p.T = bc(1.0f);
-    p.C0 = p.C1 = p.C2 = p.D = bc(0.f);
-    p.last0 = p.last1 = 0u;
+#pragma unroll
+    for (int h = 0; h < Q; h++) {
+        p.npy[h] = pk(-(float)(pix_y0 + 2u * h), -(float)(pix_y0 + 2u * h + 1u));
+        p.T[h] = bc(1.0f);
+        p.C0[h] = p.C1[h] = p.C2[h] = p.D[h] = bc(0.f);
+    }
+    unsigned all_done = 1u;
+#pragma unroll
+    for (int e = 0; e < 2 * Q; e++) {
+        done[e] = (pix_x < (unsigned)W && pix_y0 + e < (unsigned)H) ? 0u : 1u;
+        all_done &= done[e];
+        p.last[e] = 0u;
+    }
 
     const uint2 range = ranges[tile];
     const int total = (int)(range.y - range.x);
@@ -189,7 +229,10 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* _
     int toDo = total;
     for (int b = 0; b < rounds; b++, toDo -= BLEND_BATCH) {
         // barrier: everyone has left batch b-1, so its ring slot may be refilled; also the CTA-wide exit vote
-        const int num_done = __syncthreads_count((done0 & done1) != 0u);
+        all_done = 1u;
+#pragma unroll
+        for (int e = 0; e < 2 * Q; e++) all_done &= done[e];
+        const int num_done = __syncthreads_count(all_done != 0u);
         flush_seen();
         pending = -1;
         const int s = b & 1;
@@ -215,11 +258,14 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* _
         _Pragma("unroll 2") for (int j = 0; j < cnt; j++, rp += 3, fl++) {
             contributor++;
             // ballot-based early termination: the warp stops scanning once all of its 64 pixels are saturated
-            if (__all_sync(0xffffffffu, (done0 & done1) != 0u)) break;
+            all_done = 1u;
+#pragma unroll
+            for (int e = 0; e < 2 * Q; e++) all_done &= done[e];
+            if (__all_sync(0xffffffffu, all_done != 0u)) break;
             const float4 q0 = rp[0];  // x y conx cony
             const float4 q1 = rp[1];  // conz opac r g
             const float4 q2 = rp[2];  // b 1/depth t 1/kids
-            blend_pair2<LOD, DEPTH, SEEN>(p, done0, done1, q0, q1, q2, contributor, fl);
+            blend_splat<LOD, DEPTH, SEEN, Q>(p, done, q0, q1, q2, contributor, fl);
         }
     }
     if (SEEN) {
@@ -228,39 +274,44 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_fwd_kernel(const uint2* _
     }
     const size_t HW = (size_t)H * W;
     const float bg0 = bg_color[0], bg1 = bg_color[1], bg2 = bg_color[2];
-    if (inside0) {
-        const uint32_t pix_id = W * pix_y0 + pix_x;
-        final_T[pix_id] = lo(p.T);
-        n_contrib[pix_id] = p.last0;
-        out_color[0 * HW + pix_id] = __fmaf_rn(lo(p.T), bg0, lo(p.C0));
-        out_color[1 * HW + pix_id] = __fmaf_rn(lo(p.T), bg1, lo(p.C1));
-        out_color[2 * HW + pix_id] = __fmaf_rn(lo(p.T), bg2, lo(p.C2));
-        if (DEPTH) out_invdepth[pix_id] = lo(p.D);
+#pragma unroll
+    for (int e = 0; e < 2 * Q; e++) {
+        const unsigned y = pix_y0 + e;
+        if (pix_x < (unsigned)W && y < (unsigned)H) {
+            const int h = e >> 1;
+            const uint32_t pix_id = W * y + pix_x;
+            const float T = (e & 1) ? hi(p.T[h]) : lo(p.T[h]);
+            final_T[pix_id] = T;
+            n_contrib[pix_id] = p.last[e];
+            out_color[0 * HW + pix_id] = __fmaf_rn(T, bg0, (e & 1) ? hi(p.C0[h]) : lo(p.C0[h]));
+            out_color[1 * HW + pix_id] = __fmaf_rn(T, bg1, (e & 1) ? hi(p.C1[h]) : lo(p.C1[h]));
+            out_color[2 * HW + pix_id] = __fmaf_rn(T, bg2, (e & 1) ? hi(p.C2[h]) : lo(p.C2[h]));
+            if (DEPTH) out_invdepth[pix_id] = (e & 1) ? hi(p.D[h]) : lo(p.D[h]);
+        }
     }
-    if (inside1) {
-        const uint32_t pix_id = W * (pix_y0 + 1u) + pix_x;
-        final_T[pix_id] = hi(p.T);
-        n_contrib[pix_id] = p.last1;
-        out_color[0 * HW + pix_id] = __fmaf_rn(hi(p.T), bg0, hi(p.C0));
-        out_color[1 * HW + pix_id] = __fmaf_rn(hi(p.T), bg1, hi(p.C1));
-        out_color[2 * HW + pix_id] = __fmaf_rn(hi(p.T), bg2, hi(p.C2));
-        if (DEPTH) out_invdepth[pix_id] = hi(p.D);
+}
+
+template <bool LOD, bool DEPTH, bool SEEN, int Q>
+static int launch_blend_q(dim3 grid, cudaStream_t s, const uint2* ranges, const uint32_t* order, const SplatRec* recs, const uint32_t* point_list, int W, int H,
+                          const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_invdepth, int32_t* seen) {
+    static std::atomic<bool> attr_set[MAX_DEVICES];
+    const int dslot = device_slot();
+    if (!attr_set[dslot].load(std::memory_order_acquire)) {
+        LODGS_CUDA(cudaFuncSetAttribute(blend_fwd_kernel<LOD, DEPTH, SEEN, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BlendSmemT<Q>)));
+        attr_set[dslot].store(true, std::memory_order_release);
     }
+    blend_fwd_kernel<LOD, DEPTH, SEEN, Q><<<grid, BlendCfg<Q>::THREADS, sizeof(BlendSmemT<Q>), s>>>(ranges, order, recs, point_list, W, H, bg, final_T, n_contrib,
+                                                                                               out_color, out_invdepth, seen);
+    LODGS_LAUNCHED("blend_fwd_kernel");
+    return LODGS_OK;
 }
 
 template <bool LOD, bool DEPTH, bool SEEN>
 static int launch_blend_one(dim3 grid, cudaStream_t s, const uint2* ranges, const uint32_t* order, const SplatRec* recs, const uint32_t* point_list, int W, int H,
                             const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_invdepth, int32_t* seen) {
-    static std::atomic<bool> attr_set[MAX_DEVICES];
-    const int dslot = device_slot();
-    if (!attr_set[dslot].load(std::memory_order_acquire)) {
-        LODGS_CUDA(cudaFuncSetAttribute(blend_fwd_kernel<LOD, DEPTH, SEEN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BlendSmem)));
-        attr_set[dslot].store(true, std::memory_order_release);
-    }
-    blend_fwd_kernel<LOD, DEPTH, SEEN><<<grid, BLEND_THREADS, sizeof(BlendSmem), s>>>(ranges, order, recs, point_list, W, H, bg, final_T, n_contrib,
-                                                                                  out_color, out_invdepth, seen);
-    LODGS_LAUNCHED("blend_fwd_kernel");
-    return LODGS_OK;
+    static const int px = getenv("LODGS_FWD_PX") ? atoi(getenv("LODGS_FWD_PX")) : 4;   // A/B: pixels per thread (2 or 4)
+    if (px == 2) return launch_blend_q<LOD, DEPTH, SEEN, 1>(grid, s, ranges, order, recs, point_list, W, H, bg, final_T, n_contrib, out_color, out_invdepth, seen);
+    return launch_blend_q<LOD, DEPTH, SEEN, 2>(grid, s, ranges, order, recs, point_list, W, H, bg, final_T, n_contrib, out_color, out_invdepth, seen);
 }
 
 template <bool LOD, bool DEPTH>
