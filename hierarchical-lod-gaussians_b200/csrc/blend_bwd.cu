@@ -58,9 +58,17 @@ __device__ __forceinline__ float rcp_approx(float x) {
     return r;
 }
 
-// Sum v[0..9] over the warp. On return lanes with even lane id and a valid slot hold the total of value
-// `slot` (returned, -1 otherwise) in the return value `out`.
-__device__ __forceinline__ float warp_reduce10(const float (&v)[NV], unsigned lane, int& slot) {
+// Which of the ten sums lane `lane` holds after warp_reduce10 (-1: none). A function of the lane only: computed once per thread.
+__device__ __forceinline__ int reduce_slot(unsigned lane) {
+    const bool b16 = lane & 16, b8 = lane & 8, b4 = lane & 4, b2 = lane & 2;
+    const int sub = (b4 ? 2 : 0) + (b2 ? 1 : 0);
+    const bool valid = !(lane & 1) && (b8 ? sub <= 1 : sub <= 2);
+    return valid ? ((b16 ? 5 : 0) + (b8 ? 3 : 0) + sub) : -1;
+}
+
+// Sum v[0..9] over the warp with a value-splitting butterfly: every exchange halves the number of values a lane still owns
+// (10 -> 5 -> 3 -> 2 -> 1 -> 1), 12 shuffles in all. On return lane l holds the total of value reduce_slot(l).
+__device__ __forceinline__ float warp_reduce10(const float (&v)[NV], unsigned lane) {
     const bool b16 = lane & 16, b8 = lane & 8, b4 = lane & 4, b2 = lane & 2;
     float w[6], u[4], t[2];
 #pragma unroll
@@ -89,9 +97,6 @@ __device__ __forceinline__ float warp_reduce10(const float (&v)[NV], unsigned la
         t[0] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
     }
     t[0] += __shfl_xor_sync(0xffffffffu, t[0], 1);
-    const int sub = (b4 ? 2 : 0) + (b2 ? 1 : 0);
-    const bool valid = !(lane & 1) && (b8 ? sub <= 1 : sub <= 2);
-    slot = valid ? ((b16 ? 5 : 0) + (b8 ? 3 : 0) + sub) : -1;
     return t[0];
 }
 
@@ -323,6 +328,12 @@ __global__ void __launch_bounds__(BwdCfg<Q>::THREADS, BwdCfg<Q>::MIN_CTAS) blend
     const float ddelx_dx = 0.5f * W;
     const float ddely_dy = 0.5f * H;
 
+    // the lane id and the lane's slot in the reduction are pinned to registers: ptxas otherwise re-derives both from %tid inside the loop
+    unsigned lane_r = lane;
+    int my_slot = reduce_slot(lane);
+    if (!DEPTH && my_slot == 9) my_slot = -1;
+    asm volatile("" : "+r"(lane_r), "+r"(my_slot));
+
     int pending = -1;
     int my_gid = -1;
     float4 my_con = {0.f, 0.f, 0.f, 0.f};  // conic xx, xy, yy and opacity of the splat this thread flushes
@@ -388,9 +399,8 @@ __global__ void __launch_bounds__(BwdCfg<Q>::THREADS, BwdCfg<Q>::MIN_CTAS) blend
             float v[NV];
             const float4 q0 = rp[0], q1 = rp[1], q2 = rp[2];
             if (!bwd_splat<LOD, DEPTH, Q>(p2, pos, q0, q1, q2, null_thr, v)) continue;  // the same answer in every lane
-            int slot;
-            const float total = warp_reduce10(v, lane, slot);
-            if (slot >= 0 && (DEPTH || slot < 9) && total != 0.f) atomicAdd(accp + slot, total);
+            const float total = warp_reduce10(v, lane_r);
+            if (my_slot >= 0 && total != 0.f) atomicAdd(accp + my_slot, total);
         }
     }
     __syncthreads();
