@@ -35,13 +35,16 @@ template <int Q>
 struct BwdCfg {
     static constexpr int THREADS = 128 / Q;
     static constexpr int BATCH = THREADS;
+    // accumulator copies per batch: with Q >= 2 every warp owns one (plain read-modify-write, summed when the batch is flushed); Q = 1 keeps one
+    // copy for its four warps and adds to it with shared-memory atomics (a compare-and-swap loop for float)
+    static constexpr int COPIES = Q == 1 ? 1 : THREADS / 32;
     static constexpr int MIN_CTAS = Q == 1 ? 7 : Q == 2 ? 10 : 12;  // register budget asked of ptxas: 72 / 96 / 168 per thread
 };
 
 template <int Q>
 struct BwdSmemT {
     SplatRec recs[2][BwdCfg<Q>::BATCH];
-    float acc[2][BwdCfg<Q>::BATCH * NV];
+    float acc[2][BwdCfg<Q>::COPIES][BwdCfg<Q>::BATCH * NV];
     uint64_t bar[2];
     unsigned warp_max[BwdCfg<Q>::THREADS / 32];
 };
@@ -238,7 +241,7 @@ __global__ void __launch_bounds__(BwdCfg<Q>::THREADS, BwdCfg<Q>::MIN_CTAS) blend
                                                                float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic2D,
                                                                float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolors,
                                                                float* __restrict__ dL_dinvdepths) {
-    constexpr int BWD_THREADS = BwdCfg<Q>::THREADS, BWD_BATCH = BwdCfg<Q>::BATCH;
+    constexpr int BWD_THREADS = BwdCfg<Q>::THREADS, BWD_BATCH = BwdCfg<Q>::BATCH, COPIES = BwdCfg<Q>::COPIES;
     using BwdSmem = BwdSmemT<Q>;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
@@ -291,7 +294,7 @@ __global__ void __launch_bounds__(BwdCfg<Q>::THREADS, BwdCfg<Q>::MIN_CTAS) blend
         mbar_init(&sm.bar[1], BWD_THREADS);
         mbar_fence_init();
     }
-    for (int i = tid; i < 2 * BWD_BATCH * NV; i += BWD_THREADS) (&sm.acc[0][0])[i] = 0.f;
+    for (int i = tid; i < 2 * COPIES * BWD_BATCH * NV; i += BWD_THREADS) (&sm.acc[0][0][0])[i] = 0.f;
     __syncthreads();
     unsigned L = 0;
 #pragma unroll
@@ -339,13 +342,20 @@ __global__ void __launch_bounds__(BwdCfg<Q>::THREADS, BwdCfg<Q>::MIN_CTAS) blend
     float4 my_con = {0.f, 0.f, 0.f, 0.f};  // conic xx, xy, yy and opacity of the splat this thread flushes
     auto flush = [&]() {
         if (pending < 0) return;
-        float* a = &sm.acc[pending & 1][tid * NV];
         if (my_gid >= 0) {
             float v[NV];
             bool any = false;
 #pragma unroll
             for (int k = 0; k < NV; k += 2) {
-                const float2 t2 = *reinterpret_cast<const float2*>(a + k);
+                float2 t2 = make_float2(0.f, 0.f);
+#pragma unroll
+                for (int c = 0; c < COPIES; c++) {
+                    float2* a2 = reinterpret_cast<float2*>(&sm.acc[pending & 1][c][tid * NV + k]);
+                    const float2 x = *a2;
+                    if (x.x != 0.f || x.y != 0.f) *a2 = make_float2(0.f, 0.f);
+                    t2.x += x.x;
+                    t2.y += x.y;
+                }
                 v[k] = t2.x;
                 v[k + 1] = t2.y;
                 any |= (t2.x != 0.f) | (t2.y != 0.f);
@@ -362,8 +372,6 @@ __global__ void __launch_bounds__(BwdCfg<Q>::THREADS, BwdCfg<Q>::MIN_CTAS) blend
                 atomicAdd(&dL_dcolors[3 * (size_t)my_gid + 1], v[7]);
                 atomicAdd(&dL_dcolors[3 * (size_t)my_gid + 2], v[8]);
                 if (DEPTH) atomicAdd(&dL_dinvdepths[my_gid], v[9]);
-#pragma unroll
-                for (int k = 0; k < NV; k += 2) *reinterpret_cast<float2*>(a + k) = make_float2(0.f, 0.f);
             }
         }
         pending = -1;
@@ -393,14 +401,17 @@ __global__ void __launch_bounds__(BwdCfg<Q>::THREADS, BwdCfg<Q>::MIN_CTAS) blend
         if (lo >= wmax) continue;  // nothing in this batch reaches any pixel of this warp
         const int jtop = (int)min((unsigned)cnt, wmax - lo) - 1;
         const float4* __restrict__ rp = reinterpret_cast<const float4*>(&sm.recs[s][0]) + 3 * jtop;
-        float* accp = &sm.acc[s][jtop * NV];
+        float* accp = &sm.acc[s][Q == 1 ? 0 : warp][jtop * NV];
         unsigned pos = lo + (unsigned)jtop;  // 0-based position in the tile's list == contributor index - 1
         _Pragma("unroll 2") for (int j = jtop; j >= 0; j--, rp -= 3, accp -= NV, pos--) {
             float v[NV];
             const float4 q0 = rp[0], q1 = rp[1], q2 = rp[2];
             if (!bwd_splat<LOD, DEPTH, Q>(p2, pos, q0, q1, q2, null_thr, v)) continue;  // the same answer in every lane
             const float total = warp_reduce10(v, lane_r);
-            if (my_slot >= 0 && total != 0.f) atomicAdd(accp + my_slot, total);
+            if (my_slot >= 0 && total != 0.f) {
+                if (Q == 1) atomicAdd(accp + my_slot, total);
+                else accp[my_slot] += total;  // this warp's copy: lanes own distinct slots, splats are taken one after the other
+            }
         }
     }
     __syncthreads();
