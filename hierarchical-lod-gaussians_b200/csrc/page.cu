@@ -82,6 +82,16 @@ __global__ void pg_apply_kernel(const float* __restrict__ src, long long n, int 
     }
 }
 
+// ---- scratch of the allocation-free variant (lodgs_page_plan_static): the per-block kept counts of up to PG_STATIC_MAX_ROWS rows and the
+// two totals, held in the module's own device memory (every GPU that loads the library keeps these 64.4 KiB until exit).
+constexpr long long PG_STATIC_MAX_ROWS = 16ll << 20;                                   // 16 777 216 resident rows
+constexpr int PG_STATIC_WORDS = 32 + (int)(PG_STATIC_MAX_ROWS / PG_BLOCK) + 2;          // [0..1] totals, [32..] block sums
+static __device__ __align__(256) int g_pg_static_scratch[PG_STATIC_WORDS];
+
+__global__ void pg_copy_counts_kernel(const int* __restrict__ counts, int32_t* __restrict__ out) {
+    if (threadIdx.x < 2) out[threadIdx.x] = counts[threadIdx.x];
+}
+
 }  // namespace lodgs
 
 using namespace lodgs;
@@ -113,6 +123,38 @@ extern "C" int lodgs_page_plan(const uint8_t* keep_mask, int64_t n, int32_t* dst
         if (!h) { set_error("lodgs_page_plan: reading the counts back failed"); return LODGS_E_CUDA; }
         counts_host[0] = h[0]; counts_host[1] = h[1];
     }
+    return LODGS_OK;
+}
+
+extern "C" int64_t lodgs_page_plan_static_max_rows(void) { return (int64_t)PG_STATIC_MAX_ROWS; }
+
+// lodgs_page_plan without a caller workspace and without any allocation: the scan's scratch is g_pg_static_scratch. In host code that name
+// is only the host-side stand-in of the symbol; its device address is looked up once per device (with that device current) and cached.
+// The totals go to a caller-owned DEVICE buffer (no mapped-pinned read-back: that path sets up an event and pinned words on first use).
+extern "C" int lodgs_page_plan_static(const uint8_t* keep_mask, int64_t n, int32_t* dst, int32_t* counts_dev, void* stream) {
+    if (n < 0 || (n > 0 && (!keep_mask || !dst)) || !counts_dev) { set_error("lodgs_page_plan_static: bad argument"); return LODGS_E_ARG; }
+    if (n > PG_STATIC_MAX_ROWS) {
+        set_error("lodgs_page_plan_static: %lld rows exceed the static scratch's maximum of %lld (use lodgs_page_plan with a caller workspace)",
+                  (long long)n, PG_STATIC_MAX_ROWS);
+        return LODGS_E_WORKSPACE;
+    }
+    static std::atomic<int*> scratch_of[MAX_DEVICES];
+    const int dslot = device_slot();
+    int* scratch = scratch_of[dslot].load(std::memory_order_acquire);
+    if (!scratch) {
+        LODGS_CUDA(cudaGetSymbolAddress((void**)&scratch, g_pg_static_scratch));
+        scratch_of[dslot].store(scratch, std::memory_order_release);
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    int* counts = scratch;        // [0] kept, [1] evicted — written by pg_scan_sums_kernel on every call
+    int* sums = scratch + 32;     // one word per block of this call, written before it is read: nothing has to start at zero
+    const int nb = (int)((n + PG_BLOCK - 1) / PG_BLOCK);
+    if (n > 0) pg_scan_block_kernel<<<nb, PG_BLOCK, 0, s>>>(keep_mask, n, dst, sums);
+    pg_scan_sums_kernel<<<1, PG_BLOCK, 0, s>>>(nb, n, sums, counts);
+    if (n > 0) pg_scan_add_kernel<<<nb, PG_BLOCK, 0, s>>>(n, dst, sums);
+    pg_copy_counts_kernel<<<1, 32, 0, s>>>(counts, counts_dev);
+    for (int i = 0; i < (n > 0 ? 4 : 2); i++) count_launch();
+    LODGS_CUDA(cudaGetLastError());
     return LODGS_OK;
 }
 

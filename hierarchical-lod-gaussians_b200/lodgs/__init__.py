@@ -100,6 +100,8 @@ _SIGS = {
     "lodgs_upper_tree_cut": (_i, [_p, _i, _i, _p, _p, _p, _i, _p, _p, _f, _p, _i, _p, _p, _p, _p, _p, _sz, _p, _p]),
     "lodgs_page_workspace_bytes": (_sz, [_i64]),
     "lodgs_page_plan": (_i, [_p, _i64, _p, _p, _sz, _p, _p]),
+    "lodgs_page_plan_static_max_rows": (_i64, []),
+    "lodgs_page_plan_static": (_i, [_p, _i64, _p, _p, _p]),
     "lodgs_page_apply": (_i, [_p, _i64, _i, _p, _p, _p, _p, _i64, _i64, _p]),
     "lodgs_host_scatter_rows": (_i, [_p, _i64, _i64, _p, _i64, _p]),
     "lodgs_host_gather_rows": (_i, [_p, _i64, _i64, _p, _i64, _p]),

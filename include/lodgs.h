@@ -138,6 +138,16 @@ int lodgs_upper_tree_cut(const int32_t* nodes, int N, int root, const float* xyz
  * pinned staging and the big host storage tensors with memcpy over the host cores (storage[indices[i]] = staging[i] and the reverse). */
 size_t lodgs_page_workspace_bytes(int64_t n);
 int lodgs_page_plan(const uint8_t* keep_mask, int64_t n, int32_t* dst, void* ws, size_t ws_bytes, int32_t* counts_host, void* stream);
+/* lodgs_page_plan for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc). No
+ * counterpart in the reference. Same dst[] as lodgs_page_plan; the scan's scratch is a static
+ * __device__ array inside the library (64.4 KiB, held by every GPU that loads the library until exit), so n is limited to
+ * lodgs_page_plan_static_max_rows() = 16 777 216 rows — more returns LODGS_E_WORKSPACE with a message naming the limit. The totals
+ * {kept, evicted} go to counts_dev, a caller-owned DEVICE buffer of 2 ints (no host read-back). The call allocates nothing: no cudaMalloc /
+ * cudaFree / pinned memory / events, only kernel launches on `stream`. All calls on a device share the one scratch array: every word a call
+ * reads it has written first (nothing needs clearing between calls), but two calls that overlap on the GPU (different streams, no ordering)
+ * race on it — serialise them. */
+int64_t lodgs_page_plan_static_max_rows(void);
+int lodgs_page_plan_static(const uint8_t* keep_mask, int64_t n, int32_t* dst, int32_t* counts_dev, void* stream);
 int lodgs_page_apply(const float* src, int64_t n, int width, const int32_t* dst, float* out, float* evict, const float* loaded,
                      int64_t n_load, int64_t n_keep, void* stream);
 int lodgs_host_scatter_rows(void* storage, int64_t storage_rows, int64_t row_bytes, const int64_t* indices, int64_t n, const void* staging);
