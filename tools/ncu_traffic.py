@@ -27,6 +27,16 @@ def main(rep, out, note):
         b = float(r[rd].replace(",", "")) * UNIT.get(units[rd], 1.0) + float(r[wr].replace(",", "")) * UNIT.get(units[wr], 1.0)
         us = float(r[tm].replace(",", "")) * TIME.get(units[tm], 1.0)
         kernels.setdefault(name, []).append({"dram_bytes": int(b), "ncu_us": round(us, 3), "signature": sig[:120]})
+    # the library's profile names the two users of the generic sort kernels separately (LODGS_LAUNCHED labels): per step the launch order
+    # is depth histogram, 4 depth passes, tile histogram, 2 tile passes
+    if "sort_onesweep_kernel" in kernels and len(kernels["sort_onesweep_kernel"]) % 6 == 0:
+        v = kernels["sort_onesweep_kernel"]
+        kernels["sort_depth_pass_kernel"] = [e for i, e in enumerate(v) if i % 6 < 4]
+        kernels["sort_tile_pass_kernel"] = [e for i, e in enumerate(v) if i % 6 >= 4]
+    if "sort_histogram_kernel" in kernels and len(kernels["sort_histogram_kernel"]) % 2 == 0:
+        v = kernels["sort_histogram_kernel"]
+        kernels["sort_depth_hist_kernel"] = v[0::2]
+        kernels["sort_tile_hist_kernel"] = v[1::2]
     json.dump({"source": note, "kernels": kernels}, open(out, "w"), indent=1)
     for k, v in kernels.items():
         print("%-28s launches %3d  max dram bytes %12d  last ncu_us %9.3f" % (k, len(v), max(e["dram_bytes"] for e in v), v[-1]["ncu_us"]))
