@@ -22,6 +22,22 @@ from .optim import sh_adam_from_rgb
 AR_FLAGS = RASTER_SQUARE_RECT | RASTER_BACKGROUND_TWICE | RASTER_CLAMPED_ALPHA_GRAD     # antialiasing on: no NO_ANTIALIAS
 
 
+def exchange_gradients(flat, drgb=None, drgb_all=None, dsh=None):
+    """The one exchange step of multi-view training, on any torch.distributed backend (NCCL on the box, gloo in the CPU tests).
+    flat: the geometry gradients of all parameters in one buffer -> summed in place by ONE all-reduce. Then either the factored SH gradient
+    (drgb [P,3] of this rank's view gathered into drgb_all [world,P,3], rank order) or the materialised one (dsh summed in place).
+    -> (handle of the flat all-reduce, handle of the SH part, bytes this rank handed to the collectives)"""
+    w_flat = dist.all_reduce(flat, async_op=True)
+    nbytes = flat.numel() * flat.element_size()
+    if dsh is None:
+        w_sh = dist.all_gather_into_tensor(drgb_all.view(-1, drgb.size(-1)), drgb.view(-1, drgb.size(-1)), async_op=True)   # concatenation form: every backend takes it
+        nbytes += drgb.numel() * drgb.element_size()
+    else:
+        w_sh = dist.all_reduce(dsh, async_op=True)
+        nbytes += dsh.numel() * dsh.element_size()
+    return w_flat, w_sh, nbytes
+
+
 class MultiViewTrainer:
     def __init__(self, par, lrs, cam, bg, W, H, degree, rank, world, mode="auto", eps=1e-15):
         """par: dict of CUDA tensors means3D [P,3], dc [P,1,3], shs_rest [P,K,3], opacities [P,1], scales [P,3], rotations [P,4] (copied);
@@ -92,14 +108,10 @@ class MultiViewTrainer:
         nbytes = 0
         w_flat = w_rgb = w_sh = None
         if self.world > 1:
-            w_flat = dist.all_reduce(self.flat, async_op=True)
-            nbytes = self.flat.numel() * 4
             if factored:
-                w_rgb = dist.all_gather_into_tensor(self.drgb_all, self.drgb, async_op=True)
-                nbytes += self.drgb.numel() * 4
+                w_flat, w_rgb, nbytes = exchange_gradients(self.flat, self.drgb, self.drgb_all)
             else:
-                w_sh = dist.all_reduce(self.dsh, async_op=True)
-                nbytes += self.dsh.numel() * 4
+                w_flat, w_sh, nbytes = exchange_gradients(self.flat, dsh=self.dsh)
             w_flat.wait()
         if timed:
             ev[2].record()
