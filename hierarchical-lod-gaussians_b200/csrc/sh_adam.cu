@@ -16,7 +16,7 @@
 namespace lodgs {
 
 constexpr int SHA_ROWS = 128;      // rows per CTA = threads per CTA
-constexpr int SHA_STRIDE = 49;     // floats per staged row (48 + 1: conflict-free row-wise writes and element-wise reads)
+constexpr int SHA_STRIDE = 52;     // floats per staged row: 16-byte aligned rows, 13 float4 apart = conflict-free 128-bit row-wise writes and element-wise reads
 
 struct ShAdamParams {
     long long n_rows;              // selected rows (length of `relevant`, or all rows)
@@ -50,9 +50,25 @@ __device__ __forceinline__ void sh_basis(int deg, float x, float y, float z, flo
     }
 }
 
+// One element of the update (adam_rows_kernel's arithmetic, adam.cu): returns the new parameter, m and v are updated in place.
 template <bool BIAS>
-__global__ void __launch_bounds__(SHA_ROWS, 8) sh_adam_rgb_kernel(const ShAdamParams p) {
-    __shared__ float s_g[SHA_ROWS * SHA_STRIDE];
+__device__ __forceinline__ float sh_adam_one(const ShAdamParams& p, float par, float g, float step, float& m1, float& v1) {
+    if (BIAS) {
+        m1 = __fmaf_rn(g, p.omb1, __fmul_rn(m1, p.b1));
+        v1 = __fmaf_rn(__fmul_rn(g, g), p.omb2, __fmul_rn(v1, p.b2));
+        const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v1), p.bc2_sqrt), p.eps);
+        return __fmaf_rn(step, __fdiv_rn(m1, denom), par);
+    }
+    m1 = p.b1 * m1 + p.omb1 * g;
+    v1 = p.b2 * v1 + p.omb2 * g * g;
+    return par + -step * m1 / (sqrtf(v1) + p.eps);
+}
+
+// VEC: dc and rest are the two parts of ONE [P,16,3] block (row = 48 contiguous floats, 16-byte aligned), the layout both trainers use:
+// phase B then moves parameter and moments as float4 (3 x 16 B per element group and thread in flight instead of 3 x 4 B).
+template <bool BIAS, bool VEC>
+__global__ void __launch_bounds__(SHA_ROWS, VEC ? 6 : 8) sh_adam_rgb_kernel(const ShAdamParams p) {
+    __shared__ __align__(16) float s_g[SHA_ROWS * SHA_STRIDE];
     __shared__ long long s_row[SHA_ROWS];
     const long long r0 = (long long)blockIdx.x * SHA_ROWS;
     const int tid = threadIdx.x;
@@ -79,25 +95,68 @@ __global__ void __launch_bounds__(SHA_ROWS, 8) sh_adam_rgb_kernel(const ShAdamPa
                 float w[16];
                 sh_basis(p.D, dx / len, dy / len, dz / len, w);
 #pragma unroll
-                for (int k = 0; k < 16; k++) {
-                    const float wk = k < p.ncoef ? w[k] : 0.f;
-                    if (first) {
-                        g[3 * k + 0] = wk * cr; g[3 * k + 1] = wk * cg; g[3 * k + 2] = wk * cb;
-                    } else {
-                        g[3 * k + 0] += wk * cr; g[3 * k + 1] += wk * cg; g[3 * k + 2] += wk * cb;
+                for (int k = 0; k < 16; k++)
+                    if (k >= p.ncoef) w[k] = 0.f;
+                auto val = [&](int j) { const int k = j / 3, ch = j - 3 * k; return w[k] * (ch == 0 ? cr : (ch == 1 ? cg : cb)); };   // j is a constant after unrolling
+                float4* g4 = reinterpret_cast<float4*>(g);
+#pragma unroll
+                for (int q = 0; q < 12; q++) {
+                    float4 a = make_float4(val(4 * q), val(4 * q + 1), val(4 * q + 2), val(4 * q + 3));
+                    if (!first) {
+                        const float4 o = g4[q];
+                        a.x += o.x; a.y += o.y; a.z += o.z; a.w += o.w;
                     }
+                    g4[q] = a;
                 }
                 first = false;
             }
             if (first) {
+                float4* g4 = reinterpret_cast<float4*>(g);
 #pragma unroll
-                for (int j = 0; j < 48; j++) g[j] = 0.f;
+                for (int q = 0; q < 12; q++) g4[q] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
         }
     }
     __syncthreads();
     // ---- phase B: element-wise update, consecutive threads on consecutive floats of a row; U independent elements per trip: indices
     // first, then all 3U loads, then arithmetic and stores (the phase is bound by memory latency)
+    if (VEC) {
+        constexpr int UV = 3;   // 12 float4 per row and 128 rows per CTA: every thread takes 12 groups, 3 at a time
+        for (int e0 = tid; e0 < SHA_ROWS * 12; e0 += UV * SHA_ROWS) {
+            long long off[UV];
+            float4 gg[UV], pp[UV], mm[UV], vv[UV];
+            int qq[UV];
+#pragma unroll
+            for (int u = 0; u < UV; u++) {
+                const int e = e0 + u * SHA_ROWS, lr = e / 12, q = e - lr * 12;
+                const long long row = s_row[lr];
+                off[u] = row >= 0 ? row * 48 + 4 * q : -1;
+                qq[u] = q;
+                gg[u] = *reinterpret_cast<const float4*>(s_g + lr * SHA_STRIDE + 4 * q);
+            }
+#pragma unroll
+            for (int u = 0; u < UV; u++)
+                if (off[u] >= 0) {
+                    mm[u] = *reinterpret_cast<const float4*>(p.dc_m + off[u]);
+                    vv[u] = *reinterpret_cast<const float4*>(p.dc_v + off[u]);
+                    pp[u] = *reinterpret_cast<const float4*>(p.dc + off[u]);
+                }
+#pragma unroll
+            for (int u = 0; u < UV; u++) {
+                if (off[u] < 0) continue;
+                const float s012 = qq[u] == 0 ? p.step_dc : p.step_rest;   // floats 0..2 of a row are the dc coefficients
+                float4 o;
+                o.x = sh_adam_one<BIAS>(p, pp[u].x, gg[u].x, s012, mm[u].x, vv[u].x);
+                o.y = sh_adam_one<BIAS>(p, pp[u].y, gg[u].y, s012, mm[u].y, vv[u].y);
+                o.z = sh_adam_one<BIAS>(p, pp[u].z, gg[u].z, s012, mm[u].z, vv[u].z);
+                o.w = sh_adam_one<BIAS>(p, pp[u].w, gg[u].w, p.step_rest, mm[u].w, vv[u].w);
+                *reinterpret_cast<float4*>(p.dc + off[u]) = o;
+                *reinterpret_cast<float4*>(p.dc_m + off[u]) = mm[u];
+                *reinterpret_cast<float4*>(p.dc_v + off[u]) = vv[u];
+            }
+        }
+        return;
+    }
     const int row_floats = 3 + p.rest_floats;
     const int total = SHA_ROWS * row_floats;
     constexpr int U = 4;
@@ -133,18 +192,8 @@ __global__ void __launch_bounds__(SHA_ROWS, 8) sh_adam_rgb_kernel(const ShAdamPa
             const long long i = idx[u] & ~(1ll << 62);
             const float step = is_dc ? p.step_dc : p.step_rest;
             float m1 = mm[u], v1 = vv[u];
-            const float g = gg[u];
             float* P_ = is_dc ? p.dc : p.rest;
-            if (BIAS) {
-                m1 = __fmaf_rn(g, p.omb1, __fmul_rn(m1, p.b1));
-                v1 = __fmaf_rn(__fmul_rn(g, g), p.omb2, __fmul_rn(v1, p.b2));
-                const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v1), p.bc2_sqrt), p.eps);
-                P_[i] = __fmaf_rn(step, __fdiv_rn(m1, denom), pp[u]);
-            } else {
-                m1 = p.b1 * m1 + p.omb1 * g;
-                v1 = p.b2 * v1 + p.omb2 * g * g;
-                P_[i] = pp[u] + -step * m1 / (sqrtf(v1) + p.eps);
-            }
+            P_[i] = sh_adam_one<BIAS>(p, pp[u], gg[u], step, m1, v1);
             (is_dc ? p.dc_m : p.rest_m)[i] = m1;
             (is_dc ? p.dc_v : p.rest_v)[i] = v1;
         }
@@ -177,16 +226,22 @@ extern "C" int lodgs_sh_adam_from_rgb(int64_t rows, int D, int n_views, const fl
     cudaStream_t s = (cudaStream_t)stream;
     prof_stage_begin(s);
     const unsigned blocks = (unsigned)((p.n_rows + SHA_ROWS - 1) / SHA_ROWS);
+    // one fused [P,16,3] block per tensor (dc = floats 0..2 of a 48-float row, rest = the other 45), rows 16-byte aligned: vector path
+    static const bool no_vec = getenv("LODGS_SH_ADAM_SCALAR") != nullptr;   // A/B
+    const bool vec = !no_vec && rest_floats == 45 && dc_stride == 48 && rest_stride == 48 && rest == dc + 3 && rest_m == dc_m + 3 && rest_v == dc_v + 3 &&
+                     ((uintptr_t)dc % 16) == 0 && ((uintptr_t)dc_m % 16) == 0 && ((uintptr_t)dc_v % 16) == 0;
     if (bias_correction) {
         if (step < 1) { set_error("lodgs_sh_adam_from_rgb: step must be >= 1 with bias correction"); return LODGS_E_ARG; }
         const double bc1 = 1.0 - std::pow(beta1, (double)step), bc2 = 1.0 - std::pow(beta2, (double)step);   // OurAdam.py:331-337
         p.step_dc = (float)(-(lr_dc / bc1)); p.step_rest = (float)(-(lr_rest / bc1));
         p.omb1 = (float)(1.0 - beta1); p.omb2 = (float)(1.0 - beta2); p.bc2_sqrt = (float)std::sqrt(bc2);
-        sh_adam_rgb_kernel<true><<<blocks, SHA_ROWS, 0, s>>>(p);
+        if (vec) sh_adam_rgb_kernel<true, true><<<blocks, SHA_ROWS, 0, s>>>(p);
+        else sh_adam_rgb_kernel<true, false><<<blocks, SHA_ROWS, 0, s>>>(p);
     } else {
         p.step_dc = (float)lr_dc; p.step_rest = (float)lr_rest;
         p.omb1 = 1.0f - (float)beta1; p.omb2 = 1.0f - (float)beta2; p.bc2_sqrt = 1.0f;   // AR adam.cu:26-33 evaluates 1 - beta in float
-        sh_adam_rgb_kernel<false><<<blocks, SHA_ROWS, 0, s>>>(p);
+        if (vec) sh_adam_rgb_kernel<false, true><<<blocks, SHA_ROWS, 0, s>>>(p);
+        else sh_adam_rgb_kernel<false, false><<<blocks, SHA_ROWS, 0, s>>>(p);
     }
     LODGS_LAUNCHED("sh_adam_rgb_kernel");
     return LODGS_OK;

@@ -47,9 +47,14 @@ def test_backward_rgb_equals_backward_and_factorises_dsh():
     vis = radii > 0
     assert float(rgb[8][~vis].abs().max()) == 0.0
     # dL_dsh[k] = basis_k(dir) * dL_drgb: coefficient 0 carries the constant basis value
-    assert torch.allclose(full[5][:, 0], 0.28209479177387814 * rgb[8], rtol=1e-4, atol=1e-14)   # two runs: atomic order differs
+    # (two runs of the blend backward: the order of its float atomics differs, and a colour gradient is a sum of terms of both signs, so
+    # the comparison is relative to each Gaussian's own gradient scale, not element by element)
+    def close(a, b):
+        scale = torch.maximum(a.abs().amax(dim=1, keepdim=True), b.abs().amax(dim=1, keepdim=True))
+        return bool(((a - b).abs() <= 1e-3 * scale + 1e-30).all()) and float((a - b).norm()) <= 1e-5 * float(a.norm())
+    assert close(full[5][:, 0], 0.28209479177387814 * rgb[8])
     d = torch.nn.functional.normalize(sc["means3D"] - c["campos"], dim=1)
-    assert torch.allclose(full[5][:, 2], 0.4886025119029199 * d[:, 2:3] * rgb[8], rtol=1e-4, atol=1e-12)
+    assert close(full[5][:, 2], 0.4886025119029199 * d[:, 2:3] * rgb[8])
 
 
 @pytest.mark.parametrize("bias,rows", [(True, "list"), (True, "all"), (False, "mask"), (False, "all")])
