@@ -8,6 +8,7 @@
 // depth-ordered emission used here.
 #include "gaussmath.cuh"
 #include "state.cuh"
+#include <cstdlib>
 
 namespace lodgs {
 
@@ -194,22 +195,25 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(int R, const uint32_t*
 // inside a class (a stable partition: neighbouring tiles share splat records in L2; a full sort by length was measured slower on the
 // eval path for that reason). One CTA, every thread owns a contiguous run of tiles. A tile's result does not depend on when it runs.
 constexpr int ORDER_CLASSES = 4;
+constexpr int LONG_TILES_LIMIT = 2048;   // = LONG_TILES_MAX of the blend kernels
 __device__ __forceinline__ int order_class(unsigned len, unsigned mx) {
     return len >= (mx >> 1) ? 0 : len >= (mx >> 2) ? 1 : len >= (mx >> 3) ? 2 : 3;
 }
-__global__ void __launch_bounds__(1024) tile_order_kernel(const uint2* __restrict__ ranges, uint32_t* __restrict__ order, int ntiles) {
-    __shared__ unsigned s_max, s_warp[ORDER_CLASSES][32], s_base[ORDER_CLASSES];
+__global__ void __launch_bounds__(1024) tile_order_kernel(const uint2* __restrict__ ranges, uint32_t* __restrict__ order, int ntiles, int split_long) {
+    __shared__ unsigned s_max, s_total, s_warp[ORDER_CLASSES][32], s_base[ORDER_CLASSES];
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_max = 0;
+    if (tid == 0) { s_max = 0; s_total = 0; }
     __syncthreads();
     const int per = (ntiles + 1023) / 1024, lo = min(ntiles, (int)tid * per), hi = min(ntiles, lo + per);
-    unsigned m = 0;
+    unsigned m = 0, sum = 0;
     for (int t = lo; t < hi; t++) {
         const uint2 r = ranges[t];
         m = max(m, r.y - r.x);
+        sum += r.y - r.x;
     }
     m = __reduce_max_sync(0xffffffffu, m);
-    if (lane == 0) atomicMax(&s_max, m);
+    sum = __reduce_add_sync(0xffffffffu, sum);
+    if (lane == 0) { atomicMax(&s_max, m); atomicAdd(&s_total, sum); }
     __syncthreads();
     const unsigned mx = max(s_max, 8u);
     unsigned cnt[ORDER_CLASSES] = {0, 0, 0, 0}, incl[ORDER_CLASSES];
@@ -256,6 +260,20 @@ __global__ void __launch_bounds__(1024) tile_order_kernel(const uint2* __restric
         for (int k = 0; k < ORDER_CLASSES; k++)
             if (c == k) order[pos[k]++] = (uint32_t)t;
     }
+    // LONG tiles (blend_fwd.cu / blend_bwd.cu take each of them with two CTAs of two pixels per thread instead of one CTA of four): the
+    // launch is latency-bound on its longest lists when the longest alone is more than 1/1024 of all instances (a B200 keeps ~1500-2000
+    // blend CTAs resident, so every tile starts at once and the kernel lasts as long as its slowest tile). Then every tile within a factor
+    // of eight of the longest (classes 0-2, the first entries of `order`) is a candidate for the critical path — the longest lists often
+    // end early by saturation, the medium ones are walked to the end — and gets the shorter per-splat chain; at most LONG_TILES_LIMIT.
+    if (tid == 0) {
+        const bool skewed = split_long && s_max >= 256u && (unsigned long long)s_max * 1024ull > (unsigned long long)s_total;
+        unsigned n = 0;
+        if (skewed) {
+            const unsigned c01 = s_base[0] + s_base[1], c012 = c01 + s_base[2];
+            n = c012 <= (unsigned)LONG_TILES_LIMIT ? c012 : c01 <= (unsigned)LONG_TILES_LIMIT ? c01 : min(s_base[0], (unsigned)LONG_TILES_LIMIT);
+        }
+        order[ntiles] = n;
+    }
 }
 
 // LOD rendering: the last two slots of every blend record become the interpolation weight and 1/kids.
@@ -295,7 +313,8 @@ int launch_tile_ranges(int R, const BinningState& b, uint2* ranges, size_t ntile
     return LODGS_OK;
 }
 int launch_tile_order(const uint2* ranges, uint32_t* order, size_t ntiles, cudaStream_t s) {
-    tile_order_kernel<<<1, 1024, 0, s>>>(ranges, order, (int)ntiles);
+    static const int split_long = getenv("LODGS_LONG_TILES") ? atoi(getenv("LODGS_LONG_TILES")) : 1;   // A/B: 0 = every tile as one CTA
+    tile_order_kernel<<<1, 1024, 0, s>>>(ranges, order, (int)ntiles, split_long);
     LODGS_LAUNCHED("tile_order_kernel");
     return LODGS_OK;
 }

@@ -27,26 +27,46 @@ static int set_lod_cut() {
 
 constexpr int NV = 10;  // dmean.x dmean.y dconic.xx dconic.xy dconic.yy dopacity dcol.r dcol.g dcol.b dinvdepth
 
-// Q = vertically adjacent pixel PAIRS per thread. A CTA is one 16x16 tile, so it has 128 / Q threads: Q = 1 is 16 x 8 threads with two pixels
-// each (a warp covers 16x4 pixels), Q = 2 is 16 x 4 threads with a column of four pixels each (a warp covers 16x8). Everything that is paid once
-// per (warp, splat) — the three record loads, the loop, the two votes, the 12-shuffle reduction and the shared atomics — is shared by twice
-// the pixels with Q = 2. The batch (splats gathered per round, one per thread) shrinks with the CTA.
-template <int Q>
+// Q = vertically adjacent pixel PAIRS per thread: Q = 2 is a column of four pixels per thread (a warp covers 16x8 pixels), Q = 1 two pixels
+// (a warp covers 16x4). Everything that is paid once per (warp, splat) — the three record loads, the loop, the two votes, the 12-shuffle
+// reduction and the accumulate — is shared by twice the pixels with Q = 2, which is what a throughput-bound launch wants. A tile with a very
+// long list is LATENCY-bound instead (its CTA walks the list alone while the SMs run dry): there the shorter per-splat chain of Q = 1 wins.
+// The default kernel (NT = 64 threads) therefore takes a tile either as ONE CTA with Q = 2 or, for the tiles binning.cu's tile_order_kernel
+// marked as long, as TWO CTAs with Q = 1 that each own half of the tile's rows and walk the same list. NT = 128 is the round-1 shape
+// (one CTA of 16 x 8 threads per tile, Q = 1), kept for A/B (LODGS_BWD_PX=2). The batch (splats gathered per round, one per thread)
+// follows the CTA size.
+constexpr int LONG_TILES_MAX = 2048;  // upper bound of the number of long tiles (tile_order_kernel), i.e. of the extra CTAs of a launch
+template <int NT>
 struct BwdCfg {
-    static constexpr int THREADS = 128 / Q;
-    static constexpr int BATCH = THREADS;
-    // accumulator copies per batch: with Q >= 2 every warp owns one (plain read-modify-write, summed when the batch is flushed); Q = 1 keeps one
-    // copy for its four warps and adds to it with shared-memory atomics (a compare-and-swap loop for float)
-    static constexpr int COPIES = Q == 1 ? 1 : THREADS / 32;
-    static constexpr int MIN_CTAS = Q == 1 ? 7 : Q == 2 ? 10 : 12;  // register budget asked of ptxas: 72 / 96 / 168 per thread
+    static constexpr int THREADS = NT;
+    static constexpr int BATCH = NT;
+    // accumulator copies per batch: with 64 threads every warp owns one (plain read-modify-write, summed when the batch is flushed); 128
+    // threads keep one copy for their four warps and add to it with shared-memory atomics (a compare-and-swap loop for float)
+    static constexpr int COPIES = NT == 64 ? 2 : 1;
+    static constexpr int MIN_CTAS = NT == 64 ? 10 : 7;  // register budget asked of ptxas: 96 / 72 per thread
 };
 
-template <int Q>
+template <int NT>
 struct BwdSmemT {
-    SplatRec recs[2][BwdCfg<Q>::BATCH];
-    float acc[2][BwdCfg<Q>::COPIES][BwdCfg<Q>::BATCH * NV];
+    SplatRec recs[2][BwdCfg<NT>::BATCH];
+    float acc[2][BwdCfg<NT>::COPIES][BwdCfg<NT>::BATCH * NV];
     uint64_t bar[2];
-    unsigned warp_max[BwdCfg<Q>::THREADS / 32];
+    unsigned warp_max[BwdCfg<NT>::THREADS / 32];
+};
+
+struct BwdArgs {
+    const uint2* ranges;
+    const uint32_t* tile_order;   // [tiles] + the number of long tiles at [tiles]; NULL = tile-id order
+    const SplatRec* recs;
+    const uint32_t* point_list;
+    int W, H;
+    const float* bg_color;
+    float bg_mult, null_thr;
+    const int32_t* indices;
+    const float* final_Ts;
+    const uint32_t* n_contrib;
+    const float *dL_dpixels, *dL_invdepths;
+    float *dL_dmean2D, *dL_dconic2D, *dL_dopacity, *dL_dcolors, *dL_dinvdepths;
 };
 
 __device__ __forceinline__ float ex2_ftz(float x) {
@@ -231,26 +251,30 @@ __device__ __forceinline__ bool bwd_splat(BwdPix<Q>& p, const unsigned pos, cons
     return true;
 }
 
-template <bool LOD, bool DEPTH, int Q>
-__global__ void __launch_bounds__(BwdCfg<Q>::THREADS, BwdCfg<Q>::MIN_CTAS) blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const SplatRec* __restrict__ recs,
-                                                               const uint32_t* __restrict__ point_list, int W, int H,
-                                                               const float* __restrict__ bg_color, const float bg_mult,
-                                                               const float null_thr, const int32_t* __restrict__ indices,
-                                                               const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
-                                                               const float* __restrict__ dL_dpixels, const float* __restrict__ dL_invdepths,
-                                                               float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic2D,
-                                                               float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolors,
-                                                               float* __restrict__ dL_dinvdepths) {
-    constexpr int BWD_THREADS = BwdCfg<Q>::THREADS, BWD_BATCH = BwdCfg<Q>::BATCH, COPIES = BwdCfg<Q>::COPIES;
-    using BwdSmem = BwdSmemT<Q>;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
+// One tile (rows y_off .. y_off + 2*Q*NT/16 - 1 of it) replayed by the NT threads of this CTA.
+template <bool LOD, bool DEPTH, int Q, int NT>
+__device__ __forceinline__ void bwd_tile(const BwdArgs& a, BwdSmemT<NT>& sm, const unsigned tile, const unsigned y_off) {
+    constexpr int BWD_THREADS = BwdCfg<NT>::THREADS, BWD_BATCH = BwdCfg<NT>::BATCH, COPIES = BwdCfg<NT>::COPIES;
+    const uint2* __restrict__ ranges = a.ranges;
+    const SplatRec* __restrict__ recs = a.recs;
+    const uint32_t* __restrict__ point_list = a.point_list;
+    const int W = a.W, H = a.H;
+    const float* __restrict__ bg_color = a.bg_color;
+    const float bg_mult = a.bg_mult, null_thr = a.null_thr;
+    const int32_t* __restrict__ indices = a.indices;
+    const float* __restrict__ final_Ts = a.final_Ts;
+    const uint32_t* __restrict__ n_contrib = a.n_contrib;
+    const float* __restrict__ dL_dpixels = a.dL_dpixels;
+    const float* __restrict__ dL_invdepths = a.dL_invdepths;
+    float* __restrict__ dL_dmean2D = a.dL_dmean2D;
+    float* __restrict__ dL_dconic2D = a.dL_dconic2D;
+    float* __restrict__ dL_dopacity = a.dL_dopacity;
+    float* __restrict__ dL_dcolors = a.dL_dcolors;
+    float* __restrict__ dL_dinvdepths = a.dL_dinvdepths;
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, tx = tid & 15u, ty = tid >> 4;
     const unsigned horizontal_blocks = (W + TILE_X - 1) / TILE_X;
-    const unsigned cta = blockIdx.y * horizontal_blocks + blockIdx.x;
-    const unsigned tile = tile_order ? __ldg(tile_order + cta) : cta;   // longest lists first (binning.cu)
     const unsigned tile_x = tile % horizontal_blocks, tile_y = tile / horizontal_blocks;
-    const unsigned pix_x = tile_x * TILE_X + tx, pix_y0 = tile_y * TILE_Y + 2u * Q * ty;
+    const unsigned pix_x = tile_x * TILE_X + tx, pix_y0 = tile_y * TILE_Y + y_off + 2u * Q * ty;
     const uint2 range = ranges[tile];
     const size_t HW = (size_t)H * W;
     const float bg0 = bg_color[0], bg1 = bg_color[1], bg2 = bg_color[2];
@@ -401,7 +425,7 @@ __global__ void __launch_bounds__(BwdCfg<Q>::THREADS, BwdCfg<Q>::MIN_CTAS) blend
         if (lo >= wmax) continue;  // nothing in this batch reaches any pixel of this warp
         const int jtop = (int)min((unsigned)cnt, wmax - lo) - 1;
         const float4* __restrict__ rp = reinterpret_cast<const float4*>(&sm.recs[s][0]) + 3 * jtop;
-        float* accp = &sm.acc[s][Q == 1 ? 0 : warp][jtop * NV];
+        float* accp = &sm.acc[s][COPIES == 1 ? 0 : warp][jtop * NV];
         unsigned pos = lo + (unsigned)jtop;  // 0-based position in the tile's list == contributor index - 1
         _Pragma("unroll 2") for (int j = jtop; j >= 0; j--, rp -= 3, accp -= NV, pos--) {
             float v[NV];
@@ -409,7 +433,7 @@ __global__ void __launch_bounds__(BwdCfg<Q>::THREADS, BwdCfg<Q>::MIN_CTAS) blend
             if (!bwd_splat<LOD, DEPTH, Q>(p2, pos, q0, q1, q2, null_thr, v)) continue;  // the same answer in every lane
             const float total = warp_reduce10(v, lane_r);
             if (my_slot >= 0 && total != 0.f) {
-                if (Q == 1) atomicAdd(accp + my_slot, total);
+                if (COPIES == 1) atomicAdd(accp + my_slot, total);
                 else accp[my_slot] += total;  // this warp's copy: lanes own distinct slots, splats are taken one after the other
             }
         }
@@ -418,47 +442,66 @@ __global__ void __launch_bounds__(BwdCfg<Q>::THREADS, BwdCfg<Q>::MIN_CTAS) blend
     flush();
 }
 
-template <bool LOD, bool DEPTH, int Q, typename... Args>
-static int launch_bwd_variant(dim3 grid, cudaStream_t s, Args... args) {
+template <bool LOD, bool DEPTH, int NT>
+__global__ void __launch_bounds__(BwdCfg<NT>::THREADS, BwdCfg<NT>::MIN_CTAS) blend_bwd_kernel(const BwdArgs a) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    BwdSmemT<NT>& sm = *reinterpret_cast<BwdSmemT<NT>*>(smem_raw);
+    const unsigned ntiles = ((a.W + TILE_X - 1) / TILE_X) * ((a.H + TILE_Y - 1) / TILE_Y);
+    const unsigned cta = blockIdx.x;
+    if (NT == 64) {
+        // CTAs [0, 2 n_long): the long tiles, two CTAs each (upper / lower eight rows, two pixels per thread); then one CTA per remaining tile
+        const unsigned n_long = a.tile_order ? __ldg(a.tile_order + ntiles) : 0u;
+        if (cta < 2u * n_long) {
+            bwd_tile<LOD, DEPTH, 1, NT>(a, sm, __ldg(a.tile_order + (cta >> 1)), 8u * (cta & 1u));
+            return;
+        }
+        const unsigned i = cta - n_long;
+        if (i >= ntiles) return;
+        bwd_tile<LOD, DEPTH, 2, NT>(a, sm, a.tile_order ? __ldg(a.tile_order + i) : i, 0u);   // longest lists first (binning.cu)
+    } else {
+        if (cta >= ntiles) return;
+        bwd_tile<LOD, DEPTH, 1, NT>(a, sm, a.tile_order ? __ldg(a.tile_order + cta) : cta, 0u);
+    }
+}
+
+template <bool LOD, bool DEPTH, int NT>
+static int launch_bwd_variant(unsigned grid, cudaStream_t s, const BwdArgs& a) {
     static std::atomic<bool> attr_set[MAX_DEVICES];
     const int dslot = device_slot();
     if (!attr_set[dslot].load(std::memory_order_acquire)) {
-        LODGS_CUDA(cudaFuncSetAttribute(blend_bwd_kernel<LOD, DEPTH, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemT<Q>)));
+        LODGS_CUDA(cudaFuncSetAttribute(blend_bwd_kernel<LOD, DEPTH, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemT<NT>)));
         attr_set[dslot].store(true, std::memory_order_release);
     }
-    blend_bwd_kernel<LOD, DEPTH, Q><<<grid, dim3(BwdCfg<Q>::THREADS, 1, 1), sizeof(BwdSmemT<Q>), s>>>(args...);
+    blend_bwd_kernel<LOD, DEPTH, NT><<<grid, NT, sizeof(BwdSmemT<NT>), s>>>(a);
     return LODGS_OK;
 }
 
 int launch_blend_bwd(bool lod, bool depth, const ImageState& img, const BinningState& bin, const SplatRec* recs, int W, int H,
                      const float* bg, float bg_mult, float null_thr, const int32_t* indices, const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dmean2D, float* dL_dconic,
                      float* dL_dopacity, float* dL_dcolor, float* dL_dinvdepth, cudaStream_t s) {
-    dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1);
+    const unsigned ntiles = (unsigned)((W + TILE_X - 1) / TILE_X) * (unsigned)((H + TILE_Y - 1) / TILE_Y);
     static const bool tile_id_order = getenv("LODGS_BLEND_TILE_ID_ORDER") != nullptr;  // A/B: CTAs in tile-id order
-    static const int px = getenv("LODGS_BWD_PX") ? atoi(getenv("LODGS_BWD_PX")) : 4;   // A/B: pixels per thread (2 or 4)
+    static const int px = getenv("LODGS_BWD_PX") ? atoi(getenv("LODGS_BWD_PX")) : 4;   // A/B: 2 = 128-thread CTAs with two pixels per thread
     static const int lod_cut_rc = set_lod_cut();
     if (lod_cut_rc) { set_error("blend: setting the LOD cut-off switch failed"); return LODGS_E_CUDA; }
-    const uint32_t* order = tile_id_order ? nullptr : img.tile_order;
-#define LODGS_BWD_ARGS grid, s, (const uint2*)img.ranges, order, recs, (const uint32_t*)bin.point_list, W, H, bg, bg_mult, null_thr, indices, (const float*)img.final_T, \
-                       (const uint32_t*)img.n_contrib, dL_dpix, dL_dinvdepth_pix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dinvdepth
+    BwdArgs a;
+    a.ranges = img.ranges; a.tile_order = tile_id_order ? nullptr : img.tile_order; a.recs = recs; a.point_list = bin.point_list; a.W = W; a.H = H;
+    a.bg_color = bg; a.bg_mult = bg_mult; a.null_thr = null_thr; a.indices = indices; a.final_Ts = img.final_T; a.n_contrib = img.n_contrib;
+    a.dL_dpixels = dL_dpix; a.dL_invdepths = dL_dinvdepth_pix; a.dL_dmean2D = dL_dmean2D; a.dL_dconic2D = dL_dconic; a.dL_dopacity = dL_dopacity;
+    a.dL_dcolors = dL_dcolor; a.dL_dinvdepths = dL_dinvdepth;
     int rc;
     if (px == 2) {
-        if (lod && depth) rc = launch_bwd_variant<true, true, 1>(LODGS_BWD_ARGS);
-        else if (lod) rc = launch_bwd_variant<true, false, 1>(LODGS_BWD_ARGS);
-        else if (depth) rc = launch_bwd_variant<false, true, 1>(LODGS_BWD_ARGS);
-        else rc = launch_bwd_variant<false, false, 1>(LODGS_BWD_ARGS);
-    } else if (px == 8) {
-        if (lod && depth) rc = launch_bwd_variant<true, true, 4>(LODGS_BWD_ARGS);
-        else if (lod) rc = launch_bwd_variant<true, false, 4>(LODGS_BWD_ARGS);
-        else if (depth) rc = launch_bwd_variant<false, true, 4>(LODGS_BWD_ARGS);
-        else rc = launch_bwd_variant<false, false, 4>(LODGS_BWD_ARGS);
+        if (lod && depth) rc = launch_bwd_variant<true, true, 128>(ntiles, s, a);
+        else if (lod) rc = launch_bwd_variant<true, false, 128>(ntiles, s, a);
+        else if (depth) rc = launch_bwd_variant<false, true, 128>(ntiles, s, a);
+        else rc = launch_bwd_variant<false, false, 128>(ntiles, s, a);
     } else {
-        if (lod && depth) rc = launch_bwd_variant<true, true, 2>(LODGS_BWD_ARGS);
-        else if (lod) rc = launch_bwd_variant<true, false, 2>(LODGS_BWD_ARGS);
-        else if (depth) rc = launch_bwd_variant<false, true, 2>(LODGS_BWD_ARGS);
-        else rc = launch_bwd_variant<false, false, 2>(LODGS_BWD_ARGS);
+        const unsigned grid = ntiles + (a.tile_order ? (unsigned)LONG_TILES_MAX : 0u);   // the CTAs beyond tiles + n_long exit at once
+        if (lod && depth) rc = launch_bwd_variant<true, true, 64>(grid, s, a);
+        else if (lod) rc = launch_bwd_variant<true, false, 64>(grid, s, a);
+        else if (depth) rc = launch_bwd_variant<false, true, 64>(grid, s, a);
+        else rc = launch_bwd_variant<false, false, 64>(grid, s, a);
     }
-#undef LODGS_BWD_ARGS
     if (rc) return rc;
     LODGS_LAUNCHED("blend_bwd_kernel");
     return LODGS_OK;

@@ -26,21 +26,38 @@ static int set_lod_cut() {
 }
 
 
-// Q = vertically adjacent pixel PAIRS per thread: a CTA is one 16x16 tile with 128 / Q threads (Q = 1: 16 x 8 threads with two pixels each, a warp
-// covers 16x4 pixels; Q = 2: 16 x 4 threads with a column of four pixels each, a warp covers 16x8). What is paid per (warp, splat) — three
-// record loads, the loop with its exit vote, the column-constant dx terms — is shared by twice the pixels with Q = 2. Every thread gathers
-// two records per batch, so the batch shrinks with the CTA.
-template <int Q>
+// Q = vertically adjacent pixel PAIRS per thread (Q = 2: a column of four pixels, a warp covers 16x8; Q = 1: two pixels, a warp covers 16x4).
+// What is paid per (warp, splat) — three record loads, the loop with its exit vote, the column-constant dx terms — is shared by twice the
+// pixels with Q = 2, which a throughput-bound launch wants; a tile with a very long list is latency-bound and wants the shorter per-splat
+// chain of Q = 1. The default kernel (NT = 64 threads) takes a tile as ONE CTA with Q = 2 or, for the tiles tile_order_kernel (binning.cu)
+// marked as long, as TWO CTAs with Q = 1 that own the upper / lower eight rows and walk the same list; per pixel the arithmetic is the same
+// in every mapping, so the outputs stay bit-identical. NT = 128 is the round-1 shape (LODGS_FWD_PX=2). Every thread gathers two records
+// per batch, so the batch follows the CTA size.
+constexpr int LONG_TILES_MAX = 2048;  // upper bound of the number of long tiles, i.e. of the extra CTAs of a launch
+template <int NT>
 struct BlendCfg {
-    static constexpr int THREADS = 128 / Q;
-    static constexpr int BATCH = 2 * THREADS;
+    static constexpr int THREADS = NT;
+    static constexpr int BATCH = 2 * NT;
 };
 
-template <int Q>
+template <int NT>
 struct BlendSmemT {
-    SplatRec recs[2][BlendCfg<Q>::BATCH];
-    uint8_t flag[2][BlendCfg<Q>::BATCH];
+    SplatRec recs[2][BlendCfg<NT>::BATCH];
+    uint8_t flag[2][BlendCfg<NT>::BATCH];
     uint64_t bar[2];
+};
+
+struct FwdArgs {
+    const uint2* ranges;
+    const uint32_t* tile_order;   // [tiles] + the number of long tiles at [tiles]; NULL = tile-id order
+    const SplatRec* recs;
+    const uint32_t* point_list;
+    int W, H;
+    const float* bg_color;
+    float* final_T;
+    uint32_t* n_contrib;
+    float *out_color, *out_invdepth;
+    int32_t* seen;
 };
 
 // Blend state of the thread's 2Q pixels in packed FP32 pairs (pair h: lo = row 2h of the thread's column, hi = the one below it).
@@ -131,22 +148,24 @@ __device__ __forceinline__ void blend_splat(PixState<Q>& p, unsigned (&done)[2 *
     if (SEEN && blended) *flagp = 1;
 }
 
-template <bool LOD, bool DEPTH, bool SEEN, int Q>
-__global__ void __launch_bounds__(BlendCfg<Q>::THREADS) blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const SplatRec* __restrict__ recs,
-                                                                 const uint32_t* __restrict__ point_list, int W, int H,
-                                                                 const float* __restrict__ bg_color, float* __restrict__ final_T,
-                                                                 uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
-                                                                 float* __restrict__ out_invdepth, int32_t* __restrict__ seen) {
-    constexpr int BLEND_THREADS = BlendCfg<Q>::THREADS, BLEND_BATCH = BlendCfg<Q>::BATCH;
-    using BlendSmem = BlendSmemT<Q>;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    BlendSmem& sm = *reinterpret_cast<BlendSmem*>(smem_raw);
+// One tile (rows y_off .. y_off + 2*Q*NT/16 - 1 of it) blended by the NT threads of this CTA.
+template <bool LOD, bool DEPTH, bool SEEN, int Q, int NT>
+__device__ __forceinline__ void fwd_tile(const FwdArgs& a, BlendSmemT<NT>& sm, const unsigned tile, const unsigned y_off) {
+    constexpr int BLEND_THREADS = BlendCfg<NT>::THREADS, BLEND_BATCH = BlendCfg<NT>::BATCH;
+    const uint2* __restrict__ ranges = a.ranges;
+    const SplatRec* __restrict__ recs = a.recs;
+    const uint32_t* __restrict__ point_list = a.point_list;
+    const int W = a.W, H = a.H;
+    const float* __restrict__ bg_color = a.bg_color;
+    float* __restrict__ final_T = a.final_T;
+    uint32_t* __restrict__ n_contrib = a.n_contrib;
+    float* __restrict__ out_color = a.out_color;
+    float* __restrict__ out_invdepth = a.out_invdepth;
+    int32_t* __restrict__ seen = a.seen;
     const unsigned tid = threadIdx.x, tx = tid & 15u, ty = tid >> 4;
     const unsigned horizontal_blocks = (W + TILE_X - 1) / TILE_X;
-    const unsigned cta = blockIdx.y * horizontal_blocks + blockIdx.x;
-    const unsigned tile = tile_order ? __ldg(tile_order + cta) : cta;   // longest lists first (binning.cu)
     const unsigned tile_x = tile % horizontal_blocks, tile_y = tile / horizontal_blocks;
-    const unsigned pix_x = tile_x * TILE_X + tx, pix_y0 = tile_y * TILE_Y + 2u * Q * ty;
+    const unsigned pix_x = tile_x * TILE_X + tx, pix_y0 = tile_y * TILE_Y + y_off + 2u * Q * ty;
     unsigned done[2 * Q];
     PixState<Q> p;
     p.px = (float)pix_x;
@@ -291,27 +310,51 @@ __global__ void __launch_bounds__(BlendCfg<Q>::THREADS) blend_fwd_kernel(const u
     }
 }
 
-template <bool LOD, bool DEPTH, bool SEEN, int Q>
-static int launch_blend_q(dim3 grid, cudaStream_t s, const uint2* ranges, const uint32_t* order, const SplatRec* recs, const uint32_t* point_list, int W, int H,
-                          const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_invdepth, int32_t* seen) {
+template <bool LOD, bool DEPTH, bool SEEN, int NT>
+__global__ void __launch_bounds__(BlendCfg<NT>::THREADS) blend_fwd_kernel(const FwdArgs a) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    BlendSmemT<NT>& sm = *reinterpret_cast<BlendSmemT<NT>*>(smem_raw);
+    const unsigned ntiles = ((a.W + TILE_X - 1) / TILE_X) * ((a.H + TILE_Y - 1) / TILE_Y);
+    const unsigned cta = blockIdx.x;
+    if (NT == 64) {
+        // CTAs [0, 2 n_long): the long tiles, two CTAs each (upper / lower eight rows, two pixels per thread); then one CTA per remaining tile
+        const unsigned n_long = a.tile_order ? __ldg(a.tile_order + ntiles) : 0u;
+        if (cta < 2u * n_long) {
+            fwd_tile<LOD, DEPTH, SEEN, 1, NT>(a, sm, __ldg(a.tile_order + (cta >> 1)), 8u * (cta & 1u));
+            return;
+        }
+        const unsigned i = cta - n_long;
+        if (i >= ntiles) return;
+        fwd_tile<LOD, DEPTH, SEEN, 2, NT>(a, sm, a.tile_order ? __ldg(a.tile_order + i) : i, 0u);   // longest lists first (binning.cu)
+    } else {
+        if (cta >= ntiles) return;
+        fwd_tile<LOD, DEPTH, SEEN, 1, NT>(a, sm, a.tile_order ? __ldg(a.tile_order + cta) : cta, 0u);
+    }
+}
+
+template <bool LOD, bool DEPTH, bool SEEN, int NT>
+static int launch_blend_q(unsigned grid, cudaStream_t s, const FwdArgs& a) {
     static std::atomic<bool> attr_set[MAX_DEVICES];
     const int dslot = device_slot();
     if (!attr_set[dslot].load(std::memory_order_acquire)) {
-        LODGS_CUDA(cudaFuncSetAttribute(blend_fwd_kernel<LOD, DEPTH, SEEN, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BlendSmemT<Q>)));
+        LODGS_CUDA(cudaFuncSetAttribute(blend_fwd_kernel<LOD, DEPTH, SEEN, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BlendSmemT<NT>)));
         attr_set[dslot].store(true, std::memory_order_release);
     }
-    blend_fwd_kernel<LOD, DEPTH, SEEN, Q><<<grid, BlendCfg<Q>::THREADS, sizeof(BlendSmemT<Q>), s>>>(ranges, order, recs, point_list, W, H, bg, final_T, n_contrib,
-                                                                                               out_color, out_invdepth, seen);
+    blend_fwd_kernel<LOD, DEPTH, SEEN, NT><<<grid, NT, sizeof(BlendSmemT<NT>), s>>>(a);
     LODGS_LAUNCHED("blend_fwd_kernel");
     return LODGS_OK;
 }
 
 template <bool LOD, bool DEPTH, bool SEEN>
-static int launch_blend_one(dim3 grid, cudaStream_t s, const uint2* ranges, const uint32_t* order, const SplatRec* recs, const uint32_t* point_list, int W, int H,
+static int launch_blend_one(dim3 grid3, cudaStream_t s, const uint2* ranges, const uint32_t* order, const SplatRec* recs, const uint32_t* point_list, int W, int H,
                             const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_invdepth, int32_t* seen) {
-    static const int px = getenv("LODGS_FWD_PX") ? atoi(getenv("LODGS_FWD_PX")) : 4;   // A/B: pixels per thread (2 or 4)
-    if (px == 2) return launch_blend_q<LOD, DEPTH, SEEN, 1>(grid, s, ranges, order, recs, point_list, W, H, bg, final_T, n_contrib, out_color, out_invdepth, seen);
-    return launch_blend_q<LOD, DEPTH, SEEN, 2>(grid, s, ranges, order, recs, point_list, W, H, bg, final_T, n_contrib, out_color, out_invdepth, seen);
+    static const int px = getenv("LODGS_FWD_PX") ? atoi(getenv("LODGS_FWD_PX")) : 4;   // A/B: 2 = 128-thread CTAs with two pixels per thread
+    const unsigned ntiles = grid3.x * grid3.y;
+    FwdArgs a;
+    a.ranges = ranges; a.tile_order = order; a.recs = recs; a.point_list = point_list; a.W = W; a.H = H; a.bg_color = bg; a.final_T = final_T;
+    a.n_contrib = n_contrib; a.out_color = out_color; a.out_invdepth = out_invdepth; a.seen = seen;
+    if (px == 2) return launch_blend_q<LOD, DEPTH, SEEN, 128>(ntiles, s, a);
+    return launch_blend_q<LOD, DEPTH, SEEN, 64>(ntiles + (order ? (unsigned)LONG_TILES_MAX : 0u), s, a);   // the CTAs beyond tiles + n_long exit at once
 }
 
 template <bool LOD, bool DEPTH>

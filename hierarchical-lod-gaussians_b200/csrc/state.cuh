@@ -140,7 +140,7 @@ struct ImageState {
     float* final_T;       // [W*H]
     uint32_t* n_contrib;  // [W*H]
     uint2* ranges;        // [tiles]
-    uint32_t* tile_order; // [tiles] tile ids, longest list first: the order the blend CTAs take them in
+    uint32_t* tile_order; // [tiles] tile ids, longest list first: the order the blend CTAs take them in; [tiles] = number of LONG tiles (the first ones)
     size_t offsets[3];
     size_t bytes;
 };
@@ -153,7 +153,7 @@ static inline ImageState image_from_chunk(void* chunk, int W, int H) {
     s.final_T = carve_arr<float>(b, off, N);        s.offsets[0] = (char*)s.final_T - b;
     s.n_contrib = carve_arr<uint32_t>(b, off, N);   s.offsets[1] = (char*)s.n_contrib - b;
     s.ranges = carve_arr<uint2>(b, off, tiles);     s.offsets[2] = (char*)s.ranges - b;
-    s.tile_order = carve_arr<uint32_t>(b, off, tiles);
+    s.tile_order = carve_arr<uint32_t>(b, off, tiles + 4);
     s.bytes = align_up(off, 128);
     return s;
 }
