@@ -65,6 +65,8 @@ def forward(sc, cam, bg, indices=None, parent_indices=None, ts=None, kids=None, 
         res["final_T"] = _view(img, im[0], W * H * 4, torch.float32, (H, W))
         res["n_contrib"] = _view(img, im[1], W * H * 4, torch.int32, (H, W))
         res["ranges"] = _view(img, im[2], ntiles * 8, torch.int32, (ntiles, 2))
+        o_order = (im[2] + ntiles * 8 + 127) // 128 * 128                           # csrc/state.cuh: arrays are carved 128-byte aligned
+        res["tile_order"] = _view(img, o_order, (ntiles + 1) * 4, torch.int32, (ntiles + 1,))   # [ntiles] = number of LONG tiles
     return res
 
 

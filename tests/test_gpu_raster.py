@@ -128,6 +128,58 @@ def test_side_by_side_with_reference_build(P, W, H, lod):
         assert rel_l2(gm[k], gr[k]) <= 1e-3, k
 
 
+@pytest.mark.skipif(not refshim.available(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("lod", [False, True])
+def test_skewed_view_takes_the_long_tile_split_and_stays_bit_identical(lod):
+    """Half of the Gaussians (faint ones, so that nothing saturates early) sit in a small patch of the screen: a few tiles carry lists far
+    longer than 1/1024 of all instances, tile_order_kernel marks them LONG, and both blend kernels take them with two half-tile CTAs of
+    two pixels per thread (blend_fwd.cu / blend_bwd.cu). Same bar as the plain side-by-side test: integers, image, final_T bit-identical
+    to the reference build, gradients <= 1e-3 relative L2."""
+    P, W, H = 120_000, 1280, 720
+    cam_np = synth.make_camera(W=W, H=H, fx=800.0, fy=800.0)
+    sc_np = synth.make_gaussians(P, seed=11, tanfovx=cam_np["tanfovx"], tanfovy=cam_np["tanfovy"])
+    rng = np.random.default_rng(5)
+    n = P // 2
+    z = rng.uniform(2.0, 30.0, n).astype(np.float32)
+    sc_np["means3D"][:n, 0] = rng.uniform(-0.04, 0.04, n).astype(np.float32) * z
+    sc_np["means3D"][:n, 1] = rng.uniform(-0.03, 0.03, n).astype(np.float32) * z
+    sc_np["means3D"][:n, 2] = z
+    sc_np["opacities"][:n] *= 0.05
+    sc, cam, bg = cu(sc_np), cu(cam_np), torch.tensor([0.1, 0.2, 0.3], device="cuda")
+    kw = {}
+    if lod:
+        g = torch.Generator().manual_seed(4)
+        K = (3 * P) // 4
+        par = torch.randint(0, P, (K,), generator=g).int()
+        par[torch.rand(K, generator=g) < 0.25] = -1
+        kw = {"indices": torch.randperm(P, generator=g)[:K].sort().values.int().cuda(), "parent_indices": par.cuda(),
+              "ts": torch.rand(K, generator=g).cuda(), "kids": torch.randint(1, 6, (K,), generator=g).int().cuda()}
+    m = minewrap.forward(sc, cam, bg, **kw)
+    r = refshim.forward(sc, cam, bg, **kw)
+    ntiles = ((W + 15) // 16) * ((H + 15) // 16)
+    lens = (m["ranges"][:, 1] - m["ranges"][:, 0]).long()
+    n_long = int(m["tile_order"][ntiles])
+    if "LODGS_LONG_TILES" not in os.environ and "LODGS_FWD_PX" not in os.environ:
+        assert int(lens.max()) * 1024 > int(lens.sum()) and 0 < n_long <= 2048, (int(lens.max()), int(lens.sum()), n_long)
+        long_tiles = m["tile_order"][:n_long].long()
+        assert int(lens[long_tiles].min()) >= int(lens.max()) // 8                  # the marked tiles are the longest ones
+        assert sorted(m["tile_order"][:ntiles].tolist()) == list(range(ntiles))     # and the order is still a permutation
+    assert m["R"] == r["R"]
+    for k in INT_KEYS:
+        assert torch.equal(m[k].long(), r[k].long()), k
+    assert torch.equal(m["final_T"], r["final_T"])
+    assert torch.equal(m["color"], r["color"]) and torch.equal(m["invdepth"], r["invdepth"])
+    torch.manual_seed(0)
+    dL = (torch.rand(3, H, W, device="cuda") - 0.5) / (H * W)
+    dLi = (torch.rand(1, H, W, device="cuda") - 0.5) / (H * W)
+    gm = minewrap.backward(sc, cam, bg, m, dL, dLi, **kw)
+    gr = refshim.backward(sc, cam, bg, r, dL, dLi, **kw)
+    for k in GRAD_KEYS:
+        if lod and k == "dL_dmean3D":
+            continue
+        assert rel_l2(gm[k], gr[k]) <= 1e-3, k
+
+
 def test_full_size_properties():
     """1 M Gaussians at 1080p (BASELINE configs[1]): size-independent invariants of every stage."""
     cam_np = synth.make_camera()
