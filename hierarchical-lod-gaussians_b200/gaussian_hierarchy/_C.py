@@ -5,6 +5,7 @@ Device conventions of the reference are kept: expand_to_size takes
 inside the kernel) and `viewdir` as a CPU tensor; get_interpolation_weights reads `viewpoint` on the host. Either
 device is accepted and copied as needed."""
 import ctypes as C
+import os
 
 import torch
 
@@ -67,6 +68,8 @@ def expand_to_size(nodes, boxes, size, viewpoint, viewdir, render_indices, paren
     N = nodes.size(0)
     vp = viewpoint.to(device=dev, dtype=torch.float32).contiguous()
     key = _hier_key(nodes, boxes)
+    if mode is None and os.environ.get("LODGS_CUT_MODE"):        # A/B: 0 = flat pass, 1 = level-synchronous traversal
+        mode = int(os.environ["LODGS_CUT_MODE"])
     if mode is None:
         # traversal only pays on a big hierarchy cut shallowly; the previous frame's K is the predictor (first call: flat)
         mode = 1 if (N >= TRAVERSAL_MIN_NODES and _traversable.get(key, False)
