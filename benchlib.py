@@ -547,6 +547,9 @@ def run_reference(args, rank, world, dev):
         extra["train"]["optimizer_class"] = getattr(arm, "opt_kind", None)
     del arm
     extra.update(_sections("reference", args, rank, world, dev))
+    extra["native_code_note"] = ("timed regions of this arm run only the reference's code (oracle/_ref/ref_dgr/_C.so, libref_lodgs.so, scene/OurAdam.py or its "
+                                 "pinned restatement); liblodgs.so is loaded by the hier_step / eval_path sections to BUILD the synthetic hierarchy both arms "
+                                 "consume (lodgs_hier_build, untimed) — with --sections '' it is not loaded at all")
     if rank != 0:
         return None
     return _line(args, world, value, ms / args.steps, clocks, extra)
