@@ -29,9 +29,11 @@ constexpr int SCAN_ITEMS = 8;
 constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_TILE = SCAN_ITEMS * SCAN_THREADS;
 
-__global__ void __launch_bounds__(SCAN_THREADS) scan_sorted_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__ tile_box,
-                                                                  uint32_t* __restrict__ sorted_offsets, unsigned long long* state,
-                                                                  int* ticket) {
+__global__ void __launch_bounds__(SCAN_THREADS) scan_sorted_kernel(int P, const int* __restrict__ n_dev, const uint32_t* __restrict__ order,
+                                                                  const uint2* __restrict__ tile_box, uint32_t* __restrict__ sorted_offsets,
+                                                                  unsigned long long* state, int* ticket) {
+    // n_dev != NULL: only the first *n_dev positions of `order` are valid (compacted depth sort); the others count zero tiles
+    const int n_valid = n_dev ? min(P, __ldg(n_dev)) : P;
     __shared__ int s_tile;
     __shared__ unsigned s_warp_total[SCAN_THREADS / 32];
     __shared__ unsigned long long s_prefix;
@@ -44,12 +46,12 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_sorted_kernel(int P, const 
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; k++) {
         const int pos = wbase + k * 32 + (int)lane;
-        gid[k] = pos < P ? __ldg(order + pos) : 0u;
+        gid[k] = pos < n_valid ? __ldg(order + pos) : 0u;
     }
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; k++) {
         const int pos = wbase + k * 32 + (int)lane;
-        const uint2 b = pos < P ? __ldg(tile_box + gid[k]) : make_uint2(0u, 0u);
+        const uint2 b = pos < n_valid ? __ldg(tile_box + gid[k]) : make_uint2(0u, 0u);
         cnt[k] = ((b.y & 0xffffu) - (b.x & 0xffffu)) * ((b.y >> 16) - (b.x >> 16));
     }
     unsigned incl[SCAN_ITEMS];
@@ -88,6 +90,66 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_sorted_kernel(int P, const 
     for (int k = 0; k < SCAN_ITEMS; k++) {
         const int pos = wbase + k * 32 + (int)lane;
         if (pos < P) sorted_offsets[pos] = warp_off + incl[k];
+    }
+}
+
+// Render-list mode (the list comes from a hierarchy cut and is not view-culled: most entries fail the frustum test): the depth sort runs on
+// the visible entries only. One pass keeps {depth key, list position} of every entry with a key, in list order (block scan + decoupled
+// look-back, like the scan above), and leaves their number in the header; the sort and the scan above then work on that many elements.
+__global__ void __launch_bounds__(SCAN_THREADS) depth_compact_kernel(int P, const uint32_t* __restrict__ depth_keys, uint32_t* __restrict__ keys_out,
+                                                                    uint32_t* __restrict__ vals_out, unsigned long long* state, int* ticket,
+                                                                    int* __restrict__ n_out) {
+    __shared__ int s_tile;
+    __shared__ unsigned s_warp_total[SCAN_THREADS / 32];
+    __shared__ unsigned long long s_prefix;
+    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1);
+    __syncthreads();
+    const int tile = s_tile;
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int wbase = tile * SCAN_TILE + (int)warp * (32 * SCAN_ITEMS);
+    uint32_t key[SCAN_ITEMS];
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        const int pos = wbase + k * 32 + (int)lane;
+        key[k] = pos < P ? __ldg(depth_keys + pos) : 0xffffffffu;
+    }
+    unsigned before[SCAN_ITEMS];   // kept entries of this warp before item k of this lane
+    unsigned run = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        const unsigned m = __ballot_sync(0xffffffffu, key[k] != 0xffffffffu);
+        before[k] = run + __popc(m & ((1u << lane) - 1u));
+        run += __popc(m);
+    }
+    if (lane == 0) s_warp_total[warp] = run;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned block_total = 0;
+#pragma unroll
+        for (int w = 0; w < SCAN_THREADS / 32; w++) block_total += s_warp_total[w];
+        unsigned long long ex = 0;
+        if (tile == 0) {
+            if (lane == 0) st_relaxed(state, pack_state(2, block_total));
+        } else {
+            if (lane == 0) st_relaxed(state + tile, pack_state(1, block_total));
+            ex = lookback_warp(state, tile);
+            if (lane == 0) st_relaxed(state + tile, pack_state(2, ex + block_total));
+        }
+        if (lane == 0) {
+            s_prefix = ex;
+            if (tile == (P + SCAN_TILE - 1) / SCAN_TILE - 1) *n_out = (int)(ex + block_total);
+        }
+    }
+    __syncthreads();
+    unsigned warp_off = (unsigned)s_prefix;
+    for (unsigned w = 0; w < warp; w++) warp_off += s_warp_total[w];
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        if (key[k] != 0xffffffffu) {
+            const unsigned dst = warp_off + before[k];
+            keys_out[dst] = key[k];
+            vals_out[dst] = (uint32_t)(wbase + k * 32 + (int)lane);
+        }
     }
 }
 
@@ -293,10 +355,17 @@ __global__ void __launch_bounds__(256) sorted_keys_kernel(int R, const uint32_t*
     keys[i] = ((uint64_t)__ldg(tiles_sorted + i) << 32) | (uint64_t)__ldg(depth_keys + __ldg(point_list + i));
 }
 
-int launch_scan_sorted(int P, const GeomState& g, cudaStream_t s) {
-    scan_sorted_kernel<<<(P + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, s>>>(P, g.order, g.tile_box, g.sorted_offsets, g.scan2_state,
+int launch_scan_sorted(int P, const int* n_dev, const GeomState& g, cudaStream_t s) {
+    scan_sorted_kernel<<<(P + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, s>>>(P, n_dev, g.order, g.tile_box, g.sorted_offsets, g.scan2_state,
                                                                                &g.hdr->ticket2);
     LODGS_LAUNCHED("scan_sorted_kernel");
+    return LODGS_OK;
+}
+int launch_depth_compact(int P, const GeomState& g, cudaStream_t s) {
+    // look-back states and ticket of the (retired) fused scan of the preprocess kernel: cleared with the header at the start of the forward
+    depth_compact_kernel<<<(P + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, s>>>(P, g.depth_keys, g.compact_keys, g.compact_vals, g.scan_state,
+                                                                                 &g.hdr->ticket, &g.hdr->n_visible);
+    LODGS_LAUNCHED("depth_compact_kernel");
     return LODGS_OK;
 }
 int launch_emit_balanced(int P, int R, const GeomState& g, unsigned gx, uint32_t* tiles, uint32_t* vals, cudaStream_t s) {

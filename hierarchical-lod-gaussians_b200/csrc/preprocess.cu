@@ -6,6 +6,7 @@
 // per-Gaussian offsets are produced later in DEPTH order (binning.cu), which is the order instances are emitted in. SH coefficients (192 B per Gaussian at
 // degree 3) and quaternions move as 16-byte vector loads.
 #include "gaussmath.cuh"
+#include <cstdlib>
 #include "state.cuh"
 #include <cfloat>
 
@@ -15,7 +16,11 @@ int sort_pairs32_device(const uint32_t* keys_in, const uint32_t* vals_in, uint32
                         uint32_t* vals_tmp, int n, int begin_bit, int end_bit, void* ws, cudaStream_t s, const char* pass_name,
                         const char* hist_name);
 
-int launch_scan_sorted(int P, const GeomState& g, cudaStream_t s);
+int launch_scan_sorted(int P, const int* n_dev, const GeomState& g, cudaStream_t s);
+int launch_depth_compact(int P, const GeomState& g, cudaStream_t s);
+int sort_pairs32_device_n(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* keys_out, uint32_t* vals_out, uint32_t* keys_tmp,
+                          uint32_t* vals_tmp, int n, const int* n_dev, int begin_bit, int end_bit, void* ws, cudaStream_t s, const char* pass_name,
+                          const char* hist_name);
 
 struct PreParams {
     int P, D, M, W, H;
@@ -355,10 +360,25 @@ extern "C" int lodgs_forward_preprocess_lod(int P, int D, int M, int W, int H, c
         const int prc = publish_words(reinterpret_cast<const int32_t*>(&g.hdr->num_rendered), 1, s);
         if (prc) return prc;
     }
-    int rc = sort_pairs32_device(g.depth_keys, nullptr, g.depth_keys_sorted, g.order, g.sort_tmp_k, g.sort_tmp_v, P, 0, 32, g.sort_ws, s, "sort_depth_pass_kernel",
+    // Render-list mode: the list is a hierarchy cut, not view-culled, so most entries carry no depth key; the sort then runs on the
+    // compacted visible entries (their number stays on the device). LODGS_DEPTH_COMPACT=0 / 2 switches it off / on for every call (A/B).
+    static const int compact_mode = getenv("LODGS_DEPTH_COMPACT") ? atoi(getenv("LODGS_DEPTH_COMPACT")) : 1;
+    const bool compact = compact_mode == 2 || (compact_mode == 1 && indices != nullptr);
+    int rc;
+    if (compact) {
+        rc = launch_depth_compact(P, g, s);
+        if (rc) return rc;
+        const int* n_vis = &g.hdr->n_visible;
+        rc = sort_pairs32_device_n(g.compact_keys, g.compact_vals, g.depth_keys_sorted, g.order, g.sort_tmp_k, g.sort_tmp_v, P, n_vis, 0, 32, g.sort_ws, s,
+                                   "sort_depth_pass_kernel", "sort_depth_hist_kernel");
+        if (rc) return rc;
+        rc = launch_scan_sorted(P, n_vis, g, s);
+    } else {
+        rc = sort_pairs32_device(g.depth_keys, nullptr, g.depth_keys_sorted, g.order, g.sort_tmp_k, g.sort_tmp_v, P, 0, 32, g.sort_ws, s, "sort_depth_pass_kernel",
                                  "sort_depth_hist_kernel");
-    if (rc) return rc;
-    rc = launch_scan_sorted(P, g, s);
+        if (rc) return rc;
+        rc = launch_scan_sorted(P, nullptr, g, s);
+    }
     if (rc) return rc;
     if (num_rendered_host) {
         const int32_t* w = wait_words();

@@ -19,9 +19,10 @@ constexpr int SORT_WARPS = SORT_THREADS / 32;
 
 // ---- global histograms for all passes in one read of the keys
 template <typename KeyT>
-__global__ void __launch_bounds__(256) sort_histogram_kernel(const KeyT* __restrict__ keys, int n, int passes, int begin_bit,
-                                                            unsigned* hist) {
+__global__ void __launch_bounds__(256) sort_histogram_kernel(const KeyT* __restrict__ keys, int n, const int* __restrict__ n_dev, int passes,
+                                                            int begin_bit, unsigned* hist) {
     __shared__ unsigned s_hist[SORT_MAX_PASSES * SORT_RADIX];
+    if (n_dev) n = min(n, __ldg(n_dev));   // element count known only on the device (n = the capacity the grid was sized for)
     for (int i = threadIdx.x; i < passes * SORT_RADIX; i += blockDim.x) s_hist[i] = 0;
     __syncthreads();
     const unsigned lane = threadIdx.x & 31;
@@ -97,16 +98,19 @@ template <typename KeyT>
 __global__ void __launch_bounds__(SORT_THREADS, sizeof(KeyT) == 4 ? 4 : 2) sort_onesweep_kernel(const KeyT* __restrict__ keys_in,
                                                                     const uint32_t* __restrict__ vals_in,
                                                                     KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
-                                                                    int n, int shift, const unsigned* __restrict__ hist_base,
+                                                                    int n, const int* __restrict__ n_dev, int shift,
+                                                                    const unsigned* __restrict__ hist_base,
                                                                     int* ticket, unsigned* lookback /* [tiles][256] */) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SortSmem<KeyT>& sm = *reinterpret_cast<SortSmem<KeyT>*>(smem_raw);
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (n_dev) n = min(n, __ldg(n_dev));   // device-side count: the tiles beyond it leave at once (nobody looks back at a LATER tile)
     if (tid == 0) sm.tile = atomicAdd(ticket, 1);
     for (int i = tid; i < SORT_WARPS * SORT_RADIX; i += SORT_THREADS) (&sm.warp_hist[0][0])[i] = 0;
     __syncthreads();
     const int tile = sm.tile;
     const long long tile_base = (long long)tile * SORT_TILE;
+    if (tile_base >= (long long)n) return;
     const int tile_n = (int)min((long long)SORT_TILE, (long long)n - tile_base);
 
     // ---- load, warp-striped: item k of lane l in warp w is element w*512 + k*32 + l of the tile
@@ -269,7 +273,7 @@ __global__ void __launch_bounds__(SORT_THREADS, sizeof(KeyT) == 4 ? 4 : 2) sort_
 template <typename KeyT>
 int sort_pairs_device_t(const KeyT* keys_in, const uint32_t* vals_in, KeyT* keys_out, uint32_t* vals_out, KeyT* keys_tmp,
                         uint32_t* vals_tmp, int n, int begin_bit, int end_bit, void* ws, cudaStream_t s, const char* pass_name,
-                        const char* hist_name) {
+                        const char* hist_name, const int* n_dev = nullptr) {
     if (n <= 0) return LODGS_OK;
     int passes = (end_bit - begin_bit + 7) / 8;
     if (passes < 1) passes = 1;
@@ -284,7 +288,7 @@ int sort_pairs_device_t(const KeyT* keys_in, const uint32_t* vals_in, KeyT* keys
         attr_set[dslot].store(true, std::memory_order_release);
     }
     int hist_blocks = (int)min((size_t)148 * 4, ((size_t)n + 2047) / 2048);
-    sort_histogram_kernel<KeyT><<<hist_blocks, 256, 0, s>>>(keys_in, n, passes, begin_bit, w.hist);
+    sort_histogram_kernel<KeyT><<<hist_blocks, 256, 0, s>>>(keys_in, n, n_dev, passes, begin_bit, w.hist);
     LODGS_LAUNCHED(hist_name);
     const KeyT* kin = keys_in;
     const uint32_t* vin = vals_in;
@@ -293,7 +297,7 @@ int sort_pairs_device_t(const KeyT* keys_in, const uint32_t* vals_in, KeyT* keys
         KeyT* kout = to_out ? keys_out : keys_tmp;
         uint32_t* vout = to_out ? vals_out : vals_tmp;
         sort_onesweep_kernel<KeyT><<<(unsigned)tiles, SORT_THREADS, sizeof(SortSmem<KeyT>), s>>>(
-            kin, vin, kout, vout, n, begin_bit + 8 * p, w.hist + p * SORT_RADIX, w.tickets + p, w.lookback + (size_t)p * tiles * SORT_RADIX);
+            kin, vin, kout, vout, n, n_dev, begin_bit + 8 * p, w.hist + p * SORT_RADIX, w.tickets + p, w.lookback + (size_t)p * tiles * SORT_RADIX);
         LODGS_LAUNCHED(pass_name);
         kin = kout;
         vin = vout;
@@ -311,6 +315,13 @@ int sort_pairs32_device(const uint32_t* keys_in, const uint32_t* vals_in, uint32
                         const char* hist_name) {
     return sort_pairs_device_t<uint32_t>(keys_in, vals_in, keys_out, vals_out, keys_tmp, vals_tmp, n, begin_bit, end_bit, ws, s, pass_name,
                                          hist_name);
+}
+// the same with the element count on the device (*n_dev <= n): the launches are sized for n, the work follows *n_dev
+int sort_pairs32_device_n(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* keys_out, uint32_t* vals_out, uint32_t* keys_tmp,
+                          uint32_t* vals_tmp, int n, const int* n_dev, int begin_bit, int end_bit, void* ws, cudaStream_t s, const char* pass_name,
+                          const char* hist_name) {
+    return sort_pairs_device_t<uint32_t>(keys_in, vals_in, keys_out, vals_out, keys_tmp, vals_tmp, n, begin_bit, end_bit, ws, s, pass_name,
+                                         hist_name, n_dev);
 }
 
 }  // namespace lodgs
