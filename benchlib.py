@@ -464,7 +464,7 @@ def run_ours(args, rank, world, dev):
     prof = lodgs.profile_dump()
     lodgs.profile(False)
     clocks = sampler.stop() if sampler else None
-    ms_e2e = _timed(arm.step_e2e, args.steps, max(3, args.warmup // 2), world, dev, finish_fn=arm.finish_e2e)
+    ms_e2e = _timed(arm.step_e2e, args.steps, max(8, args.warmup), world, dev, finish_fn=arm.finish_e2e)
     h2d, d2h = arm.io_bytes()
     floor_ms = _copy_floor(arm, args.steps, world, dev)
     mpix = W * H / 1e6
@@ -528,7 +528,7 @@ def run_reference(args, rank, world, dev):
     sampler = ClockSampler(dev.index) if rank == 0 else None
     ms = _timed(arm.step_resident, args.steps, args.warmup, world, dev, sampler)
     clocks = sampler.stop() if sampler else None
-    ms_e2e = _timed(arm.step_e2e, args.steps, max(3, args.warmup // 2), world, dev, finish_fn=arm.finish_e2e)
+    ms_e2e = _timed(arm.step_e2e, args.steps, max(8, args.warmup), world, dev, finish_fn=arm.finish_e2e)
     h2d, d2h = arm.io_bytes()
     floor_ms = _copy_floor(arm, args.steps, world, dev)
     mpix = W * H / 1e6
