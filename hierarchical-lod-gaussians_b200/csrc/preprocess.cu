@@ -369,6 +369,7 @@ extern "C" int lodgs_forward_preprocess_lod(int P, int D, int M, int W, int H, c
         rc = launch_depth_compact(P, g, s);
         if (rc) return rc;
         const int* n_vis = &g.hdr->n_visible;
+        // input = output arrays on purpose (state.cuh): with 32 key bits there are four passes, tmp <- in, out <- tmp, tmp <- out, out <- tmp
         rc = sort_pairs32_device_n(g.compact_keys, g.compact_vals, g.depth_keys_sorted, g.order, g.sort_tmp_k, g.sort_tmp_v, P, n_vis, 0, 32, g.sort_ws, s,
                                    "sort_depth_pass_kernel", "sort_depth_hist_kernel");
         if (rc) return rc;

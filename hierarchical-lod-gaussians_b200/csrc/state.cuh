@@ -52,8 +52,10 @@ struct GeomState {
     uint32_t* sort_tmp_v;            // [P]
     uint32_t* sorted_offsets;        // [P] inclusive scan of the tile counts in depth order
     uint2* tile_box;                 // [P] tile rectangle {min.x | min.y<<16, max.x | max.y<<16}, 0 for culled Gaussians
-    uint32_t* compact_keys;          // [P] depth keys of the visible entries, in list order (render-list mode: most entries are culled)
-    uint32_t* compact_vals;          // [P] their list positions
+    // render-list mode: {depth key, list position} of the visible entries in list order (binning.cu depth_compact_kernel). They are the INPUT
+    // of the depth sort's first pass only, and that pass (of four) writes the ping-pong pair, so they live in the sort's OUTPUT arrays.
+    uint32_t* compact_keys;          // = depth_keys_sorted
+    uint32_t* compact_vals;          // = order
     unsigned long long* scan2_state; // [ceil(P/PRE_BLOCK)+1] look-back states of the emission's scan
     void* sort_ws;                   // radix sort workspace for P pairs
     size_t offsets[9];
@@ -89,8 +91,8 @@ static inline GeomState geom_from_chunk(void* chunk, size_t P) {
     g.sort_tmp_v = carve_arr<uint32_t>(b, off, P);
     g.sorted_offsets = carve_arr<uint32_t>(b, off, P);
     g.tile_box = carve_arr<uint2>(b, off, P);
-    g.compact_keys = carve_arr<uint32_t>(b, off, P);
-    g.compact_vals = carve_arr<uint32_t>(b, off, P);
+    g.compact_keys = g.depth_keys_sorted;
+    g.compact_vals = g.order;
     off = align_up(off, 128);
     g.sort_ws = b + off;
     off += sort_ws_bytes(P);
